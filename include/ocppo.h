@@ -1,0 +1,176 @@
+/* ocppo.h -- C ABI of libocppo.so: the B200 (sm_100a) PPO_OBJ learner hot path.
+ *
+ * The reference (BluemlJ/oc_cleanrl) is 100% Python and has no FFI for this
+ * path; every entry point below replaces a span of eager-torch code and cites
+ * it (paths relative to the reference root).  INTEGRATION.md shows the ctypes
+ * binding a reference maintainer would add.
+ *
+ * Conventions
+ *  - plain C types only; all data pointers are DEVICE pointers owned by the
+ *    caller (torch tensors), fp32 unless stated; `stream` is a cudaStream_t
+ *    passed as void*; calls are asynchronous on that stream and never
+ *    synchronise, allocate or start threads.
+ *  - every function returns 0 on success or a negative OCPPO_E* code;
+ *    ocppo_last_error() returns a thread-local message.  Nothing throws.
+ *  - there is no CPU fallback: a device that is not sm_100 is an error.
+ */
+#ifndef OCPPO_H
+#define OCPPO_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OCPPO_OK 0
+#define OCPPO_EINVAL (-1)   /* bad argument / unsupported shape          */
+#define OCPPO_ECUDA (-2)    /* CUDA runtime error (see last_error)       */
+#define OCPPO_EARCH (-3)    /* device is not compute capability 10.x     */
+#define OCPPO_ESTATE (-4)   /* arena / workspace not bound               */
+
+#define OCPPO_MAX_LAYERS 8
+#define OCPPO_MAX_ACTIONS 31
+#define OCPPO_NUM_STATS 8
+
+typedef struct ocppo_handle ocppo_handle;
+
+/* Shape of PPObj: cleanrl/architectures/ppo.py:61-84.  observation_space.shape
+ * = (frames, obs_dim); encoder acts on the last dim of (B, frames, obs_dim),
+ * Flatten, decoder, then actor (n_actions) and critic (1) heads. */
+typedef struct ocppo_config {
+    int32_t frames;
+    int32_t obs_dim;
+    int32_t n_actions;
+    int32_t n_encoder;
+    int32_t encoder_dims[OCPPO_MAX_LAYERS];
+    int32_t n_decoder;
+    int32_t decoder_dims[OCPPO_MAX_LAYERS];
+    int32_t device;          /* CUDA ordinal */
+    int32_t reserved;
+} ocppo_config;
+
+/* Hyper-parameters of one minibatch: cleanrl/ppo_atari_oc.py:127-151. */
+typedef struct ocppo_hparams {
+    double clip_coef;        /* python floats: kept in double, rounded per op */
+    double ent_coef;
+    double vf_coef;
+    int32_t norm_adv;        /* :577-579 */
+    int32_t clip_vloss;      /* :586-597 */
+} ocppo_hparams;
+
+/* stats[] slots written by ocppo_minibatch_fwd_bwd (:573-575,:599-602) */
+enum {
+    OCPPO_STAT_PG_LOSS = 0,
+    OCPPO_STAT_V_LOSS = 1,
+    OCPPO_STAT_ENTROPY = 2,
+    OCPPO_STAT_LOSS = 3,
+    OCPPO_STAT_OLD_APPROX_KL = 4,
+    OCPPO_STAT_APPROX_KL = 5,
+    OCPPO_STAT_CLIPFRAC = 6,
+    OCPPO_STAT_RESERVED = 7
+};
+
+const char *ocppo_last_error(void);
+int ocppo_version(void);
+
+/* ---- launch accounting / live kernel timing (measurement only) ---------- */
+/* Kernel classes: 0 GAE, 1 SGEMM fwd, 2 SGEMM dgrad, 3 SGEMM wgrad, 4 heads,
+ * 5 aux (gather/reduce/stats), 6 clip+Adam.  ocppo_launch_count() = kernels
+ * launched by this library since load.  With profiling enabled every launch is
+ * bracketed by CUDA events on its own stream; ocppo_profile_read() waits for
+ * them and returns the summed milliseconds and number of timed launches per
+ * class (8 slots), then clears the log. */
+#define OCPPO_NUM_KERNEL_CLASSES 8
+int64_t ocppo_launch_count(void);
+int ocppo_profile_enable(int32_t on);
+int ocppo_profile_read(double *ms_by_class, int64_t *timed_by_class, int32_t n_classes);
+
+/* ---- handle ------------------------------------------------------------ */
+/* Replaces PPObj.__init__ bookkeeping (architectures/ppo.py:61-84). */
+int ocppo_create(const ocppo_config *cfg, ocppo_handle **out);
+int ocppo_destroy(ocppo_handle *h);
+
+/* Number of parameter tensors (2 per Linear, nn.Module.parameters() order:
+ * network.0.weight, network.0.bias, ..., actor.weight, actor.bias,
+ * critic.weight, critic.bias) and the padded arena length in floats. */
+int ocppo_num_tensors(const ocppo_handle *h, int32_t *n_tensors, int64_t *arena_floats,
+                      int64_t *param_floats);
+/* Tensor i lives at arena[offset .. offset+rows*cols), row-major (out,in) as
+ * nn.Linear.weight; biases have cols == 1.  Gaps between tensors are padding
+ * (kept zero) so every tensor starts 128-byte aligned. */
+int ocppo_tensor_layout(const ocppo_handle *h, int32_t i, int64_t *offset, int32_t *rows,
+                        int32_t *cols);
+/* Bind the four flat fp32 arenas (params, grads, Adam exp_avg, exp_avg_sq),
+ * each arena_floats long.  grads is the buffer ppo_atari_multigpu.py:362-374
+ * builds with torch.cat and all-reduces. */
+int ocppo_bind_arena(ocppo_handle *h, float *params, float *grads, float *exp_avg,
+                     float *exp_avg_sq);
+/* Workspace for at most `max_rows` samples per forward/backward chunk. */
+int ocppo_workspace_bytes(const ocppo_handle *h, int64_t max_rows, int32_t training,
+                          int64_t *bytes);
+int ocppo_bind_workspace(ocppo_handle *h, void *workspace, int64_t bytes, int64_t max_rows,
+                         int32_t training);
+
+/* ---- rollout inference -------------------------------------------------- */
+/* PPObj.get_action_and_value(x) under no_grad, cleanrl/ppo_atari_oc.py:505-509
+ * + architectures/ppo.py:89-95.  obs (B,frames,obs_dim).  Sampling follows
+ * torch-CUDA Categorical.sample(): argmax(softmax(l)/q), q = Exp(1) from
+ * Philox4x32-10 at (seed, philox_offset) in torch's element layout.  If
+ * `given_action` != NULL it is used instead of sampling (ppo.py:93-94).
+ * Outputs: action int64 (B,), logp/entropy/value fp32 (B,); any may be NULL. */
+int ocppo_policy_step(ocppo_handle *h, const float *obs, int64_t B, uint64_t seed,
+                      uint64_t philox_offset, const int64_t *given_action, int64_t *action,
+                      float *logp, float *entropy, float *value, void *stream);
+/* PPObj.get_value(x), architectures/ppo.py:86-87 (ppo_atari_oc.py:534). */
+int ocppo_value(ocppo_handle *h, const float *obs, int64_t B, float *value, void *stream);
+/* torch.distributions.Categorical(logits=...) on given logits (B,A):
+ * sample / log_prob / entropy (architectures/ppo.py:92-95). */
+int ocppo_categorical(const float *logits, int64_t B, int32_t A, uint64_t seed,
+                      uint64_t philox_offset, const int64_t *given_action, int64_t *action,
+                      float *logp, float *entropy, void *stream);
+/* Offset increment torch's generator applies for one exponential_ of `numel`. */
+uint64_t ocppo_philox_increment(int64_t numel, int32_t sm_count, int32_t max_threads_per_sm);
+/* The Exp(1) variates themselves (parity test vs torch.empty().exponential_()). */
+int ocppo_exponential(float *out, int64_t numel, uint64_t seed, uint64_t philox_offset,
+                      void *stream);
+
+/* ---- GAE ---------------------------------------------------------------- */
+/* cleanrl/ppo_atari_oc.py:535-547.  rewards/values/dones/adv/ret are (T,N)
+ * row-major; next_value, next_done (N,).  Stateless. */
+int ocppo_gae(const float *rewards, const float *values, const float *dones,
+              const float *next_value, const float *next_done, int64_t T, int64_t N,
+              double gamma, double gae_lambda, float *advantages, float *returns,
+              void *stream);
+
+/* ---- PPO update ---------------------------------------------------------- */
+/* One minibatch of cleanrl/ppo_atari_oc.py:563-608: gather rows `idx` (int64,
+ * mb of them; flat index t*N+n) of the flattened rollout buffers, forward,
+ * losses, backward; overwrites the grad arena with d(loss)/d(params) and
+ * writes OCPPO_NUM_STATS floats to `stats` (device). */
+int ocppo_minibatch_fwd_bwd(ocppo_handle *h, const float *b_obs, const int64_t *b_actions,
+                            const float *b_logprobs, const float *b_advantages,
+                            const float *b_returns, const float *b_values, const int64_t *idx,
+                            int64_t mb, const ocppo_hparams *hp, float *stats, void *stream);
+/* nn.utils.clip_grad_norm_ + optim.Adam.step (cleanrl/ppo_atari_oc.py:609-610,
+ * :444), with the 1/world_size of ppo_atari_multigpu.py:368-374 folded in.
+ * `step` is the 1-based Adam step count.  grad_norm (device, 1 float) gets
+ * the pre-clip total norm. */
+int ocppo_clip_adam(ocppo_handle *h, float inv_world, float max_grad_norm, double lr,
+                    double beta1, double beta2, double eps, int64_t step, float *grad_norm,
+                    void *stream);
+
+/* ---- autograd bridge (compat tier: script's own loss/optimizer) --------- */
+/* Trunk forward keeping activations: hidden (B, decoder_dims[-1]). */
+int ocppo_trunk_forward(ocppo_handle *h, const float *obs, int64_t B, float *hidden,
+                        void *stream);
+/* Trunk backward from d(hidden) of the LAST ocppo_trunk_forward call; writes
+ * trunk weight/bias grads into the grad arena (heads untouched). */
+int ocppo_trunk_backward(ocppo_handle *h, const float *obs, int64_t B, const float *d_hidden,
+                         void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OCPPO_H */

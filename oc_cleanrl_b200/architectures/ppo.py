@@ -1,0 +1,226 @@
+"""Drop-in ``PPObj`` (reference: ``cleanrl/architectures/ppo.py:60-95``).
+
+Same constructor, ``get_value`` / ``get_action_and_value`` surface, parameter
+names and ``parameters()`` order as the reference class, so
+``cleanrl/ppo_atari_oc.py:438-444`` (``Agent(envs, device, encoder_dims,
+decoder_dims).to(device)`` + ``optim.Adam(agent.parameters())``) works unchanged.
+
+Differences in mechanism, not in behaviour:
+  * once the module sits on a CUDA device its parameters become views of one
+    flat fp32 arena (``self.arena``), the buffer the CUDA kernels read and the
+    buffer a data-parallel learner all-reduces (ppo_atari_multigpu.py:360-374);
+  * forward passes run in ``libocppo.so``; under ``torch.no_grad`` the whole
+    of ppo.py:89-95 (MLP, logits, Categorical sample, log-prob, entropy, value)
+    is the fused rollout path, and sampling consumes torch's CUDA Philox
+    generator exactly like ``Categorical.sample()`` would;
+  * with grad enabled the trunk is a ``torch.autograd.Function`` over the same
+    kernels (compat tier, so the script's own loss/backward/Adam keep working).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+import torch.nn as nn
+from torch.distributions.categorical import Categorical
+
+from .. import _abi
+from .common import Predictor, layer_init  # noqa: F401  (re-export like the reference)
+
+
+class _TrunkFunction(torch.autograd.Function):
+    """hidden = network(x) through libocppo, differentiable wrt the trunk params."""
+
+    @staticmethod
+    def forward(ctx, agent, x, *params):
+        B = x.shape[0]
+        agent._ensure_workspace(B, training=True)
+        hidden = torch.empty((B, agent._hidden), dtype=torch.float32, device=x.device)
+        _abi.check(_abi.lib().ocppo_trunk_forward(agent._handle.raw, _abi.ptr(x), B, _abi.ptr(hidden),
+                                                 agent._stream()))
+        ctx.agent = agent
+        ctx.save_for_backward(x)
+        ctx.version = agent._fwd_version = agent._fwd_version + 1
+        return hidden
+
+    @staticmethod
+    def backward(ctx, d_hidden):
+        agent = ctx.agent
+        if ctx.version != agent._fwd_version:
+            raise RuntimeError("PPObj compat tier keeps the activations of the latest grad-mode forward only")
+        (x,) = ctx.saved_tensors
+        d_hidden = d_hidden.contiguous()
+        _abi.check(_abi.lib().ocppo_trunk_backward(agent._handle.raw, _abi.ptr(x), x.shape[0],
+                                                  _abi.ptr(d_hidden), agent._stream()))
+        grads = [agent._grad_view(i).clone() for i in range(agent._n_trunk_tensors)]
+        return (None, None, *grads)
+
+
+class PPObj(Predictor):
+    def __init__(self, envs, device, encoder_dims=(128, 64), decoder_dims=(32,)):
+        super().__init__()
+        self.device = device
+        dims = envs.observation_space.shape
+        self._frames = int(np.prod(dims[:-1], dtype=int))
+        self._obs_dim = int(dims[-1])
+        self._n_actions = int(envs.action_space.n)
+        self._encoder_dims = tuple(int(d) for d in encoder_dims)
+        self._decoder_dims = tuple(int(d) for d in decoder_dims)
+
+        # Same module tree and RNG consumption as the reference (ppo.py:66-84).
+        mods = []
+        width = self._obs_dim
+        for out in self._encoder_dims:
+            mods += [layer_init(nn.Linear(width, out)), nn.ReLU()]
+            width = out
+        mods.append(nn.Flatten())
+        width *= self._frames
+        for out in self._decoder_dims:
+            mods += [layer_init(nn.Linear(width, out)), nn.ReLU()]
+            width = out
+        self.network = nn.Sequential(*mods)
+        self.actor = layer_init(nn.Linear(width, self._n_actions), std=0.01)
+        self.critic = layer_init(nn.Linear(width, 1), std=1)
+        self._hidden = width
+        self._n_trunk_tensors = 2 * (len(self._encoder_dims) + len(self._decoder_dims))
+
+        self._handle = None
+        self.arena = None           # flat fp32 parameters (padded), device
+        self.grad_arena = None
+        self.exp_avg = None
+        self.exp_avg_sq = None
+        self._workspace = None
+        self._ws_rows = 0
+        self._ws_training = False
+        self._fwd_version = 0
+
+    # ---- arena management ---------------------------------------------------
+    def _apply(self, fn, *args, **kwargs):
+        out = super()._apply(fn, *args, **kwargs)
+        p = next(self.parameters())
+        if p.is_cuda:
+            self._materialize(p.device)
+        return out
+
+    def _materialize(self, dev):
+        """Move the parameters into one flat device arena and re-point them."""
+        for p in self.parameters():
+            if p.dtype != torch.float32:
+                raise _abi.OcppoError("oc_cleanrl_b200.PPObj computes in fp32 only")
+        cfg = _abi.make_config(self._frames, self._obs_dim, self._n_actions, self._encoder_dims,
+                               self._decoder_dims, dev.index if dev.index is not None else torch.cuda.current_device())
+        self._handle = _abi.Handle(cfg)
+        h = self._handle
+        params = list(self.parameters())
+        if len(params) != h.n_tensors:
+            raise _abi.OcppoError("parameter list does not match the C layout")
+        with torch.no_grad():
+            arena = torch.zeros(h.arena_floats, dtype=torch.float32, device=dev)
+            for p, (off, rows, cols) in zip(params, h.layout):
+                if p.numel() != rows * cols:
+                    raise _abi.OcppoError("parameter shape does not match the C layout")
+                view = arena[off:off + rows * cols].view(p.shape)
+                view.copy_(p.data)
+                p.data = view
+        self.arena = arena
+        self.grad_arena = torch.zeros_like(arena)
+        self.exp_avg = torch.zeros_like(arena)
+        self.exp_avg_sq = torch.zeros_like(arena)
+        _abi.check(_abi.lib().ocppo_bind_arena(h.raw, _abi.ptr(self.arena), _abi.ptr(self.grad_arena),
+                                               _abi.ptr(self.exp_avg), _abi.ptr(self.exp_avg_sq)))
+        self._workspace, self._ws_rows, self._ws_training = None, 0, False
+        props = torch.cuda.get_device_properties(dev)
+        self._sm_count = props.multi_processor_count
+        self._max_threads_per_sm = props.max_threads_per_multi_processor
+        self._cuda_device = dev
+
+    def _require_handle(self):
+        if self._handle is None:
+            raise _abi.OcppoError(
+                "oc_cleanrl_b200.PPObj has no CPU path: move the agent to a CUDA (sm_100) device first")
+        return self._handle
+
+    def _ensure_workspace(self, rows, training):
+        h = self._require_handle()
+        if self._workspace is not None and rows <= self._ws_rows and (self._ws_training or not training):
+            return
+        rows = max(int(rows), self._ws_rows)
+        training = bool(training or self._ws_training)
+        nbytes = h.workspace_bytes(rows, training)
+        self._workspace = None
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=self._cuda_device)
+        _abi.check(_abi.lib().ocppo_bind_workspace(h.raw, _abi.ptr(ws), nbytes, rows, int(training)))
+        self._workspace, self._ws_rows, self._ws_training = ws, rows, training
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self._cuda_device).cuda_stream)
+
+    def _grad_view(self, i):
+        off, rows, cols = self._handle.layout[i]
+        p = list(self.parameters())[i]
+        return self.grad_arena[off:off + rows * cols].view(p.shape)
+
+    def _check_obs(self, x):
+        if not x.is_cuda:
+            raise _abi.OcppoError("observations must be on the agent's CUDA device (no CPU path)")
+        if x.dtype != torch.float32:
+            x = x.float()
+        x = x.contiguous()
+        if x.dim() < 2 or int(np.prod(x.shape[1:])) != self._frames * self._obs_dim:
+            raise _abi.OcppoError(f"expected observations (B,{self._frames},{self._obs_dim}), got {tuple(x.shape)}")
+        return x
+
+    def _philox_state(self, numel):
+        """Consume torch's CUDA generator the way ``exponential_`` of `numel`
+        elements would (ATen/native/cuda/DistributionTemplates.h:50-62)."""
+        gen = torch.cuda.default_generators[self._cuda_device.index]
+        seed, offset = gen.initial_seed(), gen.get_offset()
+        inc = _abi.lib().ocppo_philox_increment(numel, self._sm_count, self._max_threads_per_sm)
+        gen.set_offset(offset + inc)
+        return seed, offset
+
+    # ---- public surface (architectures/ppo.py:86-95) ---------------------------
+    def _needs_grad(self):
+        return torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters())
+
+    def _hidden_with_grad(self, x):
+        trunk = list(self.parameters())[: self._n_trunk_tensors]
+        return _TrunkFunction.apply(self, x, *trunk)
+
+    def get_value(self, x):
+        x = self._check_obs(x)
+        if self._needs_grad():
+            return self.critic(self._hidden_with_grad(x))
+        B = x.shape[0]
+        self._ensure_workspace(B, training=False)
+        value = torch.empty((B, 1), dtype=torch.float32, device=x.device)
+        _abi.check(_abi.lib().ocppo_value(self._handle.raw, _abi.ptr(x), B, _abi.ptr(value), self._stream()))
+        return value
+
+    def get_action_and_value(self, x, action=None):
+        x = self._check_obs(x)
+        if self._needs_grad():
+            hidden = self._hidden_with_grad(x)
+            logits = self.actor(hidden)
+            probs = Categorical(logits=logits)
+            if action is None:
+                action = probs.sample()
+            return action, probs.log_prob(action), probs.entropy(), self.critic(hidden)
+        B = x.shape[0]
+        self._ensure_workspace(B, training=False)
+        dev = x.device
+        out_action = torch.empty(B, dtype=torch.int64, device=dev)
+        logp = torch.empty(B, dtype=torch.float32, device=dev)
+        entropy = torch.empty(B, dtype=torch.float32, device=dev)
+        value = torch.empty((B, 1), dtype=torch.float32, device=dev)
+        given = None
+        seed = offset = 0
+        if action is None:
+            seed, offset = self._philox_state(B * self._n_actions)
+        else:
+            given = action.to(device=dev, dtype=torch.int64).contiguous()
+        _abi.check(_abi.lib().ocppo_policy_step(self._handle.raw, _abi.ptr(x), B, seed, offset, _abi.ptr(given),
+                                               _abi.ptr(out_action), _abi.ptr(logp), _abi.ptr(entropy),
+                                               _abi.ptr(value), self._stream()))
+        return out_action, logp, entropy, value

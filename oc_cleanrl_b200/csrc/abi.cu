@@ -1,0 +1,503 @@
+// C-ABI entry points of libocppo.so (declared in include/ocppo.h) and the
+// per-layer orchestration of the PPObj trunk forward / backward.
+#include "common.cuh"
+#include <math.h>
+#include <new>
+#include <string.h>
+
+namespace ocppo {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+// Live timing: when enabled every launch wrapper is bracketed by a pair of events on
+// its own stream; ocppo_profile_read() sums elapsed time per kernel class.
+static const int kProfMaxPairs = 8192;
+static struct {
+    bool on = false;
+    int n = 0;
+    cudaEvent_t start[kProfMaxPairs], stop[kProfMaxPairs];
+    int cls[kProfMaxPairs];
+    bool created = false;
+    int64_t launches[KC_COUNT] = {0};
+} g_prof;
+
+void prof_begin(int cls, int n_kernels, cudaStream_t s) {
+    g_prof.launches[cls] += n_kernels;
+    if (!g_prof.on || g_prof.n >= kProfMaxPairs) return;
+    g_prof.cls[g_prof.n] = cls;
+    cudaEventRecord(g_prof.start[g_prof.n], s);
+}
+void prof_end(cudaStream_t s) {
+    if (!g_prof.on || g_prof.n >= kProfMaxPairs) return;
+    cudaEventRecord(g_prof.stop[g_prof.n], s);
+    ++g_prof.n;
+}
+
+static inline cudaStream_t as_stream(void *s) { return reinterpret_cast<cudaStream_t>(s); }
+
+// ---- layout ---------------------------------------------------------------
+static int build_layout(ocppo_handle *h) {
+    const ocppo_config &c = h->cfg;
+    OCPPO_CHECK_ARG(c.frames >= 1 && c.obs_dim >= 1, "frames/obs_dim must be >= 1");
+    OCPPO_CHECK_ARG(c.n_actions >= 1 && c.n_actions <= OCPPO_MAX_ACTIONS, "n_actions must be in [1,%d]",
+                    OCPPO_MAX_ACTIONS);
+    OCPPO_CHECK_ARG(c.n_encoder >= 0 && c.n_encoder <= OCPPO_MAX_LAYERS, "bad n_encoder");
+    OCPPO_CHECK_ARG(c.n_decoder >= 0 && c.n_decoder <= OCPPO_MAX_LAYERS, "bad n_decoder");
+    OCPPO_CHECK_ARG(c.n_encoder + c.n_decoder >= 1, "need at least one trunk layer");
+    int64_t off = 0;
+    int nt = 0, nl = 0;
+    auto add_tensor = [&](int rows, int cols) {
+        h->tensor_off[nt] = off;
+        h->tensor_rows[nt] = rows;
+        h->tensor_cols[nt] = cols;
+        ++nt;
+        const int64_t o = off;
+        off = round_up(off + (int64_t)rows * cols, kArenaAlignFloats);
+        return o;
+    };
+    auto add_linear = [&](Layer &L, int in, int out, int mult) {
+        L.in_dim = in; L.out_dim = out; L.row_mult = mult;
+        L.w_off = add_tensor(out, in);
+        L.b_off = add_tensor(out, 1);
+    };
+    int width = c.obs_dim;
+    for (int i = 0; i < c.n_encoder; ++i) {
+        OCPPO_CHECK_ARG(c.encoder_dims[i] >= 1, "encoder dim must be >= 1");
+        add_linear(h->layers[nl++], width, c.encoder_dims[i], c.frames);
+        width = c.encoder_dims[i];
+    }
+    width *= c.frames;                               // nn.Flatten, architectures/ppo.py:74-75
+    for (int i = 0; i < c.n_decoder; ++i) {
+        OCPPO_CHECK_ARG(c.decoder_dims[i] >= 1, "decoder dim must be >= 1");
+        add_linear(h->layers[nl++], width, c.decoder_dims[i], 1);
+        width = c.decoder_dims[i];
+    }
+    // With no decoder the heads would read the flattened encoder output; the
+    // reference supports it (ppo.py:76,83) and so do we: hidden = frames * enc[-1].
+    h->n_layers = nl;
+    h->hidden = width;
+    add_linear(h->actor, width, c.n_actions, 1);
+    add_linear(h->critic, width, 1, 1);
+    h->n_tensors = nt;
+    h->arena_floats = off;
+    int64_t pf = 0;
+    for (int i = 0; i < nt; ++i) pf += (int64_t)h->tensor_rows[i] * h->tensor_cols[i];
+    h->param_floats = pf;
+    return OCPPO_OK;
+}
+
+struct Carver {
+    char *base;
+    int64_t off;
+    template <typename T>
+    T *take(int64_t count) {
+        T *p = base ? reinterpret_cast<T *>(base + off) : nullptr;
+        off = round_up(off + count * (int64_t)sizeof(T), 256);
+        return p;
+    }
+};
+
+static int64_t carve(ocppo_handle *h, void *base, int64_t R, int training, bool assign) {
+    Carver cv{reinterpret_cast<char *>(base), 0};
+    ocppo_handle tmp = *h;
+    ocppo_handle *t = assign ? h : &tmp;
+    const ocppo_config &c = h->cfg;
+    int64_t max_act = 0, max_w = 0, max_out = 0;
+    for (int l = 0; l < h->n_layers; ++l) {
+        const Layer &L = h->layers[l];
+        const int64_t n = R * L.row_mult * L.out_dim;
+        t->act[l] = cv.take<float>(n);
+        if (n > max_act) max_act = n;
+        if ((int64_t)L.out_dim * L.in_dim > max_w) max_w = (int64_t)L.out_dim * L.in_dim;
+        if (L.out_dim > max_out) max_out = L.out_dim;
+    }
+    const int AP = (int)round_up(c.n_actions + 1, 4);
+    if ((int64_t)AP * h->hidden > max_w) max_w = (int64_t)AP * h->hidden;
+    if (AP > max_out) max_out = AP;
+    if (training) {
+        t->x0 = cv.take<float>(R * c.frames * c.obs_dim);
+        t->gbuf[0] = cv.take<float>(max_act);
+        t->gbuf[1] = cv.take<float>(max_act);
+        t->gz = cv.take<float>(R * AP);
+        t->mb_action = cv.take<int32_t>(R);
+        t->mb_logp = cv.take<float>(R);
+        t->mb_adv = cv.take<float>(R);
+        t->mb_ret = cv.take<float>(R);
+        t->mb_val = cv.take<float>(R);
+        t->splitk = cv.take<float>((int64_t)kSplitMax * max_w);
+        t->splitk_bias = cv.take<float>((int64_t)kSplitMax * max_out);
+        t->loss_part = cv.take<double>((int64_t)kLossBlocksMax * 8);
+        t->adv_part = cv.take<double>((int64_t)kLossBlocksMax * 2);
+        t->adv_stat = cv.take<float>(8);
+        t->norm_part = cv.take<double>(kNormBlocks);
+    }
+    return cv.off;
+}
+
+static int require_ready(const ocppo_handle *h, bool need_training) {
+    if (h == nullptr) { set_error("null handle"); return OCPPO_EINVAL; }
+    if (h->cfg.device < 0) { set_error("layout-only handle (device < 0) cannot compute"); return OCPPO_ESTATE; }
+    if (h->params == nullptr) { set_error("arena not bound (ocppo_bind_arena)"); return OCPPO_ESTATE; }
+    if (h->ws == nullptr) { set_error("workspace not bound (ocppo_bind_workspace)"); return OCPPO_ESTATE; }
+    if (need_training && !h->training) { set_error("workspace was bound without training buffers"); return OCPPO_ESTATE; }
+    return OCPPO_OK;
+}
+
+// ---- trunk forward / backward ---------------------------------------------
+// x: [B*frames, obs_dim] contiguous.  Writes h->act[l] for every trunk layer.
+static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_t s) {
+    const float *in = x;
+    for (int l = 0; l < h->n_layers; ++l) {
+        const Layer &L = h->layers[l];
+        SgemmArgs a{};
+        a.A = in; a.lda = L.in_dim;
+        a.B = h->params + L.w_off; a.ldb = L.in_dim;
+        a.C = h->act[l]; a.ldc = L.out_dim;
+        a.bias = h->params + L.b_off;
+        a.M = (int)(B * L.row_mult); a.N = L.out_dim; a.K = L.in_dim;
+        a.k_per_split = round_up(L.in_dim, 8); a.splits = 1;
+        OCPPO_TRY(sgemm_launch(SGEMM_FWD, a, s));
+        in = h->act[l];
+    }
+    h->last_forward_rows = (int)B;
+    return OCPPO_OK;
+}
+
+static void pick_split(const ocppo_handle *h, int M, int N, int64_t K, int *splits, int64_t *k_per) {
+    const int64_t tiles = ceil_div(M, 128) * ceil_div(N, 128);
+    const int64_t target = (int64_t)h->sm_count * 4;
+    int64_t S = ceil_div(target, tiles);
+    const int64_t s_cap = K / 256 > 1 ? K / 256 : 1;
+    if (S > s_cap) S = s_cap;
+    if (S > kSplitMax) S = kSplitMax;
+    if (S < 1) S = 1;
+    int64_t kp = round_up(ceil_div(K, S), 8);
+    if (kp < 8) kp = 8;
+    *k_per = kp;
+    *splits = (int)ceil_div(K, kp);
+    if (*splits < 1) *splits = 1;
+}
+
+// dW[out,in] (+)= dY[rows,out]^T X[rows,in];  db[out] (+)= colsum(dY)
+static int wgrad(ocppo_handle *h, const float *dY, int out, const float *X, int in, int64_t rows, float *dW,
+                 int64_t w_count, float *db, int64_t b_count, int accumulate, cudaStream_t s) {
+    SgemmArgs a{};
+    a.A = dY; a.lda = out;
+    a.B = X; a.ldb = in;
+    a.C = h->splitk; a.ldc = in;
+    a.bias_part = h->splitk_bias;
+    a.M = out; a.N = in; a.K = rows;
+    pick_split(h, out, in, rows, &a.splits, &a.k_per_split);
+    OCPPO_TRY(sgemm_launch(SGEMM_WGRAD, a, s));
+    OCPPO_TRY(launch_splitk_reduce(h->splitk, a.splits, (int64_t)out * in, w_count, dW, accumulate, h->sm_count, s));
+    OCPPO_TRY(launch_splitk_reduce(h->splitk_bias, a.splits, out, b_count, db, accumulate, h->sm_count, s));
+    return OCPPO_OK;
+}
+
+// g0 holds d loss / d pre-activation of the last trunk layer, [B, hidden].
+static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, int accumulate, cudaStream_t s) {
+    for (int l = h->n_layers - 1; l >= 0; --l) {
+        const Layer &L = h->layers[l];
+        const int64_t rows = B * L.row_mult;
+        const float *X = (l == 0) ? x : h->act[l - 1];
+        const float *dY = h->gbuf[cur];
+        OCPPO_TRY(wgrad(h, dY, L.out_dim, X, L.in_dim, rows, h->grads + L.w_off, (int64_t)L.out_dim * L.in_dim,
+                        h->grads + L.b_off, L.out_dim, accumulate, s));
+        if (l > 0) {
+            SgemmArgs a{};
+            a.A = dY; a.lda = L.out_dim;
+            a.B = h->params + L.w_off; a.ldb = L.in_dim;
+            a.C = h->gbuf[cur ^ 1]; a.ldc = L.in_dim;
+            a.mask = h->act[l - 1];
+            a.M = (int)rows; a.N = L.in_dim; a.K = L.out_dim;
+            a.k_per_split = round_up(L.out_dim, 8); a.splits = 1;
+            OCPPO_TRY(sgemm_launch(SGEMM_DGRAD, a, s));
+            cur ^= 1;
+        }
+    }
+    return OCPPO_OK;
+}
+
+}  // namespace ocppo
+
+using namespace ocppo;
+
+extern "C" {
+
+const char *ocppo_last_error(void) { return g_err; }
+int ocppo_version(void) { return 100; }
+
+int64_t ocppo_launch_count(void) {
+    int64_t t = 0;
+    for (int i = 0; i < KC_COUNT; ++i) t += g_prof.launches[i];
+    return t;
+}
+
+int ocppo_profile_enable(int32_t on) {
+    if (on && !g_prof.created) {
+        for (int i = 0; i < kProfMaxPairs; ++i) {
+            OCPPO_CUDA(cudaEventCreate(&g_prof.start[i]));
+            OCPPO_CUDA(cudaEventCreate(&g_prof.stop[i]));
+        }
+        g_prof.created = true;
+    }
+    g_prof.on = on != 0;
+    g_prof.n = 0;
+    return OCPPO_OK;
+}
+
+int ocppo_profile_read(double *ms_by_class, int64_t *timed_by_class, int32_t n_classes) {
+    OCPPO_CHECK_ARG(ms_by_class != nullptr && n_classes >= KC_COUNT, "need %d class slots", (int)KC_COUNT);
+    for (int i = 0; i < n_classes; ++i) { ms_by_class[i] = 0; if (timed_by_class) timed_by_class[i] = 0; }
+    for (int i = 0; i < g_prof.n; ++i) {
+        OCPPO_CUDA(cudaEventSynchronize(g_prof.stop[i]));
+        float ms = 0;
+        OCPPO_CUDA(cudaEventElapsedTime(&ms, g_prof.start[i], g_prof.stop[i]));
+        ms_by_class[g_prof.cls[i]] += ms;
+        if (timed_by_class) timed_by_class[g_prof.cls[i]] += 1;
+    }
+    g_prof.n = 0;
+    return OCPPO_OK;
+}
+
+int ocppo_create(const ocppo_config *cfg, ocppo_handle **out) {
+    OCPPO_CHECK_ARG(cfg != nullptr && out != nullptr, "null argument");
+    ocppo_handle *h = new (std::nothrow) ocppo_handle();
+    OCPPO_CHECK_ARG(h != nullptr, "out of host memory");
+    memset(h, 0, sizeof(*h));
+    h->cfg = *cfg;
+    int r = build_layout(h);
+    if (r != OCPPO_OK) { delete h; return r; }
+    h->sm_count = 148;
+    h->max_threads_per_sm = 2048;
+    if (cfg->device >= 0) {
+        cudaDeviceProp prop;
+        cudaError_t e = cudaGetDeviceProperties(&prop, cfg->device);
+        if (e != cudaSuccess) {
+            set_error("cudaGetDeviceProperties(%d): %s", cfg->device, cudaGetErrorString(e));
+            delete h;
+            return OCPPO_ECUDA;
+        }
+        if (prop.major != 10) {
+            set_error("device %d is sm_%d%d; libocppo is built for sm_100a only (no fallback)", cfg->device,
+                      prop.major, prop.minor);
+            delete h;
+            return OCPPO_EARCH;
+        }
+        h->sm_count = prop.multiProcessorCount;
+        h->max_threads_per_sm = prop.maxThreadsPerMultiProcessor;
+    }
+    *out = h;
+    return OCPPO_OK;
+}
+
+int ocppo_destroy(ocppo_handle *h) {
+    delete h;
+    return OCPPO_OK;
+}
+
+int ocppo_num_tensors(const ocppo_handle *h, int32_t *n_tensors, int64_t *arena_floats, int64_t *param_floats) {
+    OCPPO_CHECK_ARG(h != nullptr, "null handle");
+    if (n_tensors) *n_tensors = h->n_tensors;
+    if (arena_floats) *arena_floats = h->arena_floats;
+    if (param_floats) *param_floats = h->param_floats;
+    return OCPPO_OK;
+}
+
+int ocppo_tensor_layout(const ocppo_handle *h, int32_t i, int64_t *offset, int32_t *rows, int32_t *cols) {
+    OCPPO_CHECK_ARG(h != nullptr, "null handle");
+    OCPPO_CHECK_ARG(i >= 0 && i < h->n_tensors, "tensor index %d out of range [0,%d)", i, h->n_tensors);
+    if (offset) *offset = h->tensor_off[i];
+    if (rows) *rows = h->tensor_rows[i];
+    if (cols) *cols = h->tensor_cols[i];
+    return OCPPO_OK;
+}
+
+int ocppo_bind_arena(ocppo_handle *h, float *params, float *grads, float *exp_avg, float *exp_avg_sq) {
+    OCPPO_CHECK_ARG(h != nullptr && params != nullptr, "null argument");
+    OCPPO_CHECK_ARG(((uintptr_t)params & 127) == 0 && ((uintptr_t)grads & 127) == 0 &&
+                        ((uintptr_t)exp_avg & 127) == 0 && ((uintptr_t)exp_avg_sq & 127) == 0,
+                    "arenas must be 128-byte aligned");
+    h->params = params; h->grads = grads; h->exp_avg = exp_avg; h->exp_avg_sq = exp_avg_sq;
+    return OCPPO_OK;
+}
+
+int ocppo_workspace_bytes(const ocppo_handle *h, int64_t max_rows, int32_t training, int64_t *bytes) {
+    OCPPO_CHECK_ARG(h != nullptr && bytes != nullptr, "null argument");
+    OCPPO_CHECK_ARG(max_rows >= 1, "max_rows must be >= 1");
+    OCPPO_CHECK_ARG(max_rows * h->cfg.frames <= 65535LL * 128, "max_rows too large (%lld)", (long long)max_rows);
+    *bytes = carve(const_cast<ocppo_handle *>(h), nullptr, max_rows, training, false);
+    return OCPPO_OK;
+}
+
+int ocppo_bind_workspace(ocppo_handle *h, void *workspace, int64_t bytes, int64_t max_rows, int32_t training) {
+    OCPPO_CHECK_ARG(h != nullptr && workspace != nullptr, "null argument");
+    OCPPO_CHECK_ARG(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+    int64_t need = 0;
+    OCPPO_TRY(ocppo_workspace_bytes(h, max_rows, training, &need));
+    OCPPO_CHECK_ARG(bytes >= need, "workspace too small: %lld < %lld", (long long)bytes, (long long)need);
+    carve(h, workspace, max_rows, training, true);
+    h->ws = workspace; h->ws_bytes = bytes; h->max_rows = max_rows; h->training = training;
+    h->last_forward_rows = 0;
+    return OCPPO_OK;
+}
+
+int ocppo_policy_step(ocppo_handle *h, const float *obs, int64_t B, uint64_t seed, uint64_t philox_offset,
+                      const int64_t *given_action, int64_t *action, float *logp, float *entropy, float *value,
+                      void *stream) {
+    OCPPO_TRY(require_ready(h, false));
+    OCPPO_CHECK_ARG(B >= 0 && (obs != nullptr || B == 0), "bad obs/B");
+    cudaStream_t s = as_stream(stream);
+    const int64_t row_floats = (int64_t)h->cfg.frames * h->cfg.obs_dim;
+    for (int64_t c0 = 0; c0 < B; c0 += h->max_rows) {
+        const int64_t rows = B - c0 < h->max_rows ? B - c0 : h->max_rows;
+        OCPPO_TRY(trunk_forward(h, obs + c0 * row_floats, rows, s));
+        OCPPO_TRY(launch_policy_head(h, h->act[h->n_layers - 1], rows, c0, B, seed, philox_offset,
+                                     given_action ? given_action + c0 : nullptr, action ? action + c0 : nullptr,
+                                     logp ? logp + c0 : nullptr, entropy ? entropy + c0 : nullptr,
+                                     value ? value + c0 : nullptr, 1, s));
+    }
+    return OCPPO_OK;
+}
+
+int ocppo_value(ocppo_handle *h, const float *obs, int64_t B, float *value, void *stream) {
+    OCPPO_TRY(require_ready(h, false));
+    OCPPO_CHECK_ARG(B >= 0 && value != nullptr && (obs != nullptr || B == 0), "bad argument");
+    cudaStream_t s = as_stream(stream);
+    const int64_t row_floats = (int64_t)h->cfg.frames * h->cfg.obs_dim;
+    for (int64_t c0 = 0; c0 < B; c0 += h->max_rows) {
+        const int64_t rows = B - c0 < h->max_rows ? B - c0 : h->max_rows;
+        OCPPO_TRY(trunk_forward(h, obs + c0 * row_floats, rows, s));
+        OCPPO_TRY(launch_policy_head(h, h->act[h->n_layers - 1], rows, c0, B, 0, 0, nullptr, nullptr, nullptr,
+                                     nullptr, value + c0, 0, s));
+    }
+    return OCPPO_OK;
+}
+
+int ocppo_categorical(const float *logits, int64_t B, int32_t A, uint64_t seed, uint64_t philox_offset,
+                      const int64_t *given_action, int64_t *action, float *logp, float *entropy, void *stream) {
+    OCPPO_CHECK_ARG(B >= 0 && A >= 1 && A <= 32, "bad B/A");
+    OCPPO_CHECK_ARG(logits != nullptr || B == 0, "null logits");
+    return launch_categorical(logits, B, A, seed, philox_offset, given_action, action, logp, entropy,
+                              as_stream(stream));
+}
+
+uint64_t ocppo_philox_increment(int64_t numel, int32_t sm_count, int32_t max_threads_per_sm) {
+    if (numel <= 0) return 0;
+    uint64_t grid = ((uint64_t)numel + 255) / 256;
+    const uint64_t cap = (uint64_t)sm_count * (uint64_t)(max_threads_per_sm / 256);
+    if (grid > cap) grid = cap;
+    return (((uint64_t)numel - 1) / (256 * grid * 4) + 1) * 4;
+}
+
+int ocppo_exponential(float *out, int64_t numel, uint64_t seed, uint64_t philox_offset, void *stream) {
+    OCPPO_CHECK_ARG(numel >= 0 && (out != nullptr || numel == 0), "bad argument");
+    return launch_exponential(out, numel, seed, philox_offset, as_stream(stream));
+}
+
+int ocppo_gae(const float *rewards, const float *values, const float *dones, const float *next_value,
+              const float *next_done, int64_t T, int64_t N, double gamma, double gae_lambda, float *advantages,
+              float *returns, void *stream) {
+    OCPPO_CHECK_ARG(T >= 0 && N >= 0, "negative T/N");
+    if (T == 0 || N == 0) return OCPPO_OK;
+    OCPPO_CHECK_ARG(rewards && values && dones && next_value && next_done && advantages && returns,
+                    "null pointer");
+    return launch_gae(rewards, values, dones, next_value, next_done, T, N, (float)gamma,
+                      (float)(gamma * gae_lambda), advantages, returns, as_stream(stream));
+}
+
+int ocppo_minibatch_fwd_bwd(ocppo_handle *h, const float *b_obs, const int64_t *b_actions, const float *b_logprobs,
+                            const float *b_advantages, const float *b_returns, const float *b_values,
+                            const int64_t *idx, int64_t mb, const ocppo_hparams *hp, float *stats, void *stream) {
+    OCPPO_TRY(require_ready(h, true));
+    OCPPO_CHECK_ARG(mb >= 1, "minibatch size must be >= 1");
+    OCPPO_CHECK_ARG(b_obs && b_actions && b_logprobs && b_advantages && b_returns && b_values && idx && hp && stats,
+                    "null pointer");
+    cudaStream_t s = as_stream(stream);
+    const int A = h->cfg.n_actions, H = h->hidden, AP = (int)round_up(A + 1, 4);
+    if (hp->norm_adv) OCPPO_TRY(launch_adv_stats(h, b_advantages, idx, mb, s));
+    const int64_t n_chunks = ceil_div(mb, h->max_rows);
+    OCPPO_CHECK_ARG(n_chunks <= kLossBlocksMax, "too many chunks");
+    int used = 0;
+    for (int64_t ci = 0; ci < n_chunks; ++ci) {
+        const int64_t c0 = ci * h->max_rows;
+        const int64_t rows = mb - c0 < h->max_rows ? mb - c0 : h->max_rows;
+        OCPPO_TRY(launch_gather(h, b_obs, b_actions, b_logprobs, b_advantages, b_returns, b_values, idx + c0, rows, s));
+        OCPPO_TRY(trunk_forward(h, h->x0, rows, s));
+        LossArgs a{};
+        a.hidden = h->act[h->n_layers - 1];
+        a.action = h->mb_action; a.logp_old = h->mb_logp; a.adv = h->mb_adv; a.ret = h->mb_ret; a.val = h->mb_val;
+        a.adv_stat = h->adv_stat;
+        a.Wa = h->params + h->actor.w_off; a.ba = h->params + h->actor.b_off;
+        a.Wc = h->params + h->critic.w_off; a.bc = h->params + h->critic.b_off;
+        a.rows = rows; a.mb = mb; a.H = H; a.A = A; a.AP = AP;
+        a.clip_lo = (float)(1.0 - hp->clip_coef); a.clip_hi = (float)(1.0 + hp->clip_coef);
+        a.clip_f = (float)hp->clip_coef; a.ent_coef = (float)hp->ent_coef; a.vf_coef = (float)hp->vf_coef;
+        a.norm_adv = hp->norm_adv; a.clip_vloss = hp->clip_vloss;
+        a.dh = h->gbuf[0]; a.gz = h->gz;
+        a.part = h->loss_part + (int64_t)used * 8;
+        int blocks = 0;
+        const int avail = (int)((kLossBlocksMax - used) / (n_chunks - ci));
+        OCPPO_TRY(launch_loss_head(h, a, &blocks, avail, s));
+        used += blocks;
+        const int acc = ci > 0;
+        // heads: d[Wa;Wc] = gz^T hidden, d[ba;bc] = colsum(gz)
+        {
+            SgemmArgs g{};
+            g.A = h->gz; g.lda = AP;
+            g.B = a.hidden; g.ldb = H;
+            g.C = h->splitk; g.ldc = H;
+            g.bias_part = h->splitk_bias;
+            g.M = AP; g.N = H; g.K = rows;
+            pick_split(h, AP, H, rows, &g.splits, &g.k_per_split);
+            OCPPO_TRY(sgemm_launch(SGEMM_WGRAD, g, s));
+            const int64_t stride = (int64_t)AP * H;
+            OCPPO_TRY(launch_splitk_reduce(h->splitk, g.splits, stride, (int64_t)A * H, h->grads + h->actor.w_off, acc, h->sm_count, s));
+            OCPPO_TRY(launch_splitk_reduce(h->splitk + (int64_t)A * H, g.splits, stride, H, h->grads + h->critic.w_off, acc, h->sm_count, s));
+            OCPPO_TRY(launch_splitk_reduce(h->splitk_bias, g.splits, AP, A, h->grads + h->actor.b_off, acc, h->sm_count, s));
+            OCPPO_TRY(launch_splitk_reduce(h->splitk_bias + A, g.splits, AP, 1, h->grads + h->critic.b_off, acc, h->sm_count, s));
+        }
+        OCPPO_TRY(trunk_backward(h, h->x0, rows, 0, acc, s));
+    }
+    OCPPO_TRY(launch_loss_finalize(h->loss_part, used, mb, (float)hp->ent_coef, (float)hp->vf_coef, stats, s));
+    return OCPPO_OK;
+}
+
+int ocppo_clip_adam(ocppo_handle *h, float inv_world, float max_grad_norm, double lr, double beta1, double beta2,
+                    double eps, int64_t step, float *grad_norm, void *stream) {
+    OCPPO_TRY(require_ready(h, true));
+    OCPPO_CHECK_ARG(step >= 1, "Adam step is 1-based");
+    OCPPO_CHECK_ARG(h->grads && h->exp_avg && h->exp_avg_sq, "grad/Adam arenas not bound");
+    return launch_clip_adam(h, inv_world, max_grad_norm, lr, beta1, beta2, eps, step, grad_norm, as_stream(stream));
+}
+
+int ocppo_trunk_forward(ocppo_handle *h, const float *obs, int64_t B, float *hidden, void *stream) {
+    OCPPO_TRY(require_ready(h, false));
+    OCPPO_CHECK_ARG(B >= 1 && B <= h->max_rows, "trunk_forward: B=%lld must be in [1,%lld]", (long long)B,
+                    (long long)h->max_rows);
+    OCPPO_CHECK_ARG(obs && hidden, "null pointer");
+    cudaStream_t s = as_stream(stream);
+    OCPPO_TRY(trunk_forward(h, obs, B, s));
+    OCPPO_CUDA(cudaMemcpyAsync(hidden, h->act[h->n_layers - 1], (size_t)B * h->hidden * sizeof(float),
+                               cudaMemcpyDeviceToDevice, s));
+    return OCPPO_OK;
+}
+
+int ocppo_trunk_backward(ocppo_handle *h, const float *obs, int64_t B, const float *d_hidden, void *stream) {
+    OCPPO_TRY(require_ready(h, true));
+    OCPPO_CHECK_ARG(B >= 1 && B == h->last_forward_rows, "trunk_backward: B=%lld does not match last forward (%d)",
+                    (long long)B, h->last_forward_rows);
+    OCPPO_CHECK_ARG(obs && d_hidden, "null pointer");
+    cudaStream_t s = as_stream(stream);
+    OCPPO_TRY(launch_relu_mask(d_hidden, h->act[h->n_layers - 1], B * h->hidden, h->gbuf[0], h->sm_count, s));
+    return trunk_backward(h, obs, B, 0, 0, s);
+}
+
+}  // extern "C"

@@ -1,0 +1,167 @@
+// Shared declarations for libocppo.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include "../../include/ocppo.h"
+
+namespace ocppo {
+
+void set_error(const char *fmt, ...);
+
+#define OCPPO_CHECK_ARG(cond, ...)                \
+    do {                                          \
+        if (!(cond)) {                            \
+            ::ocppo::set_error(__VA_ARGS__);      \
+            return OCPPO_EINVAL;                  \
+        }                                         \
+    } while (0)
+
+#define OCPPO_CUDA(expr)                                                              \
+    do {                                                                              \
+        cudaError_t _e = (expr);                                                      \
+        if (_e != cudaSuccess) {                                                      \
+            ::ocppo::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
+                               __FILE__, __LINE__);                                   \
+            return OCPPO_ECUDA;                                                       \
+        }                                                                             \
+    } while (0)
+
+#define OCPPO_LAUNCH_CHECK(name)                                                        \
+    do {                                                                                \
+        cudaError_t _e = cudaGetLastError();                                            \
+        if (_e != cudaSuccess) {                                                        \
+            ::ocppo::set_error("launch of %s failed: %s", name, cudaGetErrorString(_e)); \
+            return OCPPO_ECUDA;                                                         \
+        }                                                                               \
+    } while (0)
+
+#define OCPPO_TRY(expr)          \
+    do {                         \
+        int _r = (expr);         \
+        if (_r != OCPPO_OK) return _r; \
+    } while (0)
+
+// ---- launch accounting / live per-class kernel timing (bench.py roofline) ----
+enum KernelClass { KC_GAE = 0, KC_SGEMM_FWD = 1, KC_SGEMM_DGRAD = 2, KC_SGEMM_WGRAD = 3, KC_HEAD = 4,
+                   KC_AUX = 5, KC_ADAM = 6, KC_COUNT = 8 };
+void prof_begin(int cls, int n_kernels, cudaStream_t s);
+void prof_end(cudaStream_t s);
+struct ProfScope {
+    cudaStream_t s;
+    ProfScope(int cls, int n_kernels, cudaStream_t st) : s(st) { prof_begin(cls, n_kernels, st); }
+    ~ProfScope() { prof_end(s); }
+};
+
+static inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+static inline int64_t ceil_div(int64_t x, int64_t m) { return (x + m - 1) / m; }
+
+constexpr int kArenaAlignFloats = 32;      // every tensor starts 128 B aligned
+constexpr int kSplitMax = 32;              // max split-K factor of the wgrad kernels
+constexpr int kLossBlocksMax = 4096;       // partial-sum slots of the loss head
+constexpr int kNormBlocks = 592;           // 148 SMs x 4 CTAs for the grad-norm pass
+
+struct Layer {
+    int in_dim;       // K of the forward GEMM
+    int out_dim;      // N
+    int row_mult;     // rows per sample: frames for encoder layers, 1 after Flatten
+    int64_t w_off;    // arena offsets (floats)
+    int64_t b_off;
+};
+
+}  // namespace ocppo
+
+struct ocppo_handle {
+    ocppo_config cfg;
+    int n_layers;                       // trunk Linear layers (encoder + decoder)
+    ocppo::Layer layers[2 * OCPPO_MAX_LAYERS];
+    ocppo::Layer actor, critic;
+    int hidden;                         // width fed to the heads
+    int n_tensors;
+    int64_t tensor_off[4 * OCPPO_MAX_LAYERS + 4];
+    int32_t tensor_rows[4 * OCPPO_MAX_LAYERS + 4];
+    int32_t tensor_cols[4 * OCPPO_MAX_LAYERS + 4];
+    int64_t arena_floats, param_floats;
+    int sm_count, max_threads_per_sm;
+
+    float *params, *grads, *exp_avg, *exp_avg_sq;
+
+    // workspace carve-up (all device pointers into the caller's buffer)
+    void *ws;
+    int64_t ws_bytes, max_rows;
+    int training;
+    float *x0;                          // gathered observations [max_rows*frames, obs_dim]
+    float *act[2 * OCPPO_MAX_LAYERS];   // post-ReLU activations per trunk layer
+    float *gbuf[2];                     // ping-pong gradient buffers
+    float *gz;                          // head gradients [max_rows, AP]
+    int32_t *mb_action;
+    float *mb_logp, *mb_adv, *mb_ret, *mb_val;
+    float *splitk;                      // [kSplitMax, max(out*in)]
+    float *splitk_bias;                 // [kSplitMax, max(out)]
+    double *loss_part;                  // [kLossBlocksMax, 8]
+    double *adv_part;                   // [kLossBlocksMax, 2]
+    float *adv_stat;                    // mean, std
+    double *norm_part;                  // [kNormBlocks]
+    int last_forward_rows;
+};
+
+namespace ocppo {
+
+// ---- kernels.cu / sgemm.cu entry points used across files -----------------
+enum SgemmMode { SGEMM_FWD = 0, SGEMM_DGRAD = 1, SGEMM_WGRAD = 2 };
+
+struct SgemmArgs {
+    const float *A; int64_t lda;
+    const float *B; int64_t ldb;
+    float *C; int64_t ldc;
+    const float *bias;        // FWD: [N]
+    const float *mask;        // DGRAD: same layout as C; C = mask > 0 ? acc : 0
+    float *bias_part;         // WGRAD: [splits, M] column sums of A
+    int M, N;
+    int64_t K;                // contraction length (rows for WGRAD)
+    int64_t k_per_split;
+    int splits;
+};
+
+int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);
+
+int launch_gae(const float *rewards, const float *values, const float *dones,
+               const float *next_value, const float *next_done, int64_t T, int64_t N, float g,
+               float c, float *adv, float *ret, cudaStream_t stream);
+
+struct LossArgs {
+    const float *hidden;        // [rows, H] post-ReLU output of the last trunk layer
+    const int32_t *action;      // gathered minibatch columns, [rows]
+    const float *logp_old, *adv, *ret, *val;
+    const float *adv_stat;      // {mean, unbiased std} of the whole minibatch
+    const float *Wa, *ba, *Wc, *bc;
+    int64_t rows, mb;
+    int H, A, AP;
+    float clip_lo, clip_hi, clip_f, ent_coef, vf_coef;
+    int norm_adv, clip_vloss;
+    float *dh;                  // [rows, H]  d loss / d (pre-activation of last trunk layer)
+    float *gz;                  // [rows, AP] d loss / d (logits, value), zero padded
+    double *part;               // [gridDim.x, 8] partial sums of the logged statistics
+};
+
+int launch_policy_head(const ocppo_handle *h, const float *hidden, int64_t B, int64_t row_base, int64_t total_B,
+                       uint64_t seed, uint64_t offset, const int64_t *given, int64_t *action, float *logp,
+                       float *entropy, float *value, int want_policy, cudaStream_t stream);
+int launch_categorical(const float *logits, int64_t B, int A, uint64_t seed, uint64_t offset, const int64_t *given,
+                       int64_t *action, float *logp, float *entropy, cudaStream_t stream);
+int launch_exponential(float *out, int64_t numel, uint64_t seed, uint64_t offset, cudaStream_t stream);
+int launch_gather(const ocppo_handle *h, const float *b_obs, const int64_t *b_actions, const float *b_logp,
+                  const float *b_adv, const float *b_ret, const float *b_val, const int64_t *idx, int64_t rows,
+                  cudaStream_t stream);
+int launch_adv_stats(const ocppo_handle *h, const float *b_adv, const int64_t *idx, int64_t mb, cudaStream_t stream);
+int launch_loss_head(const ocppo_handle *h, LossArgs a, int *blocks_used, int blocks_avail, cudaStream_t stream);
+int launch_loss_finalize(const double *part, int n_part, int64_t mb, float ent_coef, float vf_coef, float *stats,
+                         cudaStream_t stream);
+int launch_splitk_reduce(const float *part, int splits, int64_t stride, int64_t count, float *out, int accumulate,
+                         int sm_count, cudaStream_t stream);
+int launch_relu_mask(const float *g, const float *act, int64_t n, float *out, int sm_count, cudaStream_t stream);
+int launch_clip_adam(ocppo_handle *h, float inv_world, float max_norm, double lr, double beta1, double beta2,
+                     double eps, int64_t step, float *grad_norm, cudaStream_t stream);
+
+}  // namespace ocppo

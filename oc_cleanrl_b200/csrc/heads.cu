@@ -1,0 +1,562 @@
+// Actor/critic heads fused with the Categorical distribution:
+//   rollout:  hidden -> logits,value -> normalise -> sample (Philox) -> logp, entropy
+//             (architectures/ppo.py:89-95 under no_grad, ppo_atari_oc.py:505-509)
+//   update :  hidden -> logits,value -> PPO losses -> d(loss)/d(logits,value,hidden)
+//             (ppo_atari_oc.py:566-602 forward, closed-form backward SURVEY.md A.4)
+// One warp per sample; lane k holds logit k (n_actions <= 32).
+#include "common.cuh"
+#include "philox.cuh"
+#include <math_constants.h>
+
+namespace ocppo {
+
+namespace {
+
+constexpr unsigned kFull = 0xffffffffu;
+constexpr int kHeadThreads = 256;
+constexpr int kWarpsPerBlock = kHeadThreads / 32;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(kFull, v, o));
+    return v;
+}
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
+    return v;
+}
+
+// torch/distributions/categorical.py:78 (logits - logsumexp), logits_to_probs
+// (softmax of the normalised logits), :159-163 (entropy).
+__device__ __forceinline__ void warp_categorical(float z, int lane, int A, float &ell, float &p, float &H) {
+    const bool on = lane < A;
+    const float m = warp_max(on ? z : -CUDART_INF_F);
+    const float s = warp_sum(on ? expf(z - m) : 0.f);
+    ell = z - (m + logf(s));
+    const float m2 = warp_max(on ? ell : -CUDART_INF_F);
+    const float e2 = on ? expf(ell - m2) : 0.f;
+    const float s2 = warp_sum(e2);
+    p = __fdiv_rn(e2, s2);
+    H = -warp_sum(on ? fmaxf(ell, -3.402823466e+38f) * p : 0.f);
+}
+
+// torch multinomial single-draw path: argmax_k p_k / q_k, first index on ties.
+__device__ __forceinline__ int warp_sample(float p, int lane, int A, const PhiloxLayout &L, uint64_t row) {
+    float r = -CUDART_INF_F;
+    if (lane < A) {
+        const uint32_t w = torch_philox_word(L, row * (uint64_t)A + (uint64_t)lane);
+        const float q = torch_exponential_from_uniform(curand_uniform_from_word(w));
+        r = __fdiv_rn(p, q);
+    }
+    int k = lane;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float r2 = __shfl_xor_sync(kFull, r, o);
+        const int k2 = __shfl_xor_sync(kFull, k, o);
+        if (r2 > r || (r2 == r && k2 < k)) { r = r2; k = k2; }
+    }
+    return k;
+}
+
+// Stage actor/critic weights: sW[(A+1)][H] (row A = critic), sB[A+1].
+__device__ __forceinline__ void stage_head_weights(float *sW, float *sB, const float *Wa, const float *ba,
+                                                   const float *Wc, const float *bc, int A, int H) {
+    for (int i = threadIdx.x; i < A * H; i += blockDim.x) sW[i] = Wa[i];
+    for (int i = threadIdx.x; i < H; i += blockDim.x) sW[A * H + i] = Wc[i];
+    for (int i = threadIdx.x; i < A; i += blockDim.x) sB[i] = ba[i];
+    if (threadIdx.x == 0) sB[A] = bc[0];
+    __syncthreads();
+}
+
+// lane k (k < A) returns logit k; value broadcast to all lanes.
+__device__ __forceinline__ void warp_head_forward(const float *__restrict__ h, const float *sW, const float *sB,
+                                                  int A, int H, int lane, float &z, float &v) {
+    z = 0.f;
+    for (int k = 0; k <= A; ++k) {
+        float part = 0.f;
+        for (int j = lane; j < H; j += 32) part = fmaf(sW[k * H + j], h[j], part);
+        part = warp_sum(part) + sB[k];
+        if (k == A) v = part;
+        else if (lane == k) z = part;
+    }
+}
+
+__global__ void __launch_bounds__(kHeadThreads)
+policy_head_kernel(const float *__restrict__ hidden, int64_t B, int H, int A, const float *Wa, const float *ba,
+                   const float *Wc, const float *bc, PhiloxLayout L, int64_t row_base,
+                   const int64_t *__restrict__ given, int64_t *__restrict__ action, float *__restrict__ logp,
+                   float *__restrict__ entropy, float *__restrict__ value, int want_policy) {
+    extern __shared__ float sm[];
+    float *sW = sm, *sB = sm + (size_t)(A + 1) * H;
+    stage_head_weights(sW, sB, Wa, ba, Wc, bc, A, H);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int64_t i = (int64_t)blockIdx.x * kWarpsPerBlock + warp; i < B; i += (int64_t)gridDim.x * kWarpsPerBlock) {
+        float z, v;
+        warp_head_forward(hidden + i * H, sW, sB, A, H, lane, z, v);
+        if (value != nullptr && lane == 0) value[i] = v;
+        if (!want_policy) continue;
+        float ell, p, Hh;
+        warp_categorical(z, lane, A, ell, p, Hh);
+        int a;
+        if (given != nullptr) a = (int)given[i];
+        else a = warp_sample(p, lane, A, L, (uint64_t)(row_base + i));
+        const float lp = __shfl_sync(kFull, ell, a & 31);
+        if (lane == 0) {
+            if (action != nullptr) action[i] = (int64_t)a;
+            if (logp != nullptr) logp[i] = lp;
+            if (entropy != nullptr) entropy[i] = Hh;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kHeadThreads)
+categorical_kernel(const float *__restrict__ logits, int64_t B, int A, PhiloxLayout L,
+                   const int64_t *__restrict__ given, int64_t *__restrict__ action,
+                   float *__restrict__ logp, float *__restrict__ entropy) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int64_t i = (int64_t)blockIdx.x * kWarpsPerBlock + warp; i < B; i += (int64_t)gridDim.x * kWarpsPerBlock) {
+        const float z = lane < A ? logits[i * A + lane] : 0.f;
+        float ell, p, Hh;
+        warp_categorical(z, lane, A, ell, p, Hh);
+        int a;
+        if (given != nullptr) a = (int)given[i];
+        else a = warp_sample(p, lane, A, L, (uint64_t)i);
+        const float lp = __shfl_sync(kFull, ell, a & 31);
+        if (lane == 0) {
+            if (action != nullptr) action[i] = (int64_t)a;
+            if (logp != nullptr) logp[i] = lp;
+            if (entropy != nullptr) entropy[i] = Hh;
+        }
+    }
+}
+
+__global__ void exponential_kernel(float *__restrict__ out, int64_t numel, PhiloxLayout L) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < numel; i += (int64_t)gridDim.x * blockDim.x)
+        out[i] = torch_exponential_from_uniform(curand_uniform_from_word(torch_philox_word(L, (uint64_t)i)));
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------
+// PPO loss head, forward + backward in one pass (ppo_atari_oc.py:566-602).
+// ---------------------------------------------------------------------------
+
+namespace {
+
+__global__ void __launch_bounds__(kHeadThreads) loss_head_kernel(LossArgs p) {
+    extern __shared__ float sm[];
+    const int A = p.A, H = p.H;
+    float *sW = sm, *sB = sm + (size_t)(A + 1) * H;
+    stage_head_weights(sW, sB, p.Wa, p.ba, p.Wc, p.bc, A, H);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float inv_mb = 1.0f / (float)p.mb;
+    float mean = 0.f, stdv = 1.f;
+    if (p.norm_adv) { mean = p.adv_stat[0]; stdv = p.adv_stat[1]; }
+
+    double acc[6] = {0, 0, 0, 0, 0, 0};   // pg, vmax, entropy, -logratio, (ratio-1)-logratio, clipped
+    for (int64_t i = (int64_t)blockIdx.x * kWarpsPerBlock + warp; i < p.rows; i += (int64_t)gridDim.x * kWarpsPerBlock) {
+        const float *h = p.hidden + i * H;
+        float z, v;
+        warp_head_forward(h, sW, sB, A, H, lane, z, v);
+        float ell, pk, Hh;
+        warp_categorical(z, lane, A, ell, pk, Hh);
+        const int a = p.action[i];
+        const float newlogp = __shfl_sync(kFull, ell, a & 31);
+        const float logratio = newlogp - p.logp_old[i];
+        const float ratio = expf(logratio);
+        float advn = p.adv[i];
+        if (p.norm_adv) advn = __fdiv_rn(advn - mean, stdv + 1e-8f);
+        // clipped surrogate (:581-583)
+        const float l1 = -advn * ratio;
+        const float rc = fminf(fmaxf(ratio, p.clip_lo), p.clip_hi);
+        const float l2 = -advn * rc;
+        const float pg = fmaxf(l1, l2);
+        const bool in_range = (ratio >= p.clip_lo) && (ratio <= p.clip_hi);
+        float g_ratio;                       // d pg / d ratio
+        if (l1 > l2) g_ratio = -advn;
+        else if (l2 > l1) g_ratio = in_range ? -advn : 0.f;
+        else g_ratio = 0.5f * (-advn) + (in_range ? 0.5f * (-advn) : 0.f);
+        // value loss (:585-597)
+        const float R = p.ret[i], Vold = p.val[i];
+        const float du = v - R;
+        const float u = du * du;
+        float vterm = u, g_v = du;           // d (0.5*vterm) / d v
+        if (p.clip_vloss) {
+            const float d = v - Vold;
+            const float dc = fminf(fmaxf(d, -p.clip_f), p.clip_f);
+            const float vc = Vold + dc;
+            const float dw = vc - R;
+            const float w = dw * dw;
+            const bool v_in = (d >= -p.clip_f) && (d <= p.clip_f);
+            const float gw = v_in ? dw : 0.f;
+            if (u > w) { vterm = u; g_v = du; }
+            else if (w > u) { vterm = w; g_v = gw; }
+            else { vterm = u; g_v = 0.5f * du + 0.5f * gw; }
+        }
+        // gradients wrt logits / value
+        const float coef_a = g_ratio * ratio * inv_mb;
+        const float coef_e = p.ent_coef * inv_mb;
+        float dz = 0.f;
+        if (lane < A) dz = coef_a * ((lane == a ? 1.f : 0.f) - pk) + coef_e * pk * (ell + Hh);
+        const float dv = p.vf_coef * inv_mb * g_v;
+        if (lane < p.AP) p.gz[i * p.AP + lane] = lane < A ? dz : (lane == A ? dv : 0.f);
+        // d hidden, masked by ReLU of the last trunk layer
+        for (int j = lane; j < H; j += 32) {
+            float s = dv * sW[A * H + j];
+            for (int k = 0; k < A; ++k) s = fmaf(__shfl_sync(kFull, dz, k), sW[k * H + j], s);
+            p.dh[i * H + j] = h[j] > 0.f ? s : 0.f;
+        }
+        if (lane == 0) {
+            acc[0] += (double)pg;
+            acc[1] += (double)vterm;
+            acc[2] += (double)Hh;
+            acc[3] += (double)(-logratio);
+            acc[4] += (double)((ratio - 1.0f) - logratio);
+            acc[5] += (fabsf(ratio - 1.0f) > p.clip_f) ? 1.0 : 0.0;
+        }
+    }
+    __shared__ double red[kWarpsPerBlock][6];
+    if (lane == 0)
+        for (int q = 0; q < 6; ++q) red[warp][q] = acc[q];
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        double s = 0;
+        for (int w = 0; w < kWarpsPerBlock; ++w) s += red[w][threadIdx.x];
+        p.part[(int64_t)blockIdx.x * 8 + threadIdx.x] = s;
+    }
+}
+
+// Single block: ordered sum of the block partials -> the seven logged scalars.
+__global__ void loss_finalize_kernel(const double *__restrict__ part, int n_part, int64_t mb, float ent_coef,
+                                     float vf_coef, float *__restrict__ stats) {
+    __shared__ double s[6];
+    if (threadIdx.x < 6) {
+        double a = 0;
+        for (int b = 0; b < n_part; ++b) a += part[(int64_t)b * 8 + threadIdx.x];
+        s[threadIdx.x] = a / (double)mb;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const float pg = (float)s[0], vl = 0.5f * (float)s[1], en = (float)s[2];
+        stats[OCPPO_STAT_PG_LOSS] = pg;
+        stats[OCPPO_STAT_V_LOSS] = vl;
+        stats[OCPPO_STAT_ENTROPY] = en;
+        stats[OCPPO_STAT_LOSS] = pg - ent_coef * en + vl * vf_coef;
+        stats[OCPPO_STAT_OLD_APPROX_KL] = (float)s[3];
+        stats[OCPPO_STAT_APPROX_KL] = (float)s[4];
+        stats[OCPPO_STAT_CLIPFRAC] = (float)s[5];
+        stats[OCPPO_STAT_RESERVED] = 0.f;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// minibatch gather (ppo_atari_oc.py:566-567,569,577,587-593) + advantage stats (:579)
+// ---------------------------------------------------------------------------
+__global__ void gather_kernel(const float *__restrict__ b_obs, const int64_t *__restrict__ b_actions,
+                              const float *__restrict__ b_logp, const float *__restrict__ b_adv,
+                              const float *__restrict__ b_ret, const float *__restrict__ b_val,
+                              const int64_t *__restrict__ idx, int64_t rows, int obs_floats,
+                              float *__restrict__ x0, int32_t *__restrict__ action, float *__restrict__ logp,
+                              float *__restrict__ adv, float *__restrict__ ret, float *__restrict__ val) {
+    const int64_t total = rows * obs_floats;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = e / obs_floats;
+        const int c = (int)(e - r * obs_floats);
+        const int64_t src = idx[r];
+        x0[e] = b_obs[src * obs_floats + c];
+        if (c == 0) {
+            action[r] = (int32_t)b_actions[src];
+            logp[r] = b_logp[src];
+            adv[r] = b_adv[src];
+            ret[r] = b_ret[src];
+            val[r] = b_val[src];
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+adv_stats_partial_kernel(const float *__restrict__ b_adv, const int64_t *__restrict__ idx, int64_t mb,
+                         double *__restrict__ part) {
+    double s = 0, s2 = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < mb; i += (int64_t)gridDim.x * blockDim.x) {
+        const double x = (double)b_adv[idx[i]];
+        s += x;
+        s2 += x * x;
+    }
+    s = warp_sum_d(s);
+    s2 = warp_sum_d(s2);
+    __shared__ double red[8][2];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) { red[warp][0] = s; red[warp][1] = s2; }
+    __syncthreads();
+    if (threadIdx.x < 2) {
+        double a = 0;
+        for (int w = 0; w < 8; ++w) a += red[w][threadIdx.x];
+        part[(int64_t)blockIdx.x * 2 + threadIdx.x] = a;
+    }
+}
+
+__global__ void adv_stats_finalize_kernel(const double *__restrict__ part, int n_part, int64_t mb,
+                                          float *__restrict__ stat) {
+    if (threadIdx.x == 0) {
+        double s = 0, s2 = 0;
+        for (int b = 0; b < n_part; ++b) { s += part[2 * b]; s2 += part[2 * b + 1]; }
+        const double mean = s / (double)mb;
+        double var = (s2 - s * mean) / (double)(mb - 1);     // unbiased, torch .std() default
+        if (var < 0 && mb > 1) var = 0;
+        stat[0] = (float)mean;
+        stat[1] = (float)sqrt(var);
+    }
+}
+
+// out[i] = (accumulate ? out[i] : 0) + sum_s part[s*stride + i], fixed order.
+__global__ void splitk_reduce_kernel(const float *__restrict__ part, int splits, int64_t stride, int64_t count,
+                                     float *__restrict__ out, int accumulate) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int k = 0; k < splits; ++k) s += part[(int64_t)k * stride + i];
+        out[i] = accumulate ? out[i] + s : s;
+    }
+}
+
+__global__ void relu_mask_kernel(const float *__restrict__ g, const float *__restrict__ act, int64_t n,
+                                 float *__restrict__ out) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        out[i] = act[i] > 0.f ? g[i] : 0.f;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------
+// clip_grad_norm_ + Adam over the flat arenas (ppo_atari_oc.py:609-610; torch
+// nn/utils/clip_grad.py, optim/adam.py single-tensor path), with
+// the 1/world_size of ppo_atari_multigpu.py:368-374 folded in.
+// HBM-bound: reads g (twice), p, m, v; writes g, p, m, v  = 8 x 4 B per param.
+// ---------------------------------------------------------------------------
+namespace {
+
+__global__ void __launch_bounds__(256)
+sumsq_kernel(const float *__restrict__ g, int64_t n, float inv_world, double *__restrict__ part) {
+    double s = 0;
+    const int64_t n4 = n >> 2;
+    const float4 *g4 = reinterpret_cast<const float4 *>(g);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        const float4 v = g4[i];
+        const float a = v.x * inv_world, b = v.y * inv_world, c = v.z * inv_world, d = v.w * inv_world;
+        s += (double)a * a + (double)b * b + (double)c * c + (double)d * d;
+    }
+    s = warp_sum_d(s);
+    __shared__ double red[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) red[warp] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0;
+        for (int w = 0; w < 8; ++w) a += red[w];
+        part[blockIdx.x] = a;
+    }
+}
+
+struct AdamArgs {
+    float *p, *g, *m, *v;
+    int64_t n;
+    const double *norm_part;
+    int n_part;
+    float inv_world, max_norm, one_minus_b1, b2, one_minus_b2, step_size, bc2_sqrt, eps;
+    float *grad_norm;
+};
+
+__global__ void __launch_bounds__(256) adam_kernel(AdamArgs a) {
+    __shared__ float s_coef;
+    if (threadIdx.x < 32) {
+        double s = 0;
+        for (int i = threadIdx.x; i < a.n_part; i += 32) s += a.norm_part[i];
+        s = warp_sum_d(s);
+        if (threadIdx.x == 0) {
+            const float total = (float)sqrt(s);
+            float coef = a.max_norm / (total + 1e-6f);
+            coef = fminf(coef, 1.0f);
+            s_coef = coef;
+            if (blockIdx.x == 0 && a.grad_norm != nullptr) *a.grad_norm = total;
+        }
+    }
+    __syncthreads();
+    const float coef = s_coef;
+    const int64_t n4 = a.n >> 2;
+    float4 *p4 = reinterpret_cast<float4 *>(a.p), *g4 = reinterpret_cast<float4 *>(a.g);
+    float4 *m4 = reinterpret_cast<float4 *>(a.m), *v4 = reinterpret_cast<float4 *>(a.v);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        float4 G = g4[i], P = p4[i], M = m4[i], V = v4[i];
+        float *gg = &G.x, *pp = &P.x, *mm = &M.x, *vv = &V.x;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const float gr = (gg[q] * a.inv_world) * coef;
+            gg[q] = gr;
+            mm[q] = mm[q] + (gr - mm[q]) * a.one_minus_b1;
+            vv[q] = vv[q] * a.b2 + a.one_minus_b2 * gr * gr;
+            const float denom = sqrtf(vv[q]) / a.bc2_sqrt + a.eps;
+            pp[q] = pp[q] - a.step_size * (mm[q] / denom);
+        }
+        g4[i] = G; p4[i] = P; m4[i] = M; v4[i] = V;
+    }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------
+// host-side launchers
+// ---------------------------------------------------------------------------
+static inline unsigned grid_for(int64_t work_items, int per_block, int cap) {
+    int64_t g = ceil_div(work_items, per_block);
+    if (g < 1) g = 1;
+    if (g > cap) g = cap;
+    return (unsigned)g;
+}
+
+static int head_smem_bytes(int A, int H) { return (int)(((size_t)(A + 1) * H + (A + 1)) * sizeof(float)); }
+
+static int ensure_head_smem(const void *fn, int bytes) {
+    if (bytes > 48 * 1024) OCPPO_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    return OCPPO_OK;
+}
+
+int launch_policy_head(const ocppo_handle *h, const float *hidden, int64_t B, int64_t row_base, int64_t total_B,
+                       uint64_t seed, uint64_t offset, const int64_t *given, int64_t *action, float *logp,
+                       float *entropy, float *value, int want_policy, cudaStream_t stream) {
+    if (B == 0) return OCPPO_OK;
+    const int A = h->cfg.n_actions, H = h->hidden;
+    PhiloxLayout L{seed, offset, torch_philox_grid(total_B * A, h->sm_count, h->max_threads_per_sm) * 256};
+    const int smem = head_smem_bytes(A, H);
+    OCPPO_TRY(ensure_head_smem((const void *)policy_head_kernel, smem));
+    const unsigned grid = grid_for(B, kWarpsPerBlock, h->sm_count * 4);
+    ProfScope ps(KC_HEAD, 1, stream);
+    policy_head_kernel<<<grid, kHeadThreads, smem, stream>>>(
+        hidden, B, H, A, h->params + h->actor.w_off, h->params + h->actor.b_off, h->params + h->critic.w_off,
+        h->params + h->critic.b_off, L, row_base, given, action, logp, entropy, value, want_policy);
+    OCPPO_LAUNCH_CHECK("policy_head_kernel");
+    return OCPPO_OK;
+}
+
+static int device_geometry(int *sm_count, int *max_threads) {
+    int dev = 0;
+    OCPPO_CUDA(cudaGetDevice(&dev));
+    OCPPO_CUDA(cudaDeviceGetAttribute(sm_count, cudaDevAttrMultiProcessorCount, dev));
+    OCPPO_CUDA(cudaDeviceGetAttribute(max_threads, cudaDevAttrMaxThreadsPerMultiProcessor, dev));
+    return OCPPO_OK;
+}
+
+int launch_categorical(const float *logits, int64_t B, int A, uint64_t seed, uint64_t offset, const int64_t *given,
+                       int64_t *action, float *logp, float *entropy, cudaStream_t stream) {
+    if (B == 0) return OCPPO_OK;
+    int sms, mt;
+    OCPPO_TRY(device_geometry(&sms, &mt));
+    PhiloxLayout L{seed, offset, torch_philox_grid(B * A, sms, mt) * 256};
+    ProfScope ps(KC_HEAD, 1, stream);
+    categorical_kernel<<<grid_for(B, kWarpsPerBlock, sms * 8), kHeadThreads, 0, stream>>>(logits, B, A, L, given,
+                                                                                         action, logp, entropy);
+    OCPPO_LAUNCH_CHECK("categorical_kernel");
+    return OCPPO_OK;
+}
+
+int launch_exponential(float *out, int64_t numel, uint64_t seed, uint64_t offset, cudaStream_t stream) {
+    if (numel == 0) return OCPPO_OK;
+    int sms, mt;
+    OCPPO_TRY(device_geometry(&sms, &mt));
+    PhiloxLayout L{seed, offset, torch_philox_grid(numel, sms, mt) * 256};
+    ProfScope ps(KC_AUX, 1, stream);
+    exponential_kernel<<<grid_for(numel, 256, sms * 8), 256, 0, stream>>>(out, numel, L);
+    OCPPO_LAUNCH_CHECK("exponential_kernel");
+    return OCPPO_OK;
+}
+
+int launch_gather(const ocppo_handle *h, const float *b_obs, const int64_t *b_actions, const float *b_logp,
+                  const float *b_adv, const float *b_ret, const float *b_val, const int64_t *idx, int64_t rows,
+                  cudaStream_t stream) {
+    const int obs_floats = h->cfg.frames * h->cfg.obs_dim;
+    ProfScope ps(KC_AUX, 1, stream);
+    gather_kernel<<<grid_for(rows * obs_floats, 256, h->sm_count * 8), 256, 0, stream>>>(
+        b_obs, b_actions, b_logp, b_adv, b_ret, b_val, idx, rows, obs_floats, h->x0, h->mb_action, h->mb_logp,
+        h->mb_adv, h->mb_ret, h->mb_val);
+    OCPPO_LAUNCH_CHECK("gather_kernel");
+    return OCPPO_OK;
+}
+
+int launch_adv_stats(const ocppo_handle *h, const float *b_adv, const int64_t *idx, int64_t mb, cudaStream_t stream) {
+    const unsigned grid = grid_for(mb, 256 * 8, h->sm_count * 2);
+    ProfScope ps(KC_AUX, 2, stream);
+    adv_stats_partial_kernel<<<grid, 256, 0, stream>>>(b_adv, idx, mb, h->adv_part);
+    OCPPO_LAUNCH_CHECK("adv_stats_partial_kernel");
+    adv_stats_finalize_kernel<<<1, 32, 0, stream>>>(h->adv_part, (int)grid, mb, h->adv_stat);
+    OCPPO_LAUNCH_CHECK("adv_stats_finalize_kernel");
+    return OCPPO_OK;
+}
+
+int launch_loss_head(const ocppo_handle *h, LossArgs a, int *blocks_used, int blocks_avail, cudaStream_t stream) {
+    const int smem = head_smem_bytes(a.A, a.H);
+    OCPPO_TRY(ensure_head_smem((const void *)loss_head_kernel, smem));
+    int cap = h->sm_count * 4;
+    if (cap > blocks_avail) cap = blocks_avail;
+    OCPPO_CHECK_ARG(cap >= 1, "loss head: out of partial-sum slots");
+    const unsigned grid = grid_for(a.rows, kWarpsPerBlock, cap);
+    ProfScope ps(KC_HEAD, 1, stream);
+    loss_head_kernel<<<grid, kHeadThreads, smem, stream>>>(a);
+    OCPPO_LAUNCH_CHECK("loss_head_kernel");
+    *blocks_used = (int)grid;
+    return OCPPO_OK;
+}
+
+int launch_loss_finalize(const double *part, int n_part, int64_t mb, float ent_coef, float vf_coef, float *stats,
+                         cudaStream_t stream) {
+    ProfScope ps(KC_AUX, 1, stream);
+    loss_finalize_kernel<<<1, 32, 0, stream>>>(part, n_part, mb, ent_coef, vf_coef, stats);
+    OCPPO_LAUNCH_CHECK("loss_finalize_kernel");
+    return OCPPO_OK;
+}
+
+int launch_splitk_reduce(const float *part, int splits, int64_t stride, int64_t count, float *out, int accumulate,
+                         int sm_count, cudaStream_t stream) {
+    if (count == 0) return OCPPO_OK;
+    ProfScope ps(KC_AUX, 1, stream);
+    splitk_reduce_kernel<<<grid_for(count, 256, sm_count * 8), 256, 0, stream>>>(part, splits, stride, count, out,
+                                                                               accumulate);
+    OCPPO_LAUNCH_CHECK("splitk_reduce_kernel");
+    return OCPPO_OK;
+}
+
+int launch_relu_mask(const float *g, const float *act, int64_t n, float *out, int sm_count, cudaStream_t stream) {
+    if (n == 0) return OCPPO_OK;
+    ProfScope ps(KC_AUX, 1, stream);
+    relu_mask_kernel<<<grid_for(n, 256, sm_count * 8), 256, 0, stream>>>(g, act, n, out);
+    OCPPO_LAUNCH_CHECK("relu_mask_kernel");
+    return OCPPO_OK;
+}
+
+int launch_clip_adam(ocppo_handle *h, float inv_world, float max_norm, double lr, double beta1, double beta2,
+                     double eps, int64_t step, float *grad_norm, cudaStream_t stream) {
+    const int64_t n = h->arena_floats;   // multiple of kArenaAlignFloats, padding is zero
+    const int blocks = kNormBlocks < h->sm_count * 4 ? kNormBlocks : h->sm_count * 4;
+    ProfScope ps(KC_ADAM, 2, stream);
+    sumsq_kernel<<<blocks, 256, 0, stream>>>(h->grads, n, inv_world, h->norm_part);
+    OCPPO_LAUNCH_CHECK("sumsq_kernel");
+    // torch/optim/adam.py _single_tensor_adam: scalars formed in python double
+    const double bc1 = 1.0 - pow(beta1, (double)step);
+    const double bc2 = 1.0 - pow(beta2, (double)step);
+    AdamArgs a;
+    a.p = h->params; a.g = h->grads; a.m = h->exp_avg; a.v = h->exp_avg_sq;
+    a.n = n; a.norm_part = h->norm_part; a.n_part = blocks;
+    a.inv_world = inv_world; a.max_norm = max_norm;
+    a.one_minus_b1 = (float)(1.0 - beta1); a.b2 = (float)beta2; a.one_minus_b2 = (float)(1.0 - beta2);
+    a.step_size = (float)(lr / bc1); a.bc2_sqrt = (float)sqrt(bc2); a.eps = (float)eps;
+    a.grad_norm = grad_norm;
+    adam_kernel<<<h->sm_count * 4, 256, 0, stream>>>(a);
+    OCPPO_LAUNCH_CHECK("adam_kernel");
+    return OCPPO_OK;
+}
+
+}  // namespace ocppo

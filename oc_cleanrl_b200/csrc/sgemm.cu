@@ -1,0 +1,216 @@
+// FP32 CUDA-core GEMM family for the PPObj trunk (the reference runs full-fp32
+// cuBLAS SGEMM through nn.Linear, architectures/ppo.py:70-84; loss.backward(),
+// ppo_atari_oc.py:608).  One templated 128x128x8 register-tiled kernel covers
+//   FWD   : Y[M,N]  = relu(X[M,K] . W[N,K]^T + b[N])
+//   DGRAD : dX[M,N] = (mask[M,N] > 0) * (dY[M,K] . W[K,N])
+//   WGRAD : dW[M,N] = dY[K,M]^T . X[K,N], split over K into deterministic
+//           partials (+ column sums of dY for the bias gradient)
+// Fixed accumulation order => run-to-run deterministic (the reference sets
+// torch.use_deterministic_algorithms(True), ppo_atari_oc.py:209).
+#include "common.cuh"
+
+namespace ocppo {
+
+namespace {
+
+constexpr int BM = 128, BN = 128, BK = 8, PAD = 4;
+constexpr int kThreads = 256;
+
+// Load one BMxBK (or BNxBK) operand slab into registers.
+//  KC  : element (r, k) at base[r*ld + k]   (k contiguous)
+//  !KC : element (r, k) at base[k*ld + r]   (r contiguous)
+template <bool KC, bool VEC>
+__device__ __forceinline__ void load_slab(float (&reg)[4], const float *__restrict__ base, int64_t ld,
+                                          int r0, int R, int64_t k0, int64_t Kend, int tid) {
+    if (KC) {
+        const int r = r0 + (tid >> 1);
+        const int64_t k = k0 + (tid & 1) * 4;
+        if (VEC) {
+            if (r < R && k < Kend) {
+                const float4 v = *reinterpret_cast<const float4 *>(base + (int64_t)r * ld + k);
+                reg[0] = v.x; reg[1] = v.y; reg[2] = v.z; reg[3] = v.w;
+            } else {
+                reg[0] = reg[1] = reg[2] = reg[3] = 0.f;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                reg[i] = (r < R && k + i < Kend) ? base[(int64_t)r * ld + k + i] : 0.f;
+        }
+    } else {
+        const int64_t k = k0 + (tid >> 5);
+        const int r = r0 + (tid & 31) * 4;
+        if (VEC) {
+            if (r < R && k < Kend) {
+                const float4 v = *reinterpret_cast<const float4 *>(base + k * ld + r);
+                reg[0] = v.x; reg[1] = v.y; reg[2] = v.z; reg[3] = v.w;
+            } else {
+                reg[0] = reg[1] = reg[2] = reg[3] = 0.f;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                reg[i] = (r + i < R && k < Kend) ? base[k * ld + r + i] : 0.f;
+        }
+    }
+}
+
+template <bool KC>
+__device__ __forceinline__ void store_slab(float (*s)[BM + PAD], const float (&reg)[4], int tid) {
+    if (KC) {
+        const int r = tid >> 1, k = (tid & 1) * 4;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) s[k + i][r] = reg[i];
+    } else {
+        const int k = tid >> 5, r = (tid & 31) * 4;
+        *reinterpret_cast<float4 *>(&s[k][r]) = make_float4(reg[0], reg[1], reg[2], reg[3]);
+    }
+}
+
+template <int MODE, bool A_VEC, bool B_VEC>
+__global__ void __launch_bounds__(kThreads, 2) sgemm_kernel(SgemmArgs p) {
+    constexpr bool A_KC = (MODE != SGEMM_WGRAD);
+    constexpr bool B_KC = (MODE == SGEMM_FWD);
+    __shared__ __align__(16) float As[2][BK][BM + PAD];
+    __shared__ __align__(16) float Bs[2][BK][BN + PAD];
+
+    const int tid = threadIdx.x;
+    const int tx = tid & 15, ty = tid >> 4;
+    const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+    const int split = blockIdx.z;
+    const int64_t kbeg = (int64_t)split * p.k_per_split;
+    const int64_t kend = (kbeg + p.k_per_split < p.K) ? kbeg + p.k_per_split : p.K;
+
+    float acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+    float bsum[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) bsum[i] = 0.f;
+    const bool do_bias = (MODE == SGEMM_WGRAD) && blockIdx.x == 0 && tx == 0 && p.bias_part != nullptr;
+
+    float ra[4], rb[4];
+    const int64_t n_tiles = (kend - kbeg + BK - 1) / BK;
+    if (n_tiles > 0) {
+        load_slab<A_KC, A_VEC>(ra, p.A, p.lda, m0, p.M, kbeg, kend, tid);
+        load_slab<B_KC, B_VEC>(rb, p.B, p.ldb, n0, p.N, kbeg, kend, tid);
+        store_slab<A_KC>(As[0], ra, tid);
+        store_slab<B_KC>(Bs[0], rb, tid);
+    }
+    __syncthreads();
+
+    for (int64_t t = 0; t < n_tiles; ++t) {
+        const int cur = (int)(t & 1);
+        if (t + 1 < n_tiles) {
+            const int64_t k0 = kbeg + (t + 1) * BK;
+            load_slab<A_KC, A_VEC>(ra, p.A, p.lda, m0, p.M, k0, kend, tid);
+            load_slab<B_KC, B_VEC>(rb, p.B, p.ldb, n0, p.N, k0, kend, tid);
+        }
+#pragma unroll
+        for (int kk = 0; kk < BK; ++kk) {
+            const float4 a0 = *reinterpret_cast<const float4 *>(&As[cur][kk][ty * 4]);
+            const float4 a1 = *reinterpret_cast<const float4 *>(&As[cur][kk][64 + ty * 4]);
+            const float4 b0 = *reinterpret_cast<const float4 *>(&Bs[cur][kk][tx * 4]);
+            const float4 b1 = *reinterpret_cast<const float4 *>(&Bs[cur][kk][64 + tx * 4]);
+            const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+            if (MODE == SGEMM_WGRAD) {
+                if (do_bias) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) bsum[i] += a[i];
+                }
+            }
+        }
+        if (t + 1 < n_tiles) {
+            store_slab<A_KC>(As[cur ^ 1], ra, tid);
+            store_slab<B_KC>(Bs[cur ^ 1], rb, tid);
+        }
+        __syncthreads();
+    }
+
+    // ---- epilogue ----
+    float *C = p.C;
+    if (MODE == SGEMM_WGRAD) C += (int64_t)split * p.M * p.N;
+    const bool c_vec = ((p.N & 3) == 0) && ((p.ldc & 3) == 0);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int m = m0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
+        if (m >= p.M) continue;
+        if (MODE == SGEMM_WGRAD && do_bias) p.bias_part[(int64_t)split * p.M + m] = bsum[i];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int n = n0 + h * 64 + tx * 4;
+            if (n >= p.N) continue;
+            float v[4] = {acc[i][h * 4 + 0], acc[i][h * 4 + 1], acc[i][h * 4 + 2], acc[i][h * 4 + 3]};
+            float *dst = C + (int64_t)m * p.ldc + n;
+            if (c_vec) {
+                if (MODE == SGEMM_FWD) {
+                    const float4 bb = *reinterpret_cast<const float4 *>(p.bias + n);
+                    v[0] = fmaxf(v[0] + bb.x, 0.f); v[1] = fmaxf(v[1] + bb.y, 0.f);
+                    v[2] = fmaxf(v[2] + bb.z, 0.f); v[3] = fmaxf(v[3] + bb.w, 0.f);
+                } else if (MODE == SGEMM_DGRAD) {
+                    const float4 mk = *reinterpret_cast<const float4 *>(p.mask + (int64_t)m * p.ldc + n);
+                    v[0] = mk.x > 0.f ? v[0] : 0.f; v[1] = mk.y > 0.f ? v[1] : 0.f;
+                    v[2] = mk.z > 0.f ? v[2] : 0.f; v[3] = mk.w > 0.f ? v[3] : 0.f;
+                }
+                *reinterpret_cast<float4 *>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if (n + j >= p.N) continue;
+                    float o = v[j];
+                    if (MODE == SGEMM_FWD) o = fmaxf(o + p.bias[n + j], 0.f);
+                    else if (MODE == SGEMM_DGRAD) o = p.mask[(int64_t)m * p.ldc + n + j] > 0.f ? o : 0.f;
+                    dst[j] = o;
+                }
+            }
+        }
+    }
+}
+
+inline bool aligned16(const void *p) { return (((uintptr_t)p) & 15) == 0; }
+
+template <int MODE>
+int dispatch(const SgemmArgs &a, bool av, bool bv, dim3 grid, cudaStream_t s) {
+    ProfScope ps(MODE == SGEMM_FWD ? KC_SGEMM_FWD : (MODE == SGEMM_DGRAD ? KC_SGEMM_DGRAD : KC_SGEMM_WGRAD), 1, s);
+    if (av && bv) sgemm_kernel<MODE, true, true><<<grid, kThreads, 0, s>>>(a);
+    else if (av) sgemm_kernel<MODE, true, false><<<grid, kThreads, 0, s>>>(a);
+    else if (bv) sgemm_kernel<MODE, false, true><<<grid, kThreads, 0, s>>>(a);
+    else sgemm_kernel<MODE, false, false><<<grid, kThreads, 0, s>>>(a);
+    OCPPO_LAUNCH_CHECK("sgemm_kernel");
+    return OCPPO_OK;
+}
+
+}  // namespace
+
+int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream) {
+    if (a.M <= 0 || a.N <= 0) return OCPPO_OK;
+    const int splits = mode == SGEMM_WGRAD ? a.splits : 1;
+    OCPPO_CHECK_ARG(splits >= 1 && splits <= kSplitMax, "sgemm: bad split count %d", splits);
+    dim3 grid((unsigned)ceil_div(a.N, BN), (unsigned)ceil_div(a.M, BM), (unsigned)splits);
+    OCPPO_CHECK_ARG(grid.y <= 65535, "sgemm: M too large for one launch (%d)", a.M);
+    // vector-load eligibility per operand
+    bool av, bv;
+    const bool kvec = (a.K % 4 == 0) && (a.k_per_split % 4 == 0);
+    if (mode == SGEMM_WGRAD) {
+        av = (a.M % 4 == 0) && (a.lda % 4 == 0) && aligned16(a.A);
+        bv = (a.N % 4 == 0) && (a.ldb % 4 == 0) && aligned16(a.B);
+    } else {
+        av = kvec && (a.lda % 4 == 0) && aligned16(a.A);
+        if (mode == SGEMM_FWD) bv = kvec && (a.ldb % 4 == 0) && aligned16(a.B);
+        else bv = (a.N % 4 == 0) && (a.ldb % 4 == 0) && aligned16(a.B);
+    }
+    switch (mode) {
+        case SGEMM_FWD: return dispatch<SGEMM_FWD>(a, av, bv, grid, stream);
+        case SGEMM_DGRAD: return dispatch<SGEMM_DGRAD>(a, av, bv, grid, stream);
+        default: return dispatch<SGEMM_WGRAD>(a, av, bv, grid, stream);
+    }
+}
+
+}  // namespace ocppo

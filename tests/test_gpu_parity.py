@@ -1,0 +1,494 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle and the
+committed golden vectors.  Needs a B200: run with ``-m gpu``.
+
+Bars (BASELINE.json north_star): GAE <= 1e-5 relative (we require bit-exact);
+loss / gradients / post-Adam weights <= 1e-4 relative; sampling and minibatch
+permutation bit-exact for the same logits and seed.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden
+from oracle import ref_ppo, ref_sample
+from oc_cleanrl_b200.synthetic import GAME_SHAPES, make_gae_inputs, make_rollout
+
+pytestmark = pytest.mark.gpu
+
+STAT_KEYS = ("pg_loss", "v_loss", "entropy", "loss", "old_approx_kl", "approx_kl", "clipfrac")
+REL_TOL = 1e-4          # loss, gradients, post-Adam weights (north_star)
+
+
+@pytest.fixture(scope="module")
+def dev(built_lib):
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return torch.device("cuda:0")
+
+
+def _stream(dev):
+    return C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+
+def rel_err(got, want):
+    got, want = np.asarray(got, np.float64), np.asarray(want, np.float64)
+    denom = np.abs(want).max()
+    return float(np.abs(got - want).max() / (denom if denom > 0 else 1.0))
+
+
+def make_pair(dev, F, D, A, enc, dec, seed=42):
+    """(device agent, CPU oracle) with bit-identical initial weights."""
+    from oc_cleanrl_b200.architectures.ppo import PPObj
+    torch.manual_seed(seed)
+    agent = PPObj(ref_ppo.stub_envs(F, D, A), dev, enc, dec).to(dev)
+    oracle = ref_ppo.make_agent(F, D, A, enc, dec, seed=seed)
+    for p, q in zip(agent.parameters(), oracle.parameters()):
+        assert torch.equal(p.detach().cpu(), q.detach())
+    return agent, oracle
+
+
+def agent_flat(agent):
+    return torch.cat([p.detach().reshape(-1) for p in agent.parameters()]).cpu().numpy()
+
+
+def agent_flat_grad(agent):
+    out = []
+    for i, _ in enumerate(agent.parameters()):
+        out.append(agent._grad_view(i).reshape(-1))
+    return torch.cat(out).cpu().numpy()
+
+
+# ---------------------------------------------------------------- GAE ------
+@pytest.mark.parametrize("T,N", [(123, 7), (128, 4096), (1, 1), (2, 33), (5, 4), (128, 4098), (300, 64),
+                                 (31, 32), (33, 36), (128, 8)])
+def test_gae_bit_exact_vs_reference_loop(dev, T, N):
+    from oc_cleanrl_b200.learner import compute_gae
+    d = make_gae_inputs(T, N, seed=42)
+    adv_ref, ret_ref = ref_ppo.ref_gae(d["rewards"], d["values"], d["dones"], d["next_value"], d["next_done"],
+                                       0.99, 0.95)
+    g = {k: v.to(dev) for k, v in d.items()}
+    adv, ret = compute_gae(g["rewards"], g["values"], g["dones"], g["next_value"], g["next_done"], 0.99, 0.95)
+    torch.cuda.synchronize()
+    assert torch.equal(adv.cpu(), adv_ref), f"adv max diff {(adv.cpu() - adv_ref).abs().max()}"
+    assert torch.equal(ret.cpu(), ret_ref), f"ret max diff {(ret.cpu() - ret_ref).abs().max()}"
+
+
+def test_gae_empty_and_sparse_rollout(dev, built_lib):
+    from oc_cleanrl_b200.learner import compute_gae
+    z = torch.zeros((0, 8), device=dev)
+    adv, ret = compute_gae(z, z, z, torch.zeros(8, device=dev), torch.zeros(8, device=dev), 0.99, 0.95)
+    assert adv.shape == (0, 8)
+    data = make_rollout(128, 256, 4, 6)           # sparse rewards, rare dones (section 8d)
+    values = torch.randn(128, 256)
+    nv = torch.randn(256)
+    a_ref, r_ref = ref_ppo.ref_gae(data["rewards"], values, data["dones"], nv, data["next_done"], 0.99, 0.95)
+    adv, ret = compute_gae(data["rewards"].to(dev), values.to(dev), data["dones"].to(dev), nv.to(dev),
+                           data["next_done"].to(dev), 0.99, 0.95)
+    assert torch.equal(adv.cpu(), a_ref) and torch.equal(ret.cpu(), r_ref)
+
+
+@pytest.mark.parametrize("N", [16384, 65536])
+def test_gae_large_batch_sweep_vs_c_oracle(dev, oracle_lib, N):
+    """BASELINE config 5 sizes: bit-exact against the C restatement."""
+    from oc_cleanrl_b200.learner import compute_gae
+    T = 128
+    d = make_gae_inputs(T, N, seed=7)
+    arrs = [np.ascontiguousarray(d[k].numpy()) for k in ("rewards", "values", "dones", "next_value", "next_done")]
+    adv_ref = np.zeros((T, N), np.float32)
+    ret_ref = np.zeros((T, N), np.float32)
+    P = lambda x: x.ctypes.data_as(C.c_void_p)  # noqa: E731
+    assert oracle_lib.ocppo_oracle_gae_f32(*[P(x) for x in arrs], C.c_int64(T), C.c_int64(N), C.c_double(0.99),
+                                           C.c_double(0.95), P(adv_ref), P(ret_ref)) == 0
+    g = {k: v.to(dev) for k, v in d.items()}
+    adv, ret = compute_gae(g["rewards"], g["values"], g["dones"], g["next_value"], g["next_done"], 0.99, 0.95)
+    assert np.array_equal(adv.cpu().numpy(), adv_ref) and np.array_equal(ret.cpu().numpy(), ret_ref)
+    # size-independent property: returns - advantages == values exactly where representable
+    assert torch.allclose(ret - adv, g["values"], atol=1e-5)
+
+
+# ---------------------------------------------------------- sampling -------
+@pytest.mark.parametrize("numel", [1, 6, 24576, 1_000_003, 1_300_000])
+def test_exponential_stream_equals_torch_cuda(dev, built_lib, numel):
+    """(i) of SURVEY section 7.4: our Philox stream == torch's exponential_ stream."""
+    seed = 1234
+    torch.cuda.manual_seed(seed)
+    gen = torch.cuda.default_generators[dev.index]
+    off0 = gen.get_offset()
+    want = torch.empty(numel, device=dev).exponential_()
+    off1 = gen.get_offset()
+    got = torch.empty(numel, device=dev)
+    assert built_lib.ocppo_exponential(C.c_void_p(got.data_ptr()), numel, seed, off0, _stream(dev)) == 0
+    torch.cuda.synchronize()
+    props = torch.cuda.get_device_properties(dev)
+    assert off1 - off0 == built_lib.ocppo_philox_increment(numel, props.multi_processor_count,
+                                                           props.max_threads_per_multi_processor)
+    neq = int((got != want).sum())
+    assert neq == 0, f"{neq}/{numel} variates differ; max abs diff {(got - want).abs().max().item()}"
+    # and the uniform words agree with the numpy oracle (CPU log may differ in the last ulp)
+    n_chk = min(numel, 50000)
+    bits = ref_sample.torch_cuda_uniform_bits(numel, seed, off0, props.multi_processor_count,
+                                              props.max_threads_per_multi_processor)[:n_chk]
+    q_ref = ref_sample.torch_cuda_exponential(ref_sample.curand_uniform_from_bits(bits))
+    assert np.allclose(got[:n_chk].cpu().numpy(), q_ref, rtol=3e-7, atol=0)
+
+
+@pytest.mark.parametrize("B,A", [(4096, 6), (8, 6), (1, 4), (5000, 18), (333, 4), (70000, 6)])
+def test_categorical_sample_equals_torch_cuda(dev, built_lib, B, A):
+    """(ii): same logits + same seed -> the same actions as torch's Categorical.sample()."""
+    from torch.distributions.categorical import Categorical
+    seed = 99
+    z = (torch.randn(B, A, generator=torch.Generator().manual_seed(B + A)) * 2.0).to(dev)
+    torch.cuda.manual_seed(seed)
+    off0 = torch.cuda.default_generators[dev.index].get_offset()
+    dist = Categorical(logits=z)
+    want = dist.sample()
+    action = torch.empty(B, dtype=torch.int64, device=dev)
+    logp = torch.empty(B, device=dev)
+    ent = torch.empty(B, device=dev)
+    rc = built_lib.ocppo_categorical(C.c_void_p(z.data_ptr()), B, A, seed, off0, None, C.c_void_p(action.data_ptr()),
+                                     C.c_void_p(logp.data_ptr()), C.c_void_p(ent.data_ptr()), _stream(dev))
+    assert rc == 0
+    torch.cuda.synchronize()
+    mism = int((action != want).sum())
+    assert mism == 0, f"{mism}/{B} sampled actions differ from torch"
+    assert torch.allclose(logp, dist.log_prob(want), rtol=1e-5, atol=1e-6)
+    assert torch.allclose(ent, dist.entropy(), rtol=1e-5, atol=1e-6)
+    # the CPU restatement of the sampler agrees too (up to last-ulp ties)
+    props = torch.cuda.get_device_properties(dev)
+    cpu = ref_sample.ref_categorical_sample(z.cpu().numpy(), seed, off0, props.multi_processor_count,
+                                            props.max_threads_per_multi_processor)
+    assert (cpu["action"] != action.cpu().numpy()).mean() < 1e-3
+
+
+def test_agent_sampling_consumes_torch_generator_like_the_reference(dev):
+    """Drop-in check: PPObj.get_action_and_value(x) under no_grad draws the same actions and
+    leaves torch's CUDA generator where the reference's Categorical.sample() would."""
+    from torch.distributions.categorical import Categorical
+    agent, _ = make_pair(dev, 4, 6, 6, (32, 64), (32,))
+    x = make_rollout(4, 64, 4, 6)["obs"].reshape(-1, 4, 6).to(dev)
+    gen = torch.cuda.default_generators[dev.index]
+    torch.cuda.manual_seed(5)
+    with torch.no_grad():
+        a1, lp1, en1, v1 = agent.get_action_and_value(x)
+        a2, _, _, _ = agent.get_action_and_value(x)
+    off_ours = gen.get_offset()
+    torch.cuda.manual_seed(5)
+    with torch.no_grad():
+        logits = agent.actor(agent.network(x))        # eager torch on the same (arena-backed) weights
+        r1 = Categorical(logits=logits).sample()
+        r2 = Categorical(logits=logits).sample()
+    assert gen.get_offset() == off_ours
+    assert (a1 != r1).float().mean() < 2e-3 and (a2 != r2).float().mean() < 2e-3     # logits differ in last ulps
+    assert not torch.equal(a1, a2)
+    assert a1.dtype == torch.int64 and lp1.shape == (256,) and en1.shape == (256,) and v1.shape == (256, 1)
+
+
+# ------------------------------------------------------ forward parity -----
+@pytest.mark.parametrize("game,B", [("pong", 4096), ("spaceinvaders", 1024), ("breakout", 512)])
+def test_rollout_forward_vs_oracle_default_dims(dev, game, B):
+    """R2/R3 at the script's default widths (encoder 256-512-1024-512, decoder 512)."""
+    D, A = GAME_SHAPES[game]
+    enc, dec = (256, 512, 1024, 512), (512,)
+    agent, oracle = make_pair(dev, 4, D, A, enc, dec)
+    T = 8
+    x_cpu = make_rollout(T, B // T, 4, D)["obs"].reshape(B, 4, D)
+    x = x_cpu.to(dev)
+    torch.cuda.manual_seed(3)
+    with torch.no_grad():
+        action, logp, ent, value = agent.get_action_and_value(x)
+        v_only = agent.get_value(x)
+        a_ref, lp_ref, en_ref, v_ref = oracle.get_action_and_value(x_cpu, action.cpu())
+        _, lp_given, en_given, v_given = agent.get_action_and_value(x, action)
+    assert torch.equal(v_only, value) and torch.equal(lp_given, logp) and torch.equal(en_given, ent)
+    assert rel_err(value.cpu(), v_ref) < REL_TOL, rel_err(value.cpu(), v_ref)
+    assert torch.allclose(logp.cpu(), lp_ref, rtol=REL_TOL, atol=1e-5)
+    assert torch.allclose(ent.cpu(), en_ref, rtol=REL_TOL, atol=1e-5)
+    assert int(action.min()) >= 0 and int(action.max()) < A
+
+
+def test_forward_is_chunk_invariant_and_handles_odd_batches(dev):
+    agent, oracle = make_pair(dev, 4, 6, 6, (32, 64), (32,))
+    for B in (1, 3, 130, 257):
+        x_cpu = torch.randint(0, 200, (B, 4, 6)).float()
+        with torch.no_grad():
+            v = agent.get_value(x_cpu.to(dev))
+            v_ref = oracle.get_value(x_cpu)
+        assert rel_err(v.cpu(), v_ref) < REL_TOL
+    # force chunking: workspace for 64 rows, batch of 257
+    agent._workspace, agent._ws_rows = None, 0
+    agent._ensure_workspace(64, training=False)
+    big = torch.randint(0, 200, (257, 4, 6)).float().to(dev)
+    from oc_cleanrl_b200 import _abi
+    out = torch.empty(257, 1, device=dev)
+    _abi.check(_abi.lib().ocppo_value(agent._handle.raw, _abi.ptr(big), 257, _abi.ptr(out), agent._stream()))
+    agent._ensure_workspace(512, training=False)
+    with torch.no_grad():
+        assert torch.equal(out, agent.get_value(big))
+
+
+# ------------------------------------------------------- update parity -----
+def _golden_case(dev, name):
+    g = load_golden(name)
+    F, D, A, T, N = (int(g[k]) for k in ("F", "D", "A", "T", "N"))
+    enc, dec = tuple(int(x) for x in g["enc"]), tuple(int(x) for x in g["dec"])
+    agent, oracle = make_pair(dev, F, D, A, enc, dec)
+    data = make_rollout(T, N, F, D, seed=1234)
+    return g, agent, oracle, data, (F, D, A, T, N)
+
+
+def _learner(agent, g, T, N, **kw):
+    from oc_cleanrl_b200.learner import LearnerArgs, PPOLearner
+    args = LearnerArgs(num_envs=N, num_steps=T, update_epochs=int(g["epochs"]), num_minibatches=int(g["minibatches"]))
+    for k, v in kw.pop("args", {}).items():
+        setattr(args, k, v)
+    return PPOLearner(agent, args, np_rng=np.random.RandomState(7), **kw)
+
+
+@pytest.mark.parametrize("name", ["small_pong", "small_wide", "default_pong"])
+def test_first_minibatch_loss_and_gradients_vs_reference_golden(dev, name):
+    g, agent, _, data, (F, D, A, T, N) = _golden_case(dev, name)
+    assert abs(float(agent_flat(agent).astype(np.float64).sum()) - float(g["init_sum"])) < 1e-6 * float(g["init_abs"])
+    # forward against the reference model's outputs
+    with torch.no_grad():
+        _, logp, ent, value = agent.get_action_and_value(data["obs"].reshape(T * N, F, D).to(dev),
+                                                         torch.as_tensor(g["actions"]).reshape(-1).to(dev))
+    assert np.allclose(logp.cpu().numpy(), g["logp"], rtol=REL_TOL, atol=1e-5)
+    assert np.allclose(ent.cpu().numpy(), g["entropy"], rtol=REL_TOL, atol=1e-5)
+    assert rel_err(value.cpu().numpy().reshape(-1), g["value"]) < REL_TOL
+    learner = _learner(agent, g, T, N)
+    flat = (data["obs"].reshape(T * N, -1).to(dev), torch.as_tensor(g["actions"]).reshape(-1).to(dev),
+            torch.as_tensor(g["logprobs_old"]).reshape(-1).to(dev), torch.as_tensor(g["adv"]).reshape(-1).to(dev),
+            torch.as_tensor(g["ret"]).reshape(-1).to(dev), torch.as_tensor(g["values_old"]).reshape(-1).to(dev))
+    idx = torch.as_tensor(g["mb0"], dtype=torch.int64).to(dev)
+    from oc_cleanrl_b200 import _abi
+    agent._ensure_workspace(idx.numel(), training=True)
+    stats = torch.zeros(8, device=dev)
+    _abi.check(_abi.lib().ocppo_minibatch_fwd_bwd(agent._handle.raw, *[_abi.ptr(t) for t in flat], _abi.ptr(idx),
+                                                  idx.numel(), C.byref(learner._hp), _abi.ptr(stats), agent._stream()))
+    torch.cuda.synchronize()
+    got_stats = stats.cpu().numpy()[:7]
+    assert np.allclose(got_stats, g["stats0"], rtol=REL_TOL, atol=1e-6), (got_stats, g["stats0"])
+    grad = agent_flat_grad(agent)
+    off = 0
+    for i, p in enumerate(agent.parameters()):
+        n = p.numel()
+        want_norm = g["grad0_per_tensor"][i, 0]
+        got_norm = float(np.linalg.norm(grad[off:off + n].astype(np.float64)))
+        assert abs(got_norm - want_norm) <= REL_TOL * max(want_norm, 1e-6), (i, got_norm, want_norm)
+        off += n
+    if "grad0" in g:
+        assert rel_err(grad, g["grad0"]) < REL_TOL, rel_err(grad, g["grad0"])
+        off = 0
+        for i, p in enumerate(agent.parameters()):          # per tensor, so small tensors are held to the bar too
+            n = p.numel()
+            assert rel_err(grad[off:off + n], g["grad0"][off:off + n]) < REL_TOL, f"tensor {i}"
+            off += n
+    else:
+        assert rel_err(grad[::997], g["grad0_sample"]) < REL_TOL
+
+
+@pytest.mark.parametrize("name", ["small_pong", "small_wide", "default_pong"])
+def test_full_update_vs_reference_golden(dev, name):
+    """Whole update section (all epochs x minibatches): logged stats, grad norms, post-Adam weights."""
+    g, agent, _, data, (F, D, A, T, N) = _golden_case(dev, name)
+    learner = _learner(agent, g, T, N)
+    out = learner.update(data["obs"].to(dev), torch.as_tensor(g["actions"]).to(dev),
+                         torch.as_tensor(g["logprobs_old"]).to(dev), torch.as_tensor(g["adv"]).to(dev),
+                         torch.as_tensor(g["ret"]).to(dev), torch.as_tensor(g["values_old"]).to(dev))
+    n_mb = g["trace_stats"].shape[0]
+    assert out["minibatches"] == n_mb
+    got = learner._stats[:n_mb, :7].cpu().numpy()
+    assert np.allclose(got, g["trace_stats"], rtol=5 * REL_TOL, atol=1e-5), (got, g["trace_stats"])
+    assert np.allclose(out["grad_norms"], g["trace_gn"], rtol=5 * REL_TOL)
+    final = agent_flat(agent)
+    if "final_flat" in g:
+        assert rel_err(final, g["final_flat"]) < REL_TOL, rel_err(final, g["final_flat"])
+    else:
+        assert rel_err(final[::997], g["final_sample"]) < REL_TOL
+    assert learner.adam_step == n_mb
+
+
+def test_update_vs_live_oracle_pong_default_dims(dev):
+    """Config-1-shaped (8 envs x 128 steps, default widths) full 4x4 update vs the CPU oracle."""
+    from oc_cleanrl_b200.learner import LearnerArgs, PPOLearner, compute_gae
+    F, D, A, T, N = 4, 6, 6, 128, 8
+    enc, dec = (256, 512, 1024, 512), (512,)
+    agent, oracle = make_pair(dev, F, D, A, enc, dec)
+    data = make_rollout(T, N, F, D)
+    obs = data["obs"].to(dev)
+    torch.cuda.manual_seed(0)
+    with torch.no_grad():
+        action, logp, _, value = agent.get_action_and_value(obs.reshape(T * N, F, D))
+        next_value = agent.get_value(data["next_obs"].to(dev)).reshape(-1)
+    values = value.reshape(T, N)
+    args = LearnerArgs(num_envs=N, num_steps=T)
+    adv, ret = compute_gae(data["rewards"].to(dev), values, data["dones"].to(dev), next_value,
+                           data["next_done"].to(dev), args.gamma, args.gae_lambda)
+    learner = PPOLearner(agent, args, np_rng=np.random.RandomState(11))
+    learner.anneal_lr(3, 10)
+    out = learner.update(obs, action.reshape(T, N), logp.reshape(T, N), adv, ret, values)
+    torch.set_num_threads(max(1, torch.get_num_threads()))
+    oargs = ref_ppo.PPOArgs(num_envs=N, num_steps=T)
+    opt = ref_ppo.make_optimizer(oracle, oargs)
+    assert ref_ppo.anneal_lr(opt, 3, 10, oargs) == pytest.approx(learner.lr)
+    trace = []
+    ref_ppo.ref_update(oracle, opt, data["obs"], action.cpu().reshape(T, N), logp.cpu().reshape(T, N), adv.cpu(),
+                       ret.cpu(), values.cpu(), oargs, np_rng=np.random.RandomState(11), trace=trace)
+    want_stats = np.array([[float(t["stats"][k]) for k in STAT_KEYS] for t in trace])
+    got_stats = learner._stats[:16, :7].cpu().numpy()
+    assert np.allclose(got_stats[0], want_stats[0], rtol=REL_TOL, atol=1e-6)
+    assert np.allclose(out["grad_norms"][0], float(trace[0]["gn"]), rtol=REL_TOL)
+    assert rel_err(agent_flat(agent), ref_ppo.flat_params(oracle).numpy()) < REL_TOL
+    assert np.allclose(got_stats, want_stats, rtol=0.02, atol=1e-3)        # later minibatches: chaotic amplification
+
+
+def test_chunked_minibatch_is_equivalent_and_deterministic(dev):
+    g, agent, _, data, (F, D, A, T, N) = _golden_case(dev, "small_pong")
+    tensors = (data["obs"].to(dev), torch.as_tensor(g["actions"]).to(dev), torch.as_tensor(g["logprobs_old"]).to(dev),
+               torch.as_tensor(g["adv"]).to(dev), torch.as_tensor(g["ret"]).to(dev),
+               torch.as_tensor(g["values_old"]).to(dev))
+    finals = []
+    for chunk in (32768, 5, 32768):
+        ag, _ = make_pair(dev, F, D, A, tuple(int(x) for x in g["enc"]), tuple(int(x) for x in g["dec"]))
+        learner = _learner(ag, g, T, N, chunk_rows=chunk)
+        learner.update(*tensors)
+        finals.append(agent_flat(ag))
+    assert np.array_equal(finals[0], finals[2])                 # run-to-run deterministic
+    assert rel_err(finals[1], finals[0]) < 1e-5                 # chunking only re-associates sums
+    assert rel_err(finals[1], g["final_flat"]) < REL_TOL
+
+
+def test_option_switches_vs_oracle(dev):
+    """norm_adv / clip_vloss off, other coefficients (ppo_atari_oc.py:138-151)."""
+    F, D, A, T, N = 4, 6, 6, 8, 8
+    enc, dec = (32, 64), (32,)
+    for kw in (dict(norm_adv=False), dict(clip_vloss=False), dict(clip_coef=0.3, ent_coef=0.05, vf_coef=1.0,
+                                                                   max_grad_norm=10.0)):
+        g = load_golden("small_pong")
+        agent, oracle = make_pair(dev, F, D, A, enc, dec)
+        data = make_rollout(T, N, F, D, seed=1234)
+        learner = _learner(agent, g, T, N, args=kw)
+        cpu = (data["obs"], torch.as_tensor(g["actions"]), torch.as_tensor(g["logprobs_old"]),
+               torch.as_tensor(g["adv"]), torch.as_tensor(g["ret"]), torch.as_tensor(g["values_old"]))
+        learner.update(*[t.to(dev) for t in cpu])
+        oargs = ref_ppo.PPOArgs(num_envs=N, num_steps=T, update_epochs=2, num_minibatches=2, **kw)
+        opt = ref_ppo.make_optimizer(oracle, oargs)
+        stats, _, gn = ref_ppo.ref_update(oracle, opt, *cpu, oargs, np_rng=np.random.RandomState(7))
+        assert rel_err(agent_flat(agent), ref_ppo.flat_params(oracle).numpy()) < REL_TOL, kw
+        assert np.allclose(learner._stats[3, :7].cpu().numpy(), [float(stats[k]) for k in STAT_KEYS],
+                           rtol=5 * REL_TOL, atol=1e-5), kw
+
+
+def test_data_parallel_two_ranks_emulated_on_one_gpu(dev):
+    """R12: two env shards, SUM of flat gradients, /world, identical clip+Adam on both ranks --
+    against the in-process K-rank oracle (ppo_atari_multigpu.py:360-377).  Ranks are run one
+    after the other on one device (no inter-kernel waiting)."""
+    from oc_cleanrl_b200 import _abi
+    from oc_cleanrl_b200.learner import LearnerArgs, PPOLearner
+    F, D, A, T, N = 4, 6, 6, 8, 8
+    enc, dec = (32, 64), (32,)
+    world = 2
+    pairs = [make_pair(dev, F, D, A, enc, dec, seed=1) for _ in range(world)]
+    oargs = ref_ppo.PPOArgs(num_envs=N, num_steps=T)
+    opts = [ref_ppo.make_optimizer(o, oargs) for _, o in pairs]
+    rs = np.random.RandomState(0)
+    batches_cpu, idxs = [], []
+    for r in range(world):
+        data = make_rollout(T, N, F, D, rank=r)
+        n = T * N
+        batches_cpu.append((data["obs"].reshape(n, F, D), torch.as_tensor(rs.randint(0, A, n)),
+                            torch.as_tensor(-1.8 + 0.2 * rs.randn(n), dtype=torch.float32),
+                            torch.as_tensor(rs.randn(n), dtype=torch.float32),
+                            torch.as_tensor(rs.randn(n), dtype=torch.float32),
+                            torch.as_tensor(rs.randn(n), dtype=torch.float32)))
+        idxs.append(np.random.RandomState(100 + r).permutation(n)[: n // 4])
+    learners = [PPOLearner(a, LearnerArgs(num_envs=N, num_steps=T), world_size=1) for a, _ in pairs]
+    lib = _abi.lib()
+    total = None
+    for r, ((agent, _), learner) in enumerate(zip(pairs, learners)):
+        flat = tuple(t.to(dev) for t in batches_cpu[r])
+        flat = (flat[0].reshape(T * N, -1),) + flat[1:]
+        idx = torch.as_tensor(idxs[r], dtype=torch.int64).to(dev)
+        agent._ensure_workspace(idx.numel(), training=True)
+        _abi.check(lib.ocppo_minibatch_fwd_bwd(agent._handle.raw, *[_abi.ptr(t) for t in flat], _abi.ptr(idx),
+                                               idx.numel(), C.byref(learner._hp), _abi.ptr(learner._stats[0]),
+                                               agent._stream()))
+        total = agent.grad_arena.clone() if total is None else total + agent.grad_arena      # all_reduce(SUM)
+    gn = torch.zeros(1, device=dev)
+    for agent, _ in pairs:
+        agent.grad_arena.copy_(total)
+        _abi.check(lib.ocppo_clip_adam(agent._handle.raw, 1.0 / world, 0.5, 2.5e-4, 0.9, 0.999, 1e-5, 1,
+                                       _abi.ptr(gn), agent._stream()))
+    _, gns, _ = ref_ppo.ref_dp_minibatch_step([o for _, o in pairs], opts, batches_cpu, idxs, oargs)
+    assert float(gn) == pytest.approx(float(gns[0]), rel=REL_TOL)
+    for agent, oracle in pairs:
+        assert rel_err(agent_flat(agent), ref_ppo.flat_params(oracle).numpy()) < REL_TOL
+    assert np.array_equal(agent_flat(pairs[0][0]), agent_flat(pairs[1][0]))
+
+
+def test_compat_tier_script_style_backward(dev):
+    """The script's own sequence (ppo_atari_oc.py:566-610): grad-mode forward through the agent,
+    torch loss, loss.backward(), clip_grad_norm_, optim.Adam -- unchanged code, our agent."""
+    F, D, A, T, N = 4, 6, 6, 8, 8
+    g = load_golden("small_pong")
+    agent, oracle = make_pair(dev, F, D, A, (32, 64), (32,))
+    data = make_rollout(T, N, F, D, seed=1234)
+    cpu = (data["obs"].reshape(T * N, F, D), torch.as_tensor(g["actions"]).reshape(-1),
+           torch.as_tensor(g["logprobs_old"]).reshape(-1), torch.as_tensor(g["adv"]).reshape(-1),
+           torch.as_tensor(g["ret"]).reshape(-1), torch.as_tensor(g["values_old"]).reshape(-1))
+    gpu = tuple(t.to(dev) for t in cpu)
+    oargs = ref_ppo.PPOArgs(num_envs=N, num_steps=T, update_epochs=2, num_minibatches=2)
+    opt_gpu = torch.optim.Adam(agent.parameters(), lr=oargs.learning_rate, eps=1e-5)
+    opt_cpu = ref_ppo.make_optimizer(oracle, oargs)
+    for step in range(2):
+        inds = np.random.RandomState(step).permutation(T * N)[:32]
+        s_gpu, gn_gpu, raw_gpu = ref_ppo.ref_minibatch_step(agent, opt_gpu, gpu, torch.as_tensor(inds).to(dev), oargs)
+        s_cpu, gn_cpu, raw_cpu = ref_ppo.ref_minibatch_step(oracle, opt_cpu, cpu, inds, oargs)
+        assert float(s_gpu["loss"]) == pytest.approx(float(s_cpu["loss"]), rel=REL_TOL, abs=1e-6)
+        assert rel_err(raw_gpu.cpu().numpy(), raw_cpu.numpy()) < REL_TOL
+        assert float(gn_gpu) == pytest.approx(float(gn_cpu), rel=REL_TOL)
+    assert rel_err(agent_flat(agent), ref_ppo.flat_params(oracle).numpy()) < REL_TOL
+    sd = agent.state_dict()
+    assert list(sd.keys()) == list(oracle.state_dict().keys())           # checkpoint keys (:487,:676)
+    oracle2 = ref_ppo.make_agent(F, D, A, (32, 64), (32,), seed=0)
+    oracle2.load_state_dict({k: v.cpu() for k, v in sd.items()})
+    assert torch.equal(ref_ppo.flat_params(oracle2), torch.as_tensor(agent_flat(agent)))
+
+
+def test_full_size_minibatch_properties(dev):
+    """BASELINE config 2 size (131,072-sample minibatch of a 4096x128 rollout, default widths):
+    too big for the CPU oracle in seconds, so size-independent properties: chunk-size invariance of
+    the gradient, determinism, and agreement with the oracle on a 2,048-sample sub-minibatch."""
+    from oc_cleanrl_b200 import _abi
+    from oc_cleanrl_b200.learner import LearnerArgs, PPOLearner
+    F, D, A, T, N = 4, 6, 6, 128, 4096
+    enc, dec = (256, 512, 1024, 512), (512,)
+    agent, oracle = make_pair(dev, F, D, A, enc, dec)
+    data = make_rollout(T, N, F, D)
+    n = T * N
+    rs = np.random.RandomState(1)
+    cpu = (data["obs"].reshape(n, F, D), torch.as_tensor(rs.randint(0, A, n)),
+           torch.as_tensor(-1.79 + 0.05 * rs.randn(n), dtype=torch.float32),
+           torch.as_tensor(rs.randn(n), dtype=torch.float32), torch.as_tensor(rs.randn(n), dtype=torch.float32),
+           torch.as_tensor(rs.randn(n), dtype=torch.float32))
+    gpu = tuple(t.to(dev) for t in cpu)
+    flat = (gpu[0].reshape(n, -1),) + gpu[1:]
+    perm = torch.as_tensor(np.random.RandomState(42).permutation(n), dtype=torch.int64).to(dev)
+    learner = PPOLearner(agent, LearnerArgs(num_envs=N, num_steps=T))
+    lib = _abi.lib()
+    grads = []
+    for chunk, mb in ((32768, 131072), (16384, 131072), (32768, 131072), (2048, 2048)):
+        agent._workspace, agent._ws_rows, agent._ws_training = None, 0, False
+        agent._ensure_workspace(chunk, training=True)
+        _abi.check(lib.ocppo_minibatch_fwd_bwd(agent._handle.raw, *[_abi.ptr(t) for t in flat], _abi.ptr(perm), mb,
+                                               C.byref(learner._hp), _abi.ptr(learner._stats[0]), agent._stream()))
+        torch.cuda.synchronize()
+        grads.append(agent_flat_grad(agent))
+        assert np.isfinite(grads[-1]).all() and np.isfinite(learner._stats[0].cpu().numpy()).all()
+    assert np.array_equal(grads[0], grads[2])
+    assert rel_err(grads[1], grads[0]) < 1e-5
+    loss, _ = ref_ppo.ref_minibatch_loss(oracle, *cpu, perm[:2048].cpu().numpy(), ref_ppo.PPOArgs())
+    loss.backward()
+    assert rel_err(grads[3], ref_ppo.flat_grads(oracle).numpy()) < REL_TOL
+    assert float(learner._stats[0, 3]) == pytest.approx(float(loss), rel=REL_TOL, abs=1e-6)
