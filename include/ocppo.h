@@ -86,6 +86,9 @@ int ocppo_version(void);
 int64_t ocppo_launch_count(void);
 int ocppo_profile_enable(int32_t on);
 int ocppo_profile_read(double *ms_by_class, int64_t *timed_by_class, int32_t n_classes);
+/* Synchronous micro-benchmark: achievable fp32 FMA TFLOP/s of the current device
+ * (the roofline denominator of the CUDA-core GEMMs; measurement only). */
+int ocppo_measure_fma_peak(double *tflops, void *stream);
 
 /* ---- handle ------------------------------------------------------------ */
 /* Replaces PPObj.__init__ bookkeeping (architectures/ppo.py:61-84). */

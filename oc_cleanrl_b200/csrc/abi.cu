@@ -240,6 +240,11 @@ int64_t ocppo_launch_count(void) {
     return t;
 }
 
+int ocppo_measure_fma_peak(double *tflops, void *stream) {
+    OCPPO_CHECK_ARG(tflops != nullptr, "null argument");
+    return measure_fma_peak(tflops, as_stream(stream));
+}
+
 int ocppo_profile_enable(int32_t on) {
     if (on && !g_prof.created) {
         for (int i = 0; i < kProfMaxPairs; ++i) {

@@ -161,6 +161,7 @@ int launch_loss_finalize(const double *part, int n_part, int64_t mb, float ent_c
 int launch_splitk_reduce(const float *part, int splits, int64_t stride, int64_t count, float *out, int accumulate,
                          int sm_count, cudaStream_t stream);
 int launch_relu_mask(const float *g, const float *act, int64_t n, float *out, int sm_count, cudaStream_t stream);
+int measure_fma_peak(double *tflops, cudaStream_t stream);
 int launch_clip_adam(ocppo_handle *h, float inv_world, float max_norm, double lr, double beta1, double beta2,
                      double eps, int64_t step, float *grad_norm, cudaStream_t stream);
 

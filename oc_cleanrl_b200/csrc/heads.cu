@@ -409,6 +409,57 @@ __global__ void __launch_bounds__(256) adam_kernel(AdamArgs a) {
 
 }  // namespace
 
+// FP32 FMA peak probe (roofline denominator for the CUDA-core GEMMs; MEASURED_PEAKS.json
+// has no fp32 figure).  16 independent FMA chains per thread.
+namespace {
+__global__ void __launch_bounds__(256) fma_peak_kernel(float *out, int iters, float a, float b) {
+    float acc[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) acc[i] = (float)(threadIdx.x + i);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) acc[i] = fmaf(acc[i], a, b);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) s += acc[i];
+    if (s == 123.456f) out[0] = s;          // never true; keeps the chains alive
+}
+}  // namespace
+
+int measure_fma_peak(double *tflops, cudaStream_t stream) {
+    int sms, mt;
+    {
+        int dev = 0;
+        OCPPO_CUDA(cudaGetDevice(&dev));
+        OCPPO_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        mt = 0;
+    }
+    (void)mt;
+    float *dummy = nullptr;
+    OCPPO_CUDA(cudaMalloc(&dummy, 256));
+    cudaEvent_t e0, e1;
+    OCPPO_CUDA(cudaEventCreate(&e0));
+    OCPPO_CUDA(cudaEventCreate(&e1));
+    const int iters = 8192, blocks = sms * 8;
+    double best = 0;
+    for (int rep = 0; rep < 5; ++rep) {
+        OCPPO_CUDA(cudaEventRecord(e0, stream));
+        fma_peak_kernel<<<blocks, 256, 0, stream>>>(dummy, iters, 0.999f, 0.001f);
+        OCPPO_CUDA(cudaEventRecord(e1, stream));
+        OCPPO_CUDA(cudaEventSynchronize(e1));
+        float ms = 0;
+        OCPPO_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        const double tf = 2.0 * blocks * 256.0 * 16.0 * iters / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(dummy);
+    *tflops = best;
+    return OCPPO_OK;
+}
+
 // ---------------------------------------------------------------------------
 // host-side launchers
 // ---------------------------------------------------------------------------
