@@ -90,6 +90,21 @@ int ocppo_profile_read(double *ms_by_class, int64_t *timed_by_class, int32_t n_c
  * (the roofline denominator of the CUDA-core GEMMs; measurement only). */
 int ocppo_measure_fma_peak(double *tflops, void *stream);
 
+/* ---- GEMM engine selection + raw GEMM (tests / measurement) -------------- */
+/* The trunk GEMMs (nn.Linear forward, dgrad, wgrad of architectures/ppo.py:70-84)
+ * run either on fp32 CUDA-core FMA kernels (mode 0) or on tcgen05 tensor cores
+ * with a 3-pass TF32 split that keeps fp32-grade accuracy (mode 1, used wherever
+ * the shape fits the 128x256x32 tile; other shapes stay on FMA). */
+int ocppo_set_gemm_mode(int32_t mode);
+int ocppo_get_gemm_mode(void);
+/* One GEMM of the family.  op 0: C[M,N] = relu(A[M,K] B[N,K]^T + bias[N]);
+ * op 1: C[M,N] = (mask[M,N] > 0) * (A[M,K] B[K,N]);
+ * op 2: C[s][M,N] = sum over rows k of split s of A[k,M]^T B[k,N] (+ bias_part[s][M]
+ * = column sums of A).  engine 0 = FMA, 1 = tcgen05 (shape must be supported). */
+int ocppo_gemm(int32_t op, int32_t engine, int32_t M, int32_t N, int64_t K, const float *A, int64_t lda,
+               const float *B, int64_t ldb, float *C, int64_t ldc, const float *bias, const float *mask,
+               float *bias_part, int32_t splits, int64_t k_per_split, void *stream);
+
 /* ---- handle ------------------------------------------------------------ */
 /* Replaces PPObj.__init__ bookkeeping (architectures/ppo.py:61-84). */
 int ocppo_create(const ocppo_config *cfg, ocppo_handle **out);

@@ -59,6 +59,9 @@ _SIGNATURES = {
     "ocppo_profile_enable": (C.c_int, [_I32]),
     "ocppo_profile_read": (C.c_int, [C.POINTER(_D), C.POINTER(_I64), _I32]),
     "ocppo_measure_fma_peak": (C.c_int, [C.POINTER(_D), _P]),
+    "ocppo_set_gemm_mode": (C.c_int, [_I32]),
+    "ocppo_get_gemm_mode": (C.c_int, []),
+    "ocppo_gemm": (C.c_int, [_I32, _I32, _I32, _I32, _I64, _P, _I64, _P, _I64, _P, _I64, _P, _P, _P, _I32, _I64, _P]),
     "ocppo_create": (C.c_int, [C.POINTER(Config), C.POINTER(_P)]),
     "ocppo_destroy": (C.c_int, [_P]),
     "ocppo_num_tensors": (C.c_int, [_P, C.POINTER(_I32), C.POINTER(_I64), C.POINTER(_I64)]),

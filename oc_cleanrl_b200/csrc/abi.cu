@@ -171,15 +171,17 @@ static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_
 }
 
 static void pick_split(const ocppo_handle *h, int M, int N, int64_t K, int *splits, int64_t *k_per) {
-    const int64_t tiles = ceil_div(M, 128) * ceil_div(N, 128);
-    const int64_t target = (int64_t)h->sm_count * 4;
-    int64_t S = ceil_div(target, tiles);
+    // tensor path: 128x256 tiles, one CTA per SM; FMA path: 128x128 tiles, 2 CTAs per SM, 2 waves
+    const bool tc = g_gemm_mode == 1 && M % 128 == 0 && N % 256 == 0;
+    const int64_t tiles = tc ? (int64_t)(M / 128) * (N / 256) : ceil_div(M, 128) * ceil_div(N, 128);
+    const int64_t target = tc ? (int64_t)h->sm_count : (int64_t)h->sm_count * 4;
+    int64_t S = tc ? (target + tiles / 2) / tiles : ceil_div(target, tiles);
     const int64_t s_cap = K / 256 > 1 ? K / 256 : 1;
     if (S > s_cap) S = s_cap;
     if (S > kSplitMax) S = kSplitMax;
     if (S < 1) S = 1;
-    int64_t kp = round_up(ceil_div(K, S), 8);
-    if (kp < 8) kp = 8;
+    int64_t kp = round_up(ceil_div(K, S), 32);
+    if (kp < 32) kp = 32;
     *k_per = kp;
     *splits = (int)ceil_div(K, kp);
     if (*splits < 1) *splits = 1;
@@ -238,6 +240,26 @@ int64_t ocppo_launch_count(void) {
     int64_t t = 0;
     for (int i = 0; i < KC_COUNT; ++i) t += g_prof.launches[i];
     return t;
+}
+
+int ocppo_set_gemm_mode(int32_t mode) {
+    OCPPO_CHECK_ARG(mode == 0 || mode == 1, "gemm mode must be 0 (fp32 FMA) or 1 (tcgen05 3xTF32)");
+    g_gemm_mode = mode;
+    return OCPPO_OK;
+}
+int ocppo_get_gemm_mode(void) { return g_gemm_mode; }
+
+int ocppo_gemm(int32_t op, int32_t engine, int32_t M, int32_t N, int64_t K, const float *A, int64_t lda,
+               const float *B, int64_t ldb, float *C, int64_t ldc, const float *bias, const float *mask,
+               float *bias_part, int32_t splits, int64_t k_per_split, void *stream) {
+    OCPPO_CHECK_ARG(op >= 0 && op <= 2 && engine >= 0 && engine <= 1, "bad op/engine");
+    OCPPO_CHECK_ARG(A && B && C, "null pointer");
+    SgemmArgs a{};
+    a.A = A; a.lda = lda; a.B = B; a.ldb = ldb; a.C = C; a.ldc = ldc; a.bias = bias; a.mask = mask;
+    a.bias_part = bias_part; a.M = M; a.N = N; a.K = K; a.splits = splits < 1 ? 1 : splits;
+    a.k_per_split = k_per_split > 0 ? k_per_split : round_up(K, 32);
+    if (engine == 1) return tc_gemm_launch((SgemmMode)op, a, as_stream(stream));
+    return fma_gemm_launch((SgemmMode)op, a, as_stream(stream));
 }
 
 int ocppo_measure_fma_peak(double *tflops, void *stream) {

@@ -124,7 +124,12 @@ struct SgemmArgs {
     int splits;
 };
 
-int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);
+int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);       // dispatches FMA / tensor
+int fma_gemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);    // sgemm.cu, fp32 CUDA cores
+bool tc_gemm_supported(SgemmMode mode, const SgemmArgs &a);                      // tc_gemm.cu, tcgen05 3xTF32
+int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);
+// 0: fp32 FMA kernels only; 1: tcgen05 3xTF32 wherever the shape fits (fp32-grade accuracy)
+extern int g_gemm_mode;
 
 int launch_gae(const float *rewards, const float *values, const float *dones,
                const float *next_value, const float *next_done, int64_t T, int64_t N, float g,

@@ -189,7 +189,14 @@ int dispatch(const SgemmArgs &a, bool av, bool bv, dim3 grid, cudaStream_t s) {
 
 }  // namespace
 
+int g_gemm_mode = 0;
+
 int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream) {
+    if (g_gemm_mode == 1 && tc_gemm_supported(mode, a)) return tc_gemm_launch(mode, a, stream);
+    return fma_gemm_launch(mode, a, stream);
+}
+
+int fma_gemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream) {
     if (a.M <= 0 || a.N <= 0) return OCPPO_OK;
     const int splits = mode == SGEMM_WGRAD ? a.splits : 1;
     OCPPO_CHECK_ARG(splits >= 1 && splits <= kSplitMax, "sgemm: bad split count %d", splits);

@@ -1,0 +1,35 @@
+"""The GEMM family (fp32 FMA and tcgen05 3xTF32 engines) against torch fp64 on device."""
+import os
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+
+CASES = [
+    (0, 128, 256, 32, 1), (0, 256, 512, 256, 1), (0, 4096, 512, 256, 1), (0, 1000, 256, 96, 1),
+    (0, 2048, 512, 2048, 1),
+    (1, 512, 256, 512, 1), (1, 4096, 1024, 512, 1), (1, 640, 2048, 512, 1),
+    (2, 256, 256, 4096, 4), (2, 512, 1024, 8192, 8), (2, 256, 512, 1000, 2), (2, 1024, 512, 16384, 9),
+]
+
+
+@pytest.mark.parametrize("engine", [0, 1])
+@pytest.mark.parametrize("op,M,N,K,S", CASES)
+def test_gemm_engine_vs_fp64(built_lib, engine, op, M, N, K, S):
+    import gemm_diag
+    msg = gemm_diag.run(op, engine, M, N, K, S, "randn", seed=op * 7 + M)
+    assert "BAD" not in msg and "rc=" not in msg, msg
+    rel = float(msg.split("rel_err=")[1].split()[0])
+    assert rel < 2e-5, msg            # fp32-grade: both engines, far inside the 1e-4 bar
+    if op == 2:
+        assert float(msg.split("bias_rel=")[1].split()[0]) < 2e-5, msg
+
+
+def test_gemm_mode_switch_roundtrip(built_lib):
+    assert built_lib.ocppo_set_gemm_mode(1) == 0 and built_lib.ocppo_get_gemm_mode() == 1
+    assert built_lib.ocppo_set_gemm_mode(0) == 0 and built_lib.ocppo_get_gemm_mode() == 0
+    assert built_lib.ocppo_set_gemm_mode(7) == -1
