@@ -122,6 +122,7 @@ struct SgemmArgs {
     int64_t K;                // contraction length (rows for WGRAD)
     int64_t k_per_split;
     int splits;
+    int dbg;                  // tc_gemm bring-up variant (0 in production)
 };
 
 int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);       // dispatches FMA / tensor

@@ -52,7 +52,8 @@ __device__ __forceinline__ float curand_uniform_from_word(uint32_t x) {
 // q ~ Exp(1) exactly as torch's CUDA exponential_ for fp32
 __device__ __forceinline__ float torch_exponential_from_uniform(float u) {
     const float eps_half = 1.1920928955078125e-07f / 2.0f;
-    const float lg = (u >= 1.0f - eps_half) ? -eps_half : logf(u);
+    // at::log on CUDA is the fast __logf (torch ATen/NumericUtils.h), not logf
+    const float lg = (u >= 1.0f - eps_half) ? -eps_half : __logf(u);
     return -1.0f * lg;
 }
 

@@ -9,6 +9,7 @@
 // canonical UMMA SWIZZLE_128B layouts -> tcgen05.mma issued by one thread; completion is
 // tracked with tcgen05.commit on an mbarrier per stage.  Epilogue: tcgen05.ld 32x32b.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace ocppo {
 
@@ -45,13 +46,17 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 }
 
 // 64-bit shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout).
-__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// layout_type: 2 = SWIZZLE_128B (K-major tiles), 1 = SWIZZLE_128B_BASE32B -- the only
+// layout the hardware takes for MN-major 32-bit (tf32) operands (CUTLASS
+// sm100_common.inl: "for mn-major tf32 operands, SW128_32B is the only available smem layout").
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                              uint32_t layout_type) {
     uint64_t d = 0;
     d |= (uint64_t)((saddr >> 4) & 0x3FFF);               // start address, bits [0,14)
     d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;     // leading byte offset, bits [16,30)
     d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;     // stride byte offset, bits [32,46)
     d |= (uint64_t)1 << 46;                               // version = 1 (Blackwell)
-    d |= (uint64_t)2 << 61;                               // layout type: SWIZZLE_128B
+    d |= (uint64_t)layout_type << 61;
     return d;
 }
 
@@ -140,7 +145,8 @@ __device__ __forceinline__ void sts_mnmajor(uint8_t *hi, uint8_t *lo, const floa
 #pragma unroll
     for (int p = 0; p < W / 32; ++p) {
         const int k = p * kRowsPerPass + kr;
-        const int off = mb * 4096 + (k >> 3) * 1024 + (k & 7) * 128 + ((c ^ (k & 7)) << 4);
+        // SW128_BASE32B atom: 32 MN floats (128 B) x 4 k-rows; 32 B chunks XOR (k & 3)
+        const int off = mb * 4096 + (k >> 2) * 512 + (k & 3) * 128 + ((((c >> 1) ^ (k & 3)) << 5) | ((c & 1) << 4));
         float4 h, l;
         split_tf32(r[p].x, h.x, l.x); split_tf32(r[p].y, h.y, l.y);
         split_tf32(r[p].z, h.z, l.z); split_tf32(r[p].w, h.w, l.w);
@@ -214,11 +220,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_gemm_kernel(SgemmArgs p) {
         __syncthreads();
         if (tid == 0) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t lbo = 4096, sbo = 1024;
-            const uint64_t da_hi = make_desc(smem_u32(a_hi), A_MN ? lbo : 16, sbo);
-            const uint64_t da_lo = make_desc(smem_u32(a_lo), A_MN ? lbo : 16, sbo);
-            const uint64_t db_hi = make_desc(smem_u32(b_hi), B_MN ? lbo : 16, sbo);
-            const uint64_t db_lo = make_desc(smem_u32(b_lo), B_MN ? lbo : 16, sbo);
+            // K-major: SBO = 8-row group stride (1024 B), LBO unused.  MN-major: LBO = stride between
+            // 32-float MN chunks (4096 B), SBO = stride between 4-row k groups (512 B).
+            const uint32_t mn_lbo = p.dbg == 1 ? 512 : 4096, mn_sbo = p.dbg == 1 ? 4096 : 512;
+            const uint64_t da_hi = make_desc(smem_u32(a_hi), A_MN ? mn_lbo : 16, A_MN ? mn_sbo : 1024, A_MN ? 1 : 2);
+            const uint64_t da_lo = make_desc(smem_u32(a_lo), A_MN ? mn_lbo : 16, A_MN ? mn_sbo : 1024, A_MN ? 1 : 2);
+            const uint64_t db_hi = make_desc(smem_u32(b_hi), B_MN ? mn_lbo : 16, B_MN ? mn_sbo : 1024, B_MN ? 1 : 2);
+            const uint64_t db_lo = make_desc(smem_u32(b_lo), B_MN ? mn_lbo : 16, B_MN ? mn_sbo : 1024, B_MN ? 1 : 2);
             // per k-step of 8: K-major advances 32 B inside the 128 B row, MN-major one 1024 B atom
             constexpr uint64_t a_step = (A_MN ? 1024 : 32) >> 4, b_step = (B_MN ? 1024 : 32) >> 4;
 #pragma unroll
@@ -329,7 +337,10 @@ bool tc_gemm_supported(SgemmMode mode, const SgemmArgs &a) {
     return true;
 }
 
-int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream) {
+int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
+    static const int dbg = getenv("OCPPO_TC_DBG") ? atoi(getenv("OCPPO_TC_DBG")) : 0;   // bring-up knob only
+    SgemmArgs a = a_in;
+    a.dbg = dbg;
     OCPPO_CHECK_ARG(tc_gemm_supported(mode, a), "tc_gemm: unsupported shape M=%d N=%d K=%lld", a.M, a.N, (long long)a.K);
     const int splits = mode == SGEMM_WGRAD ? a.splits : 1;
     dim3 grid((unsigned)(a.N / TN), (unsigned)ceil_div(a.M, TM), (unsigned)splits);

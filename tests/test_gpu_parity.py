@@ -130,7 +130,7 @@ def test_exponential_stream_equals_torch_cuda(dev, built_lib, numel):
     bits = ref_sample.torch_cuda_uniform_bits(numel, seed, off0, props.multi_processor_count,
                                               props.max_threads_per_multi_processor)[:n_chk]
     q_ref = ref_sample.torch_cuda_exponential(ref_sample.curand_uniform_from_bits(bits))
-    assert np.allclose(got[:n_chk].cpu().numpy(), q_ref, rtol=3e-7, atol=0)
+    assert np.allclose(got[:n_chk].cpu().numpy(), q_ref, rtol=2e-6, atol=5e-7)   # __logf vs libm log
 
 
 @pytest.mark.parametrize("B,A", [(4096, 6), (8, 6), (1, 4), (5000, 18), (333, 4), (70000, 6)])
