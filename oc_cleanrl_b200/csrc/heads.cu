@@ -207,10 +207,16 @@ __global__ void __launch_bounds__(kHeadThreads) loss_head_kernel(LossArgs p) {
         const float dv = p.vf_coef * inv_mb * g_v;
         if (lane < p.AP) p.gz[i * p.AP + lane] = lane < A ? dz : (lane == A ? dv : 0.f);
         // d hidden, masked by ReLU of the last trunk layer
-        for (int j = lane; j < H; j += 32) {
-            float s = dv * sW[A * H + j];
-            for (int k = 0; k < A; ++k) s = fmaf(__shfl_sync(kFull, dz, k), sW[k * H + j], s);
-            p.dh[i * H + j] = h[j] > 0.f ? s : 0.f;
+        // (warp-uniform trip count: the shuffles below need all 32 lanes, also when H % 32 != 0)
+        for (int j0 = 0; j0 < H; j0 += 32) {
+            const int j = j0 + lane;
+            const bool on = j < H;
+            float s = on ? dv * sW[A * H + j] : 0.f;
+            for (int k = 0; k < A; ++k) {
+                const float dzk = __shfl_sync(kFull, dz, k);
+                if (on) s = fmaf(dzk, sW[k * H + j], s);
+            }
+            if (on) p.dh[i * H + j] = h[j] > 0.f ? s : 0.f;
         }
         if (lane == 0) {
             acc[0] += (double)pg;

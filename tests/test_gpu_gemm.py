@@ -14,6 +14,8 @@ CASES = [
     (0, 2048, 512, 2048, 1),
     (1, 512, 256, 512, 1), (1, 4096, 1024, 512, 1), (1, 640, 2048, 512, 1),
     (2, 256, 256, 4096, 4), (2, 512, 1024, 8192, 8), (2, 256, 512, 1000, 2), (2, 1024, 512, 16384, 9),
+    # more tiles than SMs (persistent tensor-core kernel walks several tiles per CTA), ragged M
+    (0, 32768, 1024, 512, 1), (1, 19999, 2048, 512, 1), (2, 512, 2048, 32768, 19),
 ]
 
 

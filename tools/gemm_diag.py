@@ -78,6 +78,9 @@ if __name__ == "__main__":
         (1, 4096, 1024, 512, 1, "randn"),
         (2, 128, 256, 32, 1, "int"), (2, 128, 256, 64, 1, "int"), (2, 256, 256, 4096, 4, "randn"),
         (2, 512, 1024, 8192, 8, "randn"), (2, 256, 512, 1000, 2, "randn"),
+        # persistent-kernel coverage: many more tiles than SMs, ragged M, several tiles per CTA
+        (0, 32768, 1024, 512, 1, "randn"), (0, 20000, 512, 256, 1, "randn"), (1, 32768, 512, 1024, 1, "randn"),
+        (1, 19999, 2048, 512, 1, "randn"), (2, 1024, 512, 65536, 9, "randn"), (2, 512, 2048, 32768, 19, "randn"),
     ]
     for e in engines:
         for (op, M, N, K, S, kind) in cases:
