@@ -171,14 +171,28 @@ static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_
 }
 
 static void pick_split(const ocppo_handle *h, int M, int N, int64_t K, int *splits, int64_t *k_per) {
-    // tensor path: 128x256 tiles, one CTA per SM; FMA path: 128x128 tiles, 2 CTAs per SM, 2 waves
     const bool tc = g_gemm_mode == 1 && M % 128 == 0 && N % 256 == 0;
-    const int64_t tiles = tc ? (int64_t)(M / 128) * (N / 256) : ceil_div(M, 128) * ceil_div(N, 128);
-    const int64_t target = tc ? (int64_t)h->sm_count : (int64_t)h->sm_count * 4;
-    int64_t S = tc ? (target + tiles / 2) / tiles : ceil_div(target, tiles);
-    const int64_t s_cap = K / 256 > 1 ? K / 256 : 1;
-    if (S > s_cap) S = s_cap;
-    if (S > kSplitMax) S = kSplitMax;
+    int64_t S;
+    const int64_t s_cap0 = K / 256 > 1 ? K / 256 : 1;
+    const int64_t s_cap = s_cap0 < kSplitMax ? s_cap0 : kSplitMax;
+    if (tc) {
+        // persistent kernel, one CTA pair per 2 SMs, 256x256 tiles: the split count that fills the last wave best
+        // (fewest splits on ties -- less partial traffic); accuracy does not depend on it, the kernel
+        // drains its accumulator every 1024 rows.
+        const int64_t tiles = ceil_div(M, 256) * (N / 256), sms = h->sm_count / 2;   // 256x256 tiles, one per CTA pair
+        S = 1;
+        double best = 0.0;
+        for (int64_t c = 1; c <= s_cap; ++c) {
+            const int64_t w = tiles * c;
+            const double util = (double)w / (double)(ceil_div(w, sms) * sms);
+            if (util > best + 1e-9) { best = util; S = c; }
+        }
+    } else {
+        // FMA path: 128x128 tiles, 2 CTAs per SM, aim at two full waves
+        const int64_t tiles = ceil_div(M, 128) * ceil_div(N, 128);
+        S = ceil_div((int64_t)h->sm_count * 4, tiles);
+        if (S > s_cap) S = s_cap;
+    }
     if (S < 1) S = 1;
     int64_t kp = round_up(ceil_div(K, S), 32);
     if (kp < 32) kp = 32;

@@ -5,16 +5,21 @@
 //   DGRAD : dX[M,N] = (mask > 0) * (dY[M,K] . W[K,N])      A K-major,  B MN-major
 //   WGRAD : dW[M,N] = dY[K,M]^T . X[K,N]  (split-K)        A MN-major, B MN-major
 //
-// Persistent, warp-specialised: one CTA per SM walks 128 x 256 output tiles.
+// Persistent, warp-specialised, CTA-pair kernel: a cluster of two CTAs (one SM each, same TPC) walks
+// 256 x 256 output tiles with tcgen05.mma.cta_group::2.  Each CTA stages its own 128 rows of A and its own
+// 128 columns of B (so the pair fetches every operand byte once), and holds the 128 x 256 fp32 accumulator of
+// its rows in its own TMEM.  Per CTA:
 //   warps 0-3   epilogue : tcgen05.ld the finished accumulator, bias/ReLU or ReLU-mask, transpose
 //                          through a per-warp smem pad, 128 B-coalesced STG
-//   warp  4     MMA      : one thread issues tcgen05.mma; accumulators double-buffered in TMEM
-//                          (2 x 256 columns) so the epilogue of tile i overlaps the mainloop of i+1
+//   warp  4     MMA      : one thread of the LEADER CTA issues the pair's MMAs; accumulators are
+//                          double-buffered in TMEM (2 x 256 columns) so the epilogue of tile i overlaps
+//                          the mainloop of tile i+1
 //   warps 5-7   idle (pad the MMA warp to a warpgroup so setmaxnreg can move registers to the producers)
 //   warps 8-15  producers: LDG.128 -> registers (two k-blocks in flight) -> hi/lo split -> STS into
 //                          the canonical UMMA layouts (K-major: SWIZZLE_128B, MN-major tf32:
-//                          SWIZZLE_128B_BASE32B), 2 stages x 96 KB
-// All hand-offs are mbarriers: full/empty per smem stage, tmem_full/tmem_empty per accumulator.
+//                          SWIZZLE_128B_BASE32B), 3 stages x 64 KB
+// Hand-offs are mbarriers: full (leader CTA; both CTAs' producers arrive, the peer's remotely) / empty per
+// smem stage and tmem_full / tmem_empty per accumulator; tcgen05.commit multicasts to both CTAs.
 #include "common.cuh"
 #include <stdlib.h>
 
@@ -22,15 +27,19 @@ namespace ocppo {
 
 namespace {
 
-constexpr int TM = 128, TN = 256, TK = 32;
+constexpr int TM = 128;                                     // rows of A (and of the accumulator) per CTA
+constexpr int TN = 256;                                     // accumulator columns (the pair's full N tile)
+constexpr int TBW = 128;                                    // columns of B staged per CTA
+constexpr int TK = 32;
+constexpr int kPairM = 2 * TM;                              // 256-row tile per CTA pair
 constexpr int kEpiWarps = 4, kProdWarps = 8;
 constexpr int kProdThreads = kProdWarps * 32;               // 256
 constexpr int kProdTid0 = 256;                              // warpgroups 2-3
 constexpr int kTcThreads = kProdTid0 + kProdThreads;        // 512 = 4 warpgroups (setmaxnreg is per warpgroup)
 constexpr int kStageBytesA = TM * TK * 4;                   // 16 KB
-constexpr int kStageBytesB = TN * TK * 4;                   // 32 KB
-constexpr int kStageBytes = 2 * (kStageBytesA + kStageBytesB);   // hi + lo: 96 KB
-constexpr int kNumStages = 2;
+constexpr int kStageBytesB = TBW * TK * 4;                  // 16 KB
+constexpr int kStageBytes = 2 * (kStageBytesA + kStageBytesB);   // hi + lo: 64 KB
+constexpr int kNumStages = 3;
 constexpr int kTmemCols = 512;                              // two 256-column accumulators
 constexpr int kEpiPadBytes = kEpiWarps * 32 * 33 * 4;       // per-warp 32 x 33 transpose pads
 constexpr int kBiasRedBytes = 8 * TM * 4;                   // WGRAD bias partials [8 k-lanes][128]
@@ -41,8 +50,23 @@ __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)_
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive (release at cluster scope) on the barrier at the same smem offset in CTA `cta` of the pair
+__device__ __forceinline__ void mbar_arrive_on(uint32_t bar, uint32_t cta) {
+    asm volatile(
+        "{\n\t.reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}"
+        ::"r"(bar), "r"(cta)
+        : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     const long long t0 = clock64();
@@ -50,7 +74,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     while (true) {
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
             "selp.u32 %0, 1, 0, p;\n\t}"
             : "=r"(done)
             : "r"(bar), "r"(parity)
@@ -85,22 +109,25 @@ __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint6
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+// arrives (count 1) on the barrier at this smem offset in BOTH CTAs once all prior MMAs have completed
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)3)
+                 : "memory");
 }
 
+// a = hi + lo with hi on the TF32 grid.  tools/tc_probe.cu (Q1) shows kind::tf32 reads the top 19 bits of
+// its fp32 operands and ignores the rest (truncation), so hi is rounded here with two integer ops
+// (round-half-up on the magnitude; cvt.rna.tf32 costs four with its NaN fix-up and made the producers
+// issue-bound) and lo = a - hi (exact in fp32, |lo| <= 2^-11 |a|) is handed over as is: the hardware keeps
+// its top 11 bits, leaving a residual <= 2^-21 |a|.
 __device__ __forceinline__ void split_tf32(float x, float &hi, float &lo) {
-    uint32_t h;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h) : "f"(x));
-    hi = __uint_as_float(h);
-    const float r = x - hi;                                // exact
-    uint32_t l;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l) : "f"(r));
-    lo = __uint_as_float(l);
+    hi = __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
+    lo = x - hi;
 }
 __device__ __forceinline__ void split4(const float4 &v, float4 &h, float4 &l) {
     split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y);
@@ -179,7 +206,7 @@ __device__ __forceinline__ TileCoord tile_coord(const SgemmArgs &p, int tile, in
     const int rest = tile / nt_n;
     const int mb = rest % nt_m;
     t.split = rest / nt_m;
-    t.m0 = mb * TM;
+    t.m0 = mb * kPairM;
     t.n0 = nb * TN;
     t.kbeg = (int64_t)t.split * p.k_per_split;
     t.kend = (t.kbeg + p.k_per_split < p.K) ? t.kbeg + p.k_per_split : p.K;
@@ -200,64 +227,97 @@ __device__ __forceinline__ TileCoord tile_coord(const SgemmArgs &p, int tile, in
         : "memory")
 
 template <int MODE>
-__global__ void __launch_bounds__(kTcThreads, 1) tc_gemm_kernel(SgemmArgs p, int nt_n, int nt_m, int ntiles) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_gemm_kernel(SgemmArgs p, int nt_n, int nt_m, int ntiles) {
     constexpr bool A_MN = (MODE == SGEMM_WGRAD);
     constexpr bool B_MN = (MODE != SGEMM_FWD);
+    // The TMEM accumulator adds with truncation (measured: error grows linearly with the number of MMAs
+    // chained into one accumulator), so WGRAD, whose contraction runs over >= 10^4 rows, is cut into
+    // 1024-row segments; each is drained by the epilogue and summed in fp32 round-to-nearest in fixed order.
+    constexpr int kSegStages = (MODE == SGEMM_WGRAD) ? 32 : (1 << 30);
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     float *epi_pad = reinterpret_cast<float *>(smem + kNumStages * kStageBytes);
     float *bias_red = reinterpret_cast<float *>(smem + kNumStages * kStageBytes + kEpiPadBytes);
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kNumStages * kStageBytes + kEpiPadBytes + kBiasRedBytes);
-    // bars[0..1] full, [2..3] empty, [4..5] tmem_full, [6..7] tmem_empty
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 8);
-    const uint32_t bar_full = smem_u32(&bars[0]), bar_empty = smem_u32(&bars[2]);
-    const uint32_t bar_tfull = smem_u32(&bars[4]), bar_tempty = smem_u32(&bars[6]);
+    // bars[0..2] full (used in the leader CTA), [3..5] empty, [6..7] tmem_full, [8..9] tmem_empty (leader)
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 10);
+    const uint32_t bar_full = smem_u32(&bars[0]), bar_empty = smem_u32(&bars[3]);
+    const uint32_t bar_tfull = smem_u32(&bars[6]), bar_tempty = smem_u32(&bars[8]);
+    const uint32_t cta_rank = cluster_ctarank();             // 0 = leader of the pair
+    const int ncl = gridDim.x >> 1, cl = blockIdx.x >> 1;    // clusters in the grid, this cluster
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
     if (tid == 0) {
         for (int s = 0; s < kNumStages; ++s) {
-            mbar_init(bar_full + 8 * s, kProdWarps);
+            mbar_init(bar_full + 8 * s, 2 * kProdWarps);     // both CTAs' producer warps
             mbar_init(bar_empty + 8 * s, 1);
-            mbar_init(bar_tfull + 8 * s, 1);
-            mbar_init(bar_tempty + 8 * s, kEpiWarps);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(bar_tfull + 8 * a, 1);
+            mbar_init(bar_tempty + 8 * a, 2 * kEpiWarps);    // both CTAs' epilogue warps
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == kEpiWarps) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
                      "r"((uint32_t)kTmemCols)
                      : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
+    cluster_sync_all();          // barriers of BOTH CTAs initialised before anyone arrives remotely
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp < kEpiWarps) {
         // ===================== epilogue =====================
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 96;");
+        // (keeps the 128 registers it was launched with: 4*32*(128+40) + 8*32*168 = 64512 <= 65536)
         float *pad = epi_pad + warp * 32 * 33;
-        int ti = 0;
-        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++ti) {
-            const TileCoord t = tile_coord(p, tile, nt_n, nt_m);
-            const int acc = ti & 1;
-            mbar_wait(bar_tfull + 8 * acc, (uint32_t)((ti >> 1) & 1));
+        int ai = 0;                           // accumulator passes handled so far (tile x k-segment)
+        for (int tile = cl; tile < ntiles; tile += ncl) {
+          const TileCoord t = tile_coord(p, tile, nt_n, nt_m);
+          for (int kb0 = 0; kb0 < t.nk; kb0 += kSegStages, ++ai) {
+            const int acc = ai & 1;
+            const bool rmw = (MODE == SGEMM_WGRAD) && kb0 > 0;     // later k-segments add onto the first
+            mbar_wait(bar_tfull + 8 * acc, (uint32_t)((ai >> 1) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             float *Cb = p.C;
             if (MODE == SGEMM_WGRAD) Cb += (int64_t)t.split * p.M * p.N;
+            const int m0c = t.m0 + (int)cta_rank * TM;          // this CTA's rows of the pair tile
             const int r_sub = lane >> 3, col = (lane & 7) * 4;
+            // DGRAD: the ReLU mask of chunk cc+1 is fetched while chunk cc is drained (8 independent
+            // LDG.128 per lane in flight instead of one DRAM round trip per row group).  WGRAD k-segments
+            // after the first fetch the running partial the same way (written by this very thread).
+            float4 mk[8], mk_next[8];
+            auto load_mask = [&](int cc, float4 (&dst)[8]) {
+                const int n = t.n0 + cc * 32 + col;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int m = m0c + warp * 32 + i * 4 + r_sub;
+                    if (m >= p.M) dst[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    else if (MODE == SGEMM_DGRAD) dst[i] = __ldg(reinterpret_cast<const float4 *>(p.mask + (int64_t)m * p.ldc + n));
+                    else dst[i] = __ldcg(reinterpret_cast<const float4 *>(Cb + (int64_t)m * p.ldc + n));
+                }
+            };
+            if (MODE == SGEMM_DGRAD) load_mask(0, mk_next);
 #pragma unroll 1
             for (int cc = 0; cc < TN / 32; ++cc) {
                 uint32_t v[32];
                 const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(acc * TN + cc * 32);
                 OCPPO_TMEM_LD32(v, taddr);
+                if (MODE == SGEMM_DGRAD) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) mk[i] = mk_next[i];
+                    if (cc + 1 < TN / 32) load_mask(cc + 1, mk_next);
+                } else if (rmw) {
+                    load_mask(cc, mk);         // L2-resident partial; single-buffered to stay within 128 registers
+                }
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                 if (cc == TN / 32 - 1) {       // accumulator drained: hand it back to the MMA warp
                     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+                    if (lane == 0) mbar_arrive_on(bar_tempty + 8 * acc, 0);
                 }
 #pragma unroll
                 for (int j = 0; j < 32; ++j) pad[lane * 33 + j] = __uint_as_float(v[j]);
@@ -268,45 +328,50 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_gemm_kernel(SgemmArgs p, int
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                     const int row = i * 4 + r_sub;
-                    const int m = t.m0 + warp * 32 + row;
+                    const int m = m0c + warp * 32 + row;
                     const float *src = pad + row * 33 + col;
                     float4 o = make_float4(src[0], src[1], src[2], src[3]);
-                    if (m < p.M) {
+                    if (m < p.M && !(p.dbg & 2)) {
                         if (MODE == SGEMM_FWD) {
                             o.x = fmaxf(o.x + bb.x, 0.f); o.y = fmaxf(o.y + bb.y, 0.f);
                             o.z = fmaxf(o.z + bb.z, 0.f); o.w = fmaxf(o.w + bb.w, 0.f);
                         } else if (MODE == SGEMM_DGRAD) {
-                            const float4 mk = __ldg(reinterpret_cast<const float4 *>(p.mask + (int64_t)m * p.ldc + n));
-                            o.x = mk.x > 0.f ? o.x : 0.f; o.y = mk.y > 0.f ? o.y : 0.f;
-                            o.z = mk.z > 0.f ? o.z : 0.f; o.w = mk.w > 0.f ? o.w : 0.f;
+                            o.x = mk[i].x > 0.f ? o.x : 0.f; o.y = mk[i].y > 0.f ? o.y : 0.f;
+                            o.z = mk[i].z > 0.f ? o.z : 0.f; o.w = mk[i].w > 0.f ? o.w : 0.f;
+                        } else if (rmw) {
+                            o.x += mk[i].x; o.y += mk[i].y; o.z += mk[i].z; o.w += mk[i].w;
                         }
                         *reinterpret_cast<float4 *>(Cb + (int64_t)m * p.ldc + n) = o;
                     }
                 }
                 __syncwarp();
             }
+          }
         }
     } else if (warp < 2 * kEpiWarps) {
         // ===================== MMA issuer (warp 4; warps 5-7 idle) =====================
         asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-        if (warp == kEpiWarps && lane == 0) {
-            constexpr uint32_t idesc = make_idesc(TM, TN, A_MN, B_MN);
+        if (warp == kEpiWarps && lane == 0 && cta_rank == 0) {
+            constexpr uint32_t idesc = make_idesc(kPairM, TN, A_MN, B_MN);   // M = 256 across the pair
             // K-major: SBO = 8-row group stride (1024 B), LBO unused.  MN-major: LBO = stride between
             // 32-float MN chunks (4096 B), SBO = stride between 4-row k groups (512 B).
             constexpr uint32_t a_lbo = A_MN ? 4096 : 16, a_sbo = A_MN ? 512 : 1024, a_ty = A_MN ? 1 : 2;
             constexpr uint32_t b_lbo = B_MN ? 4096 : 16, b_sbo = B_MN ? 512 : 1024, b_ty = B_MN ? 1 : 2;
             // per k-step of 8: K-major advances 32 B inside the 128 B row, MN-major two 512 B atoms
             constexpr uint64_t a_step = (A_MN ? 1024 : 32) >> 4, b_step = (B_MN ? 1024 : 32) >> 4;
-            int it = 0, ti = 0;
-            for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++ti) {
-                const TileCoord t = tile_coord(p, tile, nt_n, nt_m);
-                const int acc = ti & 1;
-                mbar_wait(bar_tempty + 8 * acc, (uint32_t)(((ti >> 1) & 1) ^ 1));
+            int stage = 0, sphase = 0, ai = 0;
+            for (int tile = cl; tile < ntiles; tile += ncl) {
+              const TileCoord t = tile_coord(p, tile, nt_n, nt_m);
+              for (int kb0 = 0; kb0 < t.nk; kb0 += kSegStages, ++ai) {
+                const int acc = ai & 1;
+                mbar_wait(bar_tempty + 8 * acc, (uint32_t)(((ai >> 1) & 1) ^ 1));
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t d_tmem = tmem_base + (uint32_t)(acc * TN);
-                for (int kb = 0; kb < t.nk; ++kb, ++it) {
-                    const int s = it & 1;
-                    mbar_wait(bar_full + 8 * s, (uint32_t)((it >> 1) & 1));
+                const int kb1 = (t.nk - kb0 < kSegStages) ? t.nk : kb0 + kSegStages;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    const int s = stage;
+                    mbar_wait(bar_full + 8 * s, (uint32_t)sphase);
+                    if (++stage == kNumStages) { stage = 0; sphase ^= 1; }
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     uint8_t *st = smem + s * kStageBytes;
                     const uint32_t a_hi = smem_u32(st), a_lo = a_hi + kStageBytesA;
@@ -315,14 +380,15 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_gemm_kernel(SgemmArgs p, int
                     const uint64_t db_hi = make_desc(b_hi, b_lbo, b_sbo, b_ty), db_lo = make_desc(b_lo, b_lbo, b_sbo, b_ty);
 #pragma unroll
                     for (int ks = 0; ks < TK / 8; ++ks) {
-                        const uint32_t acc0 = (kb > 0 || ks > 0) ? 1u : 0u;
+                        const uint32_t acc0 = (kb > kb0 || ks > 0) ? 1u : 0u;
                         umma_tf32(d_tmem, da_lo + ks * a_step, db_hi + ks * b_step, idesc, acc0);
                         umma_tf32(d_tmem, da_hi + ks * a_step, db_lo + ks * b_step, idesc, 1u);
                         umma_tf32(d_tmem, da_hi + ks * a_step, db_hi + ks * b_step, idesc, 1u);
                     }
-                    umma_commit(bar_empty + 8 * s);          // stage free once these MMAs have read it
+                    umma_commit_pair(bar_empty + 8 * s);     // stage free (in both CTAs) once these MMAs have read it
                 }
-                umma_commit(bar_tfull + 8 * acc);            // accumulator complete
+                umma_commit_pair(bar_tfull + 8 * acc);       // accumulator (k-segment) complete in both CTAs
+              }
             }
         }
         __syncwarp();
@@ -331,22 +397,28 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_gemm_kernel(SgemmArgs p, int
         asm volatile("setmaxnreg.inc.sync.aligned.u32 168;");
         const int pt = tid - kProdTid0;
         const int pwarp_lane0 = (lane == 0);
-        int it = 0;
-        float4 ra0[4], rb0[8], ra1[4], rb1[8];
-        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        int stage = 0, sphase = 0;
+        float4 ra0[4], rb0[4], ra1[4], rb1[4];
+        const int rank_m = (int)cta_rank * TM, rank_n = (int)cta_rank * TBW;
+        for (int tile = cl; tile < ntiles; tile += ncl) {
             const TileCoord t = tile_coord(p, tile, nt_n, nt_m);
             const bool do_bias = (MODE == SGEMM_WGRAD) && t.n0 == 0 && p.bias_part != nullptr;
             float4 bsum = make_float4(0.f, 0.f, 0.f, 0.f);
-            auto load = [&](int kb, float4 (&ra)[4], float4 (&rb)[8]) {
+            auto load = [&](int kb, float4 (&ra)[4], float4 (&rb)[4]) {
+                if (p.dbg & 1) {             // bring-up experiment: no global loads
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) { ra[q] = make_float4(1.f, 2.f, 3.f, 4.f); rb[q] = ra[q]; }
+                    return;
+                }
                 const int64_t k0 = t.kbeg + (int64_t)kb * TK;
-                if (A_MN) ldg_mnmajor<TM>(ra, p.A, p.lda, t.m0, p.M, k0, t.kend, pt);
-                else ldg_kmajor<TM>(ra, p.A, p.lda, t.m0, p.M, k0, t.kend, pt);
-                if (B_MN) ldg_mnmajor<TN>(rb, p.B, p.ldb, t.n0, p.N, k0, t.kend, pt);
-                else ldg_kmajor<TN>(rb, p.B, p.ldb, t.n0, p.N, k0, t.kend, pt);
+                if (A_MN) ldg_mnmajor<TM>(ra, p.A, p.lda, t.m0 + rank_m, p.M, k0, t.kend, pt);
+                else ldg_kmajor<TM>(ra, p.A, p.lda, t.m0 + rank_m, p.M, k0, t.kend, pt);
+                if (B_MN) ldg_mnmajor<TBW>(rb, p.B, p.ldb, t.n0 + rank_n, p.N, k0, t.kend, pt);
+                else ldg_kmajor<TBW>(rb, p.B, p.ldb, t.n0 + rank_n, p.N, k0, t.kend, pt);
             };
-            auto store = [&](const float4 (&ra)[4], const float4 (&rb)[8]) {
-                const int s = it & 1;
-                mbar_wait(bar_empty + 8 * s, (uint32_t)(((it >> 1) & 1) ^ 1));
+            auto store = [&](const float4 (&ra)[4], const float4 (&rb)[4]) {
+                const int s = stage;
+                mbar_wait(bar_empty + 8 * s, (uint32_t)(sphase ^ 1));
                 uint8_t *st = smem + s * kStageBytes;
                 uint8_t *a_hi = st, *a_lo = st + kStageBytesA, *b_hi = st + 2 * kStageBytesA, *b_lo = b_hi + kStageBytesB;
                 if (MODE == SGEMM_WGRAD) {
@@ -357,12 +429,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_gemm_kernel(SgemmArgs p, int
                 }
                 if (A_MN) sts_mnmajor<TM>(a_hi, a_lo, ra, pt);
                 else sts_kmajor<TM>(a_hi, a_lo, ra, pt);
-                if (B_MN) sts_mnmajor<TN>(b_hi, b_lo, rb, pt);
-                else sts_kmajor<TN>(b_hi, b_lo, rb, pt);
+                if (B_MN) sts_mnmajor<TBW>(b_hi, b_lo, rb, pt);
+                else sts_kmajor<TBW>(b_hi, b_lo, rb, pt);
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
-                if (pwarp_lane0) mbar_arrive(bar_full + 8 * s);
-                ++it;
+                if (pwarp_lane0) mbar_arrive_on(bar_full + 8 * s, 0);      // the leader CTA's barrier
+                if (++stage == kNumStages) { stage = 0; sphase ^= 1; }
             };
             load(0, ra0, rb0);
             if (t.nk > 1) load(1, ra1, rb1);
@@ -383,7 +455,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_gemm_kernel(SgemmArgs p, int
                         float sum = 0.f;
 #pragma unroll
                         for (int kr = 0; kr < 8; ++kr) sum += bias_red[kr * TM + pt];
-                        if (t.m0 + pt < p.M) p.bias_part[(int64_t)t.split * p.M + t.m0 + pt] = sum;
+                        if (t.m0 + rank_m + pt < p.M) p.bias_part[(int64_t)t.split * p.M + t.m0 + rank_m + pt] = sum;
                     }
                     asm volatile("bar.sync 1, %0;" ::"n"(kProdThreads) : "memory");
                 }
@@ -391,9 +463,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_gemm_kernel(SgemmArgs p, int
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
+    cluster_sync_all();          // neither CTA leaves (or frees TMEM) while its peer can still touch it
     if (warp == kEpiWarps) {
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTmemCols)
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTmemCols)
                      : "memory");
     }
 }
@@ -418,10 +490,13 @@ bool tc_gemm_supported(SgemmMode mode, const SgemmArgs &a) {
     return true;
 }
 
-int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream) {
+int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
+    static const int dbg = getenv("OCPPO_TC_DBG") ? atoi(getenv("OCPPO_TC_DBG")) : 0;   // bring-up knob only
+    SgemmArgs a = a_in;
+    a.dbg = dbg;
     OCPPO_CHECK_ARG(tc_gemm_supported(mode, a), "tc_gemm: unsupported shape M=%d N=%d K=%lld", a.M, a.N, (long long)a.K);
     const int splits = mode == SGEMM_WGRAD ? a.splits : 1;
-    const int nt_n = a.N / TN, nt_m = (int)ceil_div(a.M, TM);
+    const int nt_n = a.N / TN, nt_m = (int)ceil_div(a.M, kPairM);
     const int64_t ntiles64 = (int64_t)nt_n * nt_m * splits;
     OCPPO_CHECK_ARG(ntiles64 < (1LL << 31), "tc_gemm: too many tiles");
     const int ntiles = (int)ntiles64;
@@ -434,7 +509,7 @@ int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream) {
         OCPPO_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<SGEMM_DGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
         OCPPO_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<SGEMM_WGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
     }
-    const int grid = ntiles < sms ? ntiles : sms;
+    const int grid = 2 * (ntiles < sms / 2 ? ntiles : sms / 2);     // CTA pairs
     ProfScope ps(mode == SGEMM_FWD ? KC_SGEMM_FWD : (mode == SGEMM_DGRAD ? KC_SGEMM_DGRAD : KC_SGEMM_WGRAD), 1, stream);
     if (mode == SGEMM_FWD) tc_gemm_kernel<SGEMM_FWD><<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles);
     else if (mode == SGEMM_DGRAD) tc_gemm_kernel<SGEMM_DGRAD><<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles);
