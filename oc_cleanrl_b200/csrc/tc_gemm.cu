@@ -21,6 +21,7 @@
 // Hand-offs are mbarriers: full (leader CTA; both CTAs' producers arrive, the peer's remotely) / empty per
 // smem stage and tmem_full / tmem_empty per accumulator; tcgen05.commit multicasts to both CTAs.
 #include "common.cuh"
+#include <cuda.h>
 #include <stdlib.h>
 
 namespace ocppo {
@@ -120,82 +121,60 @@ __device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
                  : "memory");
 }
 
-// a = hi + lo with hi on the TF32 grid.  tools/tc_probe.cu (Q1) shows kind::tf32 reads the top 19 bits of
-// its fp32 operands and ignores the rest (truncation), so hi is rounded here with two integer ops
-// (round-half-up on the magnitude; cvt.rna.tf32 costs four with its NaN fix-up and made the producers
-// issue-bound) and lo = a - hi (exact in fp32, |lo| <= 2^-11 |a|) is handed over as is: the hardware keeps
-// its top 11 bits, leaving a residual <= 2^-21 |a|.
-__device__ __forceinline__ void split_tf32(float x, float &hi, float &lo) {
-    hi = __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
-    lo = x - hi;
+// ---- lo-tile generation (p = producer-local thread id, 0..255) ---------------
+// TMA has landed the raw fp32 tile in the canonical UMMA layout; kind::tf32 reads only its top 19 bits, so
+// the raw tile IS the hi operand.  The producers read it back, form lo = x - trunc_tf32(x) rounded to the TF32
+// grid and write it at the same offset of the lo tile (same layout, so no index arithmetic beyond the
+// thread -> 16-byte chunk map below, chosen so every warp access is bank-conflict free).
+__device__ __forceinline__ float lo_of(float x) {
+    const float r = x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);      // exact, |r| < 2^-10 |x|
+    return __uint_as_float((__float_as_uint(r) + 0x1000u) & 0xFFFFE000u);       // to the TF32 grid, half-up
 }
-__device__ __forceinline__ void split4(const float4 &v, float4 &h, float4 &l) {
-    split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y);
-    split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
+__device__ __forceinline__ float4 lo4(const float4 &v) {
+    return make_float4(lo_of(v.x), lo_of(v.y), lo_of(v.z), lo_of(v.w));
 }
-
-// ---- operand staging (p = producer-local thread id, 0..255) ------------------
-// K-major tile of ROWS rows x 32 floats: 8 threads per row (16 B each), 32 rows per pass.
-template <int ROWS>
-__device__ __forceinline__ void ldg_kmajor(float4 (&r)[ROWS / 32], const float *__restrict__ base, int64_t ld,
-                                           int row0, int row_limit, int64_t k0, int64_t k_limit, int p) {
+// K-major tile of 128 rows x 32 floats (SWIZZLE_128B): 8 threads per row, 32 rows per pass.
+__device__ __forceinline__ void conv_kmajor(const uint8_t *hi, uint8_t *lo, int p) {
     const int rr = p >> 3, c = p & 7;
 #pragma unroll
-    for (int q = 0; q < ROWS / 32; ++q) {
-        const int row = row0 + q * 32 + rr;
-        const int64_t k = k0 + c * 4;
-        if (row < row_limit && k < k_limit)
-            r[q] = __ldg(reinterpret_cast<const float4 *>(base + (int64_t)row * ld + k));
-        else
-            r[q] = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-}
-template <int ROWS>
-__device__ __forceinline__ void sts_kmajor(uint8_t *hi, uint8_t *lo, const float4 (&r)[ROWS / 32], int p) {
-    const int rr = p >> 3, c = p & 7;
-#pragma unroll
-    for (int q = 0; q < ROWS / 32; ++q) {
+    for (int q = 0; q < 4; ++q) {
         const int row = q * 32 + rr;
-        const int off = (row >> 3) * 1024 + (row & 7) * 128 + ((c ^ (row & 7)) << 4);
-        float4 h, l;
-        split4(r[q], h, l);
-        *reinterpret_cast<float4 *>(hi + off) = h;
-        *reinterpret_cast<float4 *>(lo + off) = l;
+        const int off = row * 128 + ((c ^ (row & 7)) << 4);
+        const float4 v = *reinterpret_cast<const float4 *>(hi + off);
+        *reinterpret_cast<float4 *>(lo + off) = lo4(v);
     }
 }
-// MN-major tile of 32 k-rows x W contiguous floats: W/4 chunks per k-row.
-template <int W>
-__device__ __forceinline__ void ldg_mnmajor(float4 (&r)[W / 32], const float *__restrict__ base, int64_t ld,
-                                            int col0, int col_limit, int64_t k0, int64_t k_limit, int p) {
-    constexpr int kChunks = W / 4;                 // per k-row
-    constexpr int kRowsPerPass = kProdThreads / kChunks;
-    const int q = p % kChunks, kr = p / kChunks;
-#pragma unroll
-    for (int i = 0; i < W / 32; ++i) {
-        const int64_t k = k0 + i * kRowsPerPass + kr;
-        const int col = col0 + q * 4;
-        if (k < k_limit && col < col_limit)
-            r[i] = __ldg(reinterpret_cast<const float4 *>(base + k * ld + col));
-        else
-            r[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-}
-template <int W>
-__device__ __forceinline__ void sts_mnmajor(uint8_t *hi, uint8_t *lo, const float4 (&r)[W / 32], int p) {
-    constexpr int kChunks = W / 4;
-    constexpr int kRowsPerPass = kProdThreads / kChunks;
-    const int q = p % kChunks, kr = p / kChunks;
+// MN-major tile of 32 k-rows x 128 floats (4 chunks of [32 k][32 floats], SWIZZLE_128B_BASE32B).  Thread p
+// owns the 4 columns (p % 32) * 4.. in k-rows p / 32 + 8 i; `colsum` accumulates them (WGRAD bias gradient).
+template <bool SUM>
+__device__ __forceinline__ void conv_mnmajor(const uint8_t *hi, uint8_t *lo, int p, float4 &colsum) {
+    const int q = p & 31, kr = p >> 5;
     const int mb = q >> 3, c = q & 7;
 #pragma unroll
-    for (int i = 0; i < W / 32; ++i) {
-        const int k = i * kRowsPerPass + kr;
-        // SW128_BASE32B atom: 32 MN floats (128 B) x 4 k-rows; 32 B chunks XOR (k & 3)
-        const int off = mb * 4096 + (k >> 2) * 512 + (k & 3) * 128 + ((((c >> 1) ^ (k & 3)) << 5) | ((c & 1) << 4));
-        float4 h, l;
-        split4(r[i], h, l);
-        *reinterpret_cast<float4 *>(hi + off) = h;
-        *reinterpret_cast<float4 *>(lo + off) = l;
+    for (int i = 0; i < 4; ++i) {
+        const int k = i * 8 + kr;
+        const int off = mb * 4096 + k * 128 + ((((c >> 1) ^ (k & 3)) << 5) | ((c & 1) << 4));
+        const float4 v = *reinterpret_cast<const float4 *>(hi + off);
+        if (SUM) { colsum.x += v.x; colsum.y += v.y; colsum.z += v.z; colsum.w += v.w; }
+        *reinterpret_cast<float4 *>(lo + off) = lo4(v);
     }
+}
+
+// ---- TMA ----------------------------------------------------------------------
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *tm, int c0, int c1, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tm)), "r"(c0), "r"(c1), "r"(bar)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *tm, int c0, int c1, int c2, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tm)), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+        : "memory");
 }
 
 struct TileCoord { int m0, n0, split; int64_t kbeg, kend; int nk; };
@@ -227,7 +206,8 @@ __device__ __forceinline__ TileCoord tile_coord(const SgemmArgs &p, int tile, in
         : "memory")
 
 template <int MODE>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_gemm_kernel(SgemmArgs p, int nt_n, int nt_m, int ntiles) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_gemm_kernel(SgemmArgs p, int nt_n, int nt_m, int ntiles, const __grid_constant__ CUtensorMap tmA,
+                                                                                         const __grid_constant__ CUtensorMap tmB) {
     constexpr bool A_MN = (MODE == SGEMM_WGRAD);
     constexpr bool B_MN = (MODE != SGEMM_FWD);
     // The TMEM accumulator adds with truncation (measured: error grows linearly with the number of MMAs
@@ -239,8 +219,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
     float *epi_pad = reinterpret_cast<float *>(smem + kNumStages * kStageBytes);
     float *bias_red = reinterpret_cast<float *>(smem + kNumStages * kStageBytes + kEpiPadBytes);
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kNumStages * kStageBytes + kEpiPadBytes + kBiasRedBytes);
-    // bars[0..2] full (used in the leader CTA), [3..5] empty, [6..7] tmem_full, [8..9] tmem_empty (leader)
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 10);
+    // bars[0..2] full (used in the leader CTA), [3..5] empty, [6..7] tmem_full, [8..9] tmem_empty (leader),
+    // [10..12] tma (raw tile landed, per CTA)
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 13);
+    const uint32_t bar_tma = smem_u32(&bars[10]);
     const uint32_t bar_full = smem_u32(&bars[0]), bar_empty = smem_u32(&bars[3]);
     const uint32_t bar_tfull = smem_u32(&bars[6]), bar_tempty = smem_u32(&bars[8]);
     const uint32_t cta_rank = cluster_ctarank();             // 0 = leader of the pair
@@ -252,6 +234,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
         for (int s = 0; s < kNumStages; ++s) {
             mbar_init(bar_full + 8 * s, 2 * kProdWarps);     // both CTAs' producer warps
             mbar_init(bar_empty + 8 * s, 1);
+            mbar_init(bar_tma + 8 * s, 1);
         }
         for (int a = 0; a < 2; ++a) {
             mbar_init(bar_tfull + 8 * a, 1);
@@ -272,7 +255,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
 
     if (warp < kEpiWarps) {
         // ===================== epilogue =====================
-        // (keeps the 128 registers it was launched with: 4*32*(128+40) + 8*32*168 = 64512 <= 65536)
         float *pad = epi_pad + warp * 32 * 33;
         int ai = 0;                           // accumulator passes handled so far (tile x k-segment)
         for (int tile = cl; tile < ntiles; tile += ncl) {
@@ -350,7 +332,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
         }
     } else if (warp < 2 * kEpiWarps) {
         // ===================== MMA issuer (warp 4; warps 5-7 idle) =====================
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
         if (warp == kEpiWarps && lane == 0 && cta_rank == 0) {
             constexpr uint32_t idesc = make_idesc(kPairM, TN, A_MN, B_MN);   // M = 256 across the pair
             // K-major: SBO = 8-row group stride (1024 B), LBO unused.  MN-major: LBO = stride between
@@ -391,60 +372,56 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
               }
             }
         }
+        else if (warp == kEpiWarps + 1 && lane == 0) {
+            // ===================== TMA issuer (warp 5, both CTAs) =====================
+            // raw fp32 tiles of this CTA's A rows / B columns, straight into the hi slots of the stage ring
+            const int rank_m = (int)cta_rank * TM, rank_n = (int)cta_rank * TBW;
+            int stage = 0, sphase = 0;
+            for (int tile = cl; tile < ntiles; tile += ncl) {
+                const TileCoord t = tile_coord(p, tile, nt_n, nt_m);
+                for (int kb = 0; kb < t.nk; ++kb) {
+                    const int s = stage;
+                    mbar_wait(bar_empty + 8 * s, (uint32_t)(sphase ^ 1));
+                    const uint32_t a_hi = smem_u32(smem + s * kStageBytes), b_hi = a_hi + 2 * kStageBytesA;
+                    const uint32_t bar = bar_tma + 8 * s;
+                    const int k0 = (int)(t.kbeg + (int64_t)kb * TK);
+                    mbar_expect_tx(bar, kStageBytesA + kStageBytesB);
+                    if (A_MN) tma_load_3d(a_hi, &tmA, 0, k0, (t.m0 + rank_m) >> 5, bar);
+                    else tma_load_2d(a_hi, &tmA, k0, t.m0 + rank_m, bar);
+                    if (B_MN) tma_load_3d(b_hi, &tmB, 0, k0, (t.n0 + rank_n) >> 5, bar);
+                    else tma_load_2d(b_hi, &tmB, k0, t.n0 + rank_n, bar);
+                    if (++stage == kNumStages) { stage = 0; sphase ^= 1; }
+                }
+            }
+        }
         __syncwarp();
     } else {
         // ===================== producers =====================
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 168;");
         const int pt = tid - kProdTid0;
         const int pwarp_lane0 = (lane == 0);
         int stage = 0, sphase = 0;
-        float4 ra0[4], rb0[4], ra1[4], rb1[4];
-        const int rank_m = (int)cta_rank * TM, rank_n = (int)cta_rank * TBW;
+        const int rank_m = (int)cta_rank * TM;
         for (int tile = cl; tile < ntiles; tile += ncl) {
             const TileCoord t = tile_coord(p, tile, nt_n, nt_m);
             const bool do_bias = (MODE == SGEMM_WGRAD) && t.n0 == 0 && p.bias_part != nullptr;
-            float4 bsum = make_float4(0.f, 0.f, 0.f, 0.f);
-            auto load = [&](int kb, float4 (&ra)[4], float4 (&rb)[4]) {
-                if (p.dbg & 1) {             // bring-up experiment: no global loads
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) { ra[q] = make_float4(1.f, 2.f, 3.f, 4.f); rb[q] = ra[q]; }
-                    return;
-                }
-                const int64_t k0 = t.kbeg + (int64_t)kb * TK;
-                if (A_MN) ldg_mnmajor<TM>(ra, p.A, p.lda, t.m0 + rank_m, p.M, k0, t.kend, pt);
-                else ldg_kmajor<TM>(ra, p.A, p.lda, t.m0 + rank_m, p.M, k0, t.kend, pt);
-                if (B_MN) ldg_mnmajor<TBW>(rb, p.B, p.ldb, t.n0 + rank_n, p.N, k0, t.kend, pt);
-                else ldg_kmajor<TBW>(rb, p.B, p.ldb, t.n0 + rank_n, p.N, k0, t.kend, pt);
-            };
-            auto store = [&](const float4 (&ra)[4], const float4 (&rb)[4]) {
+            float4 bsum = make_float4(0.f, 0.f, 0.f, 0.f), unused = bsum;
+            for (int kb = 0; kb < t.nk; ++kb) {
                 const int s = stage;
-                mbar_wait(bar_empty + 8 * s, (uint32_t)(sphase ^ 1));
+                mbar_wait(bar_tma + 8 * s, (uint32_t)sphase);           // raw tile landed (TMA complete_tx)
                 uint8_t *st = smem + s * kStageBytes;
                 uint8_t *a_hi = st, *a_lo = st + kStageBytesA, *b_hi = st + 2 * kStageBytesA, *b_lo = b_hi + kStageBytesB;
-                if (MODE == SGEMM_WGRAD) {
-                    if (do_bias) {
-#pragma unroll
-                        for (int q = 0; q < 4; ++q) { bsum.x += ra[q].x; bsum.y += ra[q].y; bsum.z += ra[q].z; bsum.w += ra[q].w; }
-                    }
+                if (A_MN) {
+                    if (do_bias) conv_mnmajor<true>(a_hi, a_lo, pt, bsum);
+                    else conv_mnmajor<false>(a_hi, a_lo, pt, unused);
+                } else {
+                    conv_kmajor(a_hi, a_lo, pt);
                 }
-                if (A_MN) sts_mnmajor<TM>(a_hi, a_lo, ra, pt);
-                else sts_kmajor<TM>(a_hi, a_lo, ra, pt);
-                if (B_MN) sts_mnmajor<TBW>(b_hi, b_lo, rb, pt);
-                else sts_kmajor<TBW>(b_hi, b_lo, rb, pt);
+                if (B_MN) conv_mnmajor<false>(b_hi, b_lo, pt, unused);
+                else conv_kmajor(b_hi, b_lo, pt);
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
                 if (pwarp_lane0) mbar_arrive_on(bar_full + 8 * s, 0);      // the leader CTA's barrier
                 if (++stage == kNumStages) { stage = 0; sphase ^= 1; }
-            };
-            load(0, ra0, rb0);
-            if (t.nk > 1) load(1, ra1, rb1);
-            for (int kb = 0; kb < t.nk; kb += 2) {
-                store(ra0, rb0);
-                if (kb + 2 < t.nk) load(kb + 2, ra0, rb0);
-                if (kb + 1 < t.nk) {
-                    store(ra1, rb1);
-                    if (kb + 3 < t.nk) load(kb + 3, ra1, rb1);
-                }
             }
             if (MODE == SGEMM_WGRAD) {
                 if (do_bias) {           // tile-uniform across the producer warps
@@ -490,6 +467,52 @@ bool tc_gemm_supported(SgemmMode mode, const SgemmArgs &a) {
     return true;
 }
 
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (fn == nullptr) {
+        void *sym = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(sym);
+    }
+    return fn;
+}
+
+// K-major operand [rows, K] (row stride ld floats): 2-D map {K, rows}, box 32 x 128, SWIZZLE_128B.
+// MN-major operand [K, cols]: 3-D map {32, K, cols/32}, box 32 x 32 x 4 -> smem [chunk][k][32 floats],
+// SWIZZLE_128B_ATOM_32B (the TMA name of UMMA's SWIZZLE_128B_BASE32B).
+int make_map(CUtensorMap *tm, const float *base, bool mn_major, int64_t rows_or_cols, int64_t K, int64_t ld) {
+    EncodeTiledFn fn = encode_fn();
+    if (fn == nullptr) { set_error("cuTensorMapEncodeTiled entry point not available"); return OCPPO_ECUDA; }
+    CUresult r;
+    if (!mn_major) {
+        const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows_or_cols};
+        const cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+        const cuuint32_t box[2] = {32, 128}, estr[2] = {1, 1};
+        r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    } else {
+        const cuuint64_t dims[3] = {32, (cuuint64_t)K, (cuuint64_t)(rows_or_cols / 32)};
+        const cuuint64_t strides[2] = {(cuuint64_t)ld * 4, 128};
+        const cuuint32_t box[3] = {32, 32, 4}, estr[3] = {1, 1, 1};
+        r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float *>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    }
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d)", (int)r); return OCPPO_ECUDA; }
+    return OCPPO_OK;
+}
+
+}  // namespace
+
 int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
     static const int dbg = getenv("OCPPO_TC_DBG") ? atoi(getenv("OCPPO_TC_DBG")) : 0;   // bring-up knob only
     SgemmArgs a = a_in;
@@ -510,10 +533,13 @@ int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
         OCPPO_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<SGEMM_WGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
     }
     const int grid = 2 * (ntiles < sms / 2 ? ntiles : sms / 2);     // CTA pairs
+    CUtensorMap tmA, tmB;
+    OCPPO_TRY(make_map(&tmA, a.A, mode == SGEMM_WGRAD, a.M, a.K, a.lda));
+    OCPPO_TRY(make_map(&tmB, a.B, mode != SGEMM_FWD, a.N, a.K, a.ldb));
     ProfScope ps(mode == SGEMM_FWD ? KC_SGEMM_FWD : (mode == SGEMM_DGRAD ? KC_SGEMM_DGRAD : KC_SGEMM_WGRAD), 1, stream);
-    if (mode == SGEMM_FWD) tc_gemm_kernel<SGEMM_FWD><<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles);
-    else if (mode == SGEMM_DGRAD) tc_gemm_kernel<SGEMM_DGRAD><<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles);
-    else tc_gemm_kernel<SGEMM_WGRAD><<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles);
+    if (mode == SGEMM_FWD) tc_gemm_kernel<SGEMM_FWD><<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles, tmA, tmB);
+    else if (mode == SGEMM_DGRAD) tc_gemm_kernel<SGEMM_DGRAD><<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles, tmA, tmB);
+    else tc_gemm_kernel<SGEMM_WGRAD><<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles, tmA, tmB);
     OCPPO_LAUNCH_CHECK("tc_gemm_kernel");
     return OCPPO_OK;
 }
