@@ -60,12 +60,15 @@ __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-// arrive (release at cluster scope) on the barrier at the same smem offset in CTA `cta` of the pair
+// arrive on the barrier at the same smem offset in CTA `cta` of the pair.  Plain (default-semantics) arrive
+// and try_wait, as CUTLASS's ClusterBarrier uses for its transform -> 2-SM MMA pipelines: the explicit
+// .release.cluster / .acquire.cluster forms compile to MEMBAR.ALL.GPU + ERRBAR per arrive and a CCTL.IVALL
+// per poll, which ncu showed as 35% of all stall samples.  Writers fence.proxy.async before arriving.
 __device__ __forceinline__ void mbar_arrive_on(uint32_t bar, uint32_t cta) {
     asm volatile(
         "{\n\t.reg .b32 ra;\n\t"
         "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
-        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}"
+        "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}"
         ::"r"(bar), "r"(cta)
         : "memory");
 }
@@ -75,7 +78,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     while (true) {
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
             "selp.u32 %0, 1, 0, p;\n\t}"
             : "=r"(done)
             : "r"(bar), "r"(parity)
@@ -133,30 +136,37 @@ __device__ __forceinline__ float lo_of(float x) {
 __device__ __forceinline__ float4 lo4(const float4 &v) {
     return make_float4(lo_of(v.x), lo_of(v.y), lo_of(v.z), lo_of(v.w));
 }
+// offsets of the 4 chunks thread p owns in a 16 KB operand tile
 // K-major tile of 128 rows x 32 floats (SWIZZLE_128B): 8 threads per row, 32 rows per pass.
-__device__ __forceinline__ void conv_kmajor(const uint8_t *hi, uint8_t *lo, int p) {
-    const int rr = p >> 3, c = p & 7;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        const int row = q * 32 + rr;
-        const int off = row * 128 + ((c ^ (row & 7)) << 4);
-        const float4 v = *reinterpret_cast<const float4 *>(hi + off);
-        *reinterpret_cast<float4 *>(lo + off) = lo4(v);
-    }
+__device__ __forceinline__ int off_kmajor(int p, int q) {
+    const int row = q * 32 + (p >> 3), c = p & 7;
+    return row * 128 + ((c ^ (row & 7)) << 4);
 }
 // MN-major tile of 32 k-rows x 128 floats (4 chunks of [32 k][32 floats], SWIZZLE_128B_BASE32B).  Thread p
-// owns the 4 columns (p % 32) * 4.. in k-rows p / 32 + 8 i; `colsum` accumulates them (WGRAD bias gradient).
-template <bool SUM>
-__device__ __forceinline__ void conv_mnmajor(const uint8_t *hi, uint8_t *lo, int p, float4 &colsum) {
-    const int q = p & 31, kr = p >> 5;
-    const int mb = q >> 3, c = q & 7;
+// owns the 4 columns (p % 32) * 4.. in k-rows p / 32 + 8 q (so its values sum into one float4 of column sums).
+__device__ __forceinline__ int off_mnmajor(int p, int q) {
+    const int g = p & 31, k = q * 8 + (p >> 5);
+    const int mb = g >> 3, c = g & 7;
+    return mb * 4096 + k * 128 + ((((c >> 1) ^ (k & 3)) << 5) | ((c & 1) << 4));
+}
+// One stage: read this thread's 8 raw chunks (A and B) first, then derive and store the lo chunks.
+template <bool A_MN, bool B_MN, bool SUM>
+__device__ __forceinline__ void convert_stage(const uint8_t *a_hi, uint8_t *a_lo, const uint8_t *b_hi, uint8_t *b_lo,
+                                              int p, float4 &colsum) {
+    int oa[4], ob[4];
+    float4 va[4], vb[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int k = i * 8 + kr;
-        const int off = mb * 4096 + k * 128 + ((((c >> 1) ^ (k & 3)) << 5) | ((c & 1) << 4));
-        const float4 v = *reinterpret_cast<const float4 *>(hi + off);
-        if (SUM) { colsum.x += v.x; colsum.y += v.y; colsum.z += v.z; colsum.w += v.w; }
-        *reinterpret_cast<float4 *>(lo + off) = lo4(v);
+    for (int q = 0; q < 4; ++q) {
+        oa[q] = A_MN ? off_mnmajor(p, q) : off_kmajor(p, q);
+        ob[q] = B_MN ? off_mnmajor(p, q) : off_kmajor(p, q);
+        va[q] = *reinterpret_cast<const float4 *>(a_hi + oa[q]);
+        vb[q] = *reinterpret_cast<const float4 *>(b_hi + ob[q]);
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        if (SUM) { colsum.x += va[q].x; colsum.y += va[q].y; colsum.z += va[q].z; colsum.w += va[q].w; }
+        *reinterpret_cast<float4 *>(a_lo + oa[q]) = lo4(va[q]);
+        *reinterpret_cast<float4 *>(b_lo + ob[q]) = lo4(vb[q]);
     }
 }
 
@@ -404,20 +414,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
         for (int tile = cl; tile < ntiles; tile += ncl) {
             const TileCoord t = tile_coord(p, tile, nt_n, nt_m);
             const bool do_bias = (MODE == SGEMM_WGRAD) && t.n0 == 0 && p.bias_part != nullptr;
-            float4 bsum = make_float4(0.f, 0.f, 0.f, 0.f), unused = bsum;
+            float4 bsum = make_float4(0.f, 0.f, 0.f, 0.f);
             for (int kb = 0; kb < t.nk; ++kb) {
                 const int s = stage;
                 mbar_wait(bar_tma + 8 * s, (uint32_t)sphase);           // raw tile landed (TMA complete_tx)
                 uint8_t *st = smem + s * kStageBytes;
                 uint8_t *a_hi = st, *a_lo = st + kStageBytesA, *b_hi = st + 2 * kStageBytesA, *b_lo = b_hi + kStageBytesB;
-                if (A_MN) {
-                    if (do_bias) conv_mnmajor<true>(a_hi, a_lo, pt, bsum);
-                    else conv_mnmajor<false>(a_hi, a_lo, pt, unused);
-                } else {
-                    conv_kmajor(a_hi, a_lo, pt);
-                }
-                if (B_MN) conv_mnmajor<false>(b_hi, b_lo, pt, unused);
-                else conv_kmajor(b_hi, b_lo, pt);
+                if (A_MN && do_bias) convert_stage<A_MN, B_MN, true>(a_hi, a_lo, b_hi, b_lo, pt, bsum);
+                else convert_stage<A_MN, B_MN, false>(a_hi, a_lo, b_hi, b_lo, pt, bsum);
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
                 if (pwarp_lane0) mbar_arrive_on(bar_full + 8 * s, 0);      // the leader CTA's barrier
