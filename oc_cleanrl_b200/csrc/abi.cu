@@ -133,6 +133,16 @@ static int64_t carve(ocppo_handle *h, void *base, int64_t R, int training, bool 
         t->mb_val = cv.take<float>(R);
         t->splitk = cv.take<float>((int64_t)kSplitMax * max_w);
         t->splitk_bias = cv.take<float>((int64_t)kSplitMax * max_out);
+        {   // slab partials of the skinny weight-gradient kernels (first trunk layer, heads)
+            const Layer &L0 = h->layers[0];
+            const int64_t g0 = (int64_t)h->sm_count * 4, gh = g0;     // upper bound of the slab count
+            int64_t need = gh * ((int64_t)h->hidden * 33 + 32);
+            if (L0.in_dim <= 32) {
+                const int64_t n0 = g0 * (int64_t)L0.out_dim * 33;
+                if (n0 > need) need = n0;
+            }
+            t->skinny = cv.take<float>(need);
+        }
         t->loss_part = cv.take<double>((int64_t)kLossBlocksMax * 8);
         t->adv_part = cv.take<double>((int64_t)kLossBlocksMax * 2);
         t->adv_stat = cv.take<float>(8);
@@ -204,6 +214,14 @@ static void pick_split(const ocppo_handle *h, int M, int N, int64_t K, int *spli
 // dW[out,in] (+)= dY[rows,out]^T X[rows,in];  db[out] (+)= colsum(dY)
 static int wgrad(ocppo_handle *h, const float *dY, int out, const float *X, int in, int64_t rows, float *dW,
                  int64_t w_count, float *db, int64_t b_count, int accumulate, cudaStream_t s) {
+    if (in <= 32) {          // skinny contraction (first trunk layer): HBM-bound dedicated kernel
+        int G = 0, NS = 0;
+        float *part = h->skinny, *wsum = h->skinny + (int64_t)h->sm_count * 4 * out * 32;
+        OCPPO_TRY(launch_skinny_wgrad(dY, out, out, X, in, in, rows, h->sm_count, part, wsum, nullptr, &G, &NS, s));
+        OCPPO_TRY(launch_skinny_reduce(part, G, out, NS, 0, in, dW, 1, in, accumulate, s));
+        OCPPO_TRY(launch_skinny_reduce(wsum, G, out, 1, 0, 1, db, 1, 1, accumulate, s));
+        return OCPPO_OK;
+    }
     SgemmArgs a{};
     a.A = dY; a.lda = out;
     a.B = X; a.ldb = in;
@@ -490,6 +508,15 @@ int ocppo_minibatch_fwd_bwd(ocppo_handle *h, const float *b_obs, const int64_t *
         used += blocks;
         const int acc = ci > 0;
         // heads: d[Wa;Wc] = gz^T hidden, d[ba;bc] = colsum(gz)
+        if (A + 1 <= 32) {
+            int G = 0, NS = 0;
+            float *part = h->skinny, *ssum = h->skinny + (int64_t)h->sm_count * 4 * H * 32;
+            OCPPO_TRY(launch_skinny_wgrad(a.hidden, H, H, h->gz, AP, A + 1, rows, h->sm_count, part, nullptr, ssum, &G, &NS, s));
+            OCPPO_TRY(launch_skinny_reduce(part, G, H, NS, 0, A, h->grads + h->actor.w_off, H, 1, acc, s));
+            OCPPO_TRY(launch_skinny_reduce(part, G, H, NS, A, A + 1, h->grads + h->critic.w_off, H, 1, acc, s));
+            OCPPO_TRY(launch_skinny_reduce(ssum, G, 1, NS, 0, A, h->grads + h->actor.b_off, 1, 0, acc, s));
+            OCPPO_TRY(launch_skinny_reduce(ssum, G, 1, NS, A, A + 1, h->grads + h->critic.b_off, 1, 0, acc, s));
+        } else
         {
             SgemmArgs g{};
             g.A = h->gz; g.lda = AP;

@@ -99,6 +99,7 @@ struct ocppo_handle {
     float *mb_logp, *mb_adv, *mb_ret, *mb_val;
     float *splitk;                      // [kSplitMax, max(out*in)]
     float *splitk_bias;                 // [kSplitMax, max(out)]
+    float *skinny;                      // slab partials of the skinny wgrad kernels
     double *loss_part;                  // [kLossBlocksMax, 8]
     double *adv_part;                   // [kLossBlocksMax, 2]
     float *adv_stat;                    // mean, std
@@ -166,6 +167,13 @@ int launch_loss_finalize(const double *part, int n_part, int64_t mb, float ent_c
                          cudaStream_t stream);
 int launch_splitk_reduce(const float *part, int splits, int64_t stride, int64_t count, float *out, int accumulate,
                          int sm_count, cudaStream_t stream);
+int skinny_slabs(int64_t rows, int sm_count, int64_t *rows_per_cta);
+static inline int64_t skinny_slabs_max(int64_t rows, int sm_count) { int64_t per; return skinny_slabs(rows, sm_count, &per); }
+int launch_skinny_wgrad(const float *wide, int64_t ldw, int nw, const float *skinny, int64_t lds, int ns, int64_t rows,
+                        int sm_count, float *part, float *wsum_part, float *ssum_part, int *G_out, int *NS_out,
+                        cudaStream_t stream);
+int launch_skinny_reduce(const float *part, int G, int nw, int NS, int i0, int i1, float *out, int64_t si, int64_t sj,
+                         int accumulate, cudaStream_t stream);
 int launch_relu_mask(const float *g, const float *act, int64_t n, float *out, int sm_count, cudaStream_t stream);
 int measure_fma_peak(double *tflops, cudaStream_t stream);
 int launch_clip_adam(ocppo_handle *h, float inv_world, float max_norm, double lr, double beta1, double beta2,

@@ -510,20 +510,28 @@ def test_full_size_minibatch_properties(dev, gemm_engine):
         assert np.isfinite(grads[-1]).all() and np.isfinite(learner._stats[0].cpu().numpy()).all()
     assert np.array_equal(grads[0], grads[2])
     assert rel_err(grads[1], grads[0]) < (5e-5 if gemm_engine == "tc" else 1e-5)
-    # the FULL 131,072-sample minibatch against an fp64 run of the reference restatement (torch, on the
-    # device only because the CPU would take minutes; same operator sequence as ppo_atari_oc.py:566-608)
-    oracle64 = ref_ppo.make_agent(F, D, A, enc, dec, seed=42, dtype=torch.float64).to(dev)
-    gpu64 = tuple(t.double() if t.is_floating_point() else t for t in gpu)
-    loss64, st64 = ref_ppo.ref_minibatch_loss(oracle64, *gpu64, perm[:131072], ref_ppo.PPOArgs())
-    loss64.backward()
-    g64 = torch.cat([q.grad.reshape(-1) for q in oracle64.parameters()]).cpu().numpy()
-    del oracle64, gpu64, loss64
-    torch.cuda.empty_cache()
+    # the FULL 131,072-sample minibatch against the reference restatement run by torch on the device (the CPU
+    # would take minutes; same operator sequence as ppo_atari_oc.py:566-608): in fp32 -- what the reference
+    # itself computes on a GPU, cuBLAS SGEMM with TF32 off -- held to the 1e-4 bar per tensor, and in fp64,
+    # where our distance may exceed the bar only by the fp32 reference's own distance from fp64.
+    assert not torch.backends.cuda.matmul.allow_tf32
+    def torch_grads(dtype):
+        o = ref_ppo.make_agent(F, D, A, enc, dec, seed=42, dtype=dtype).to(dev)
+        args_t = tuple(t.to(dtype) if t.is_floating_point() else t for t in gpu)
+        l, _ = ref_ppo.ref_minibatch_loss(o, *args_t, perm[:131072], ref_ppo.PPOArgs())
+        l.backward()
+        g = torch.cat([q.grad.reshape(-1) for q in o.parameters()]).double().cpu().numpy()
+        del o, args_t, l
+        torch.cuda.empty_cache()
+        return g
+    g32, g64 = torch_grads(torch.float32), torch_grads(torch.float64)
     off = 0
     for i, q in enumerate(agent.parameters()):
         k = q.numel()
-        e = rel_err(grads[0][off:off + k], g64[off:off + k])
-        assert e < REL_TOL, f"tensor {i}: rel err {e:.3e} vs fp64 at full minibatch size"
+        ours, r32, r64 = grads[0][off:off + k], g32[off:off + k], g64[off:off + k]
+        e32, e64, ref_e = rel_err(ours, r32), rel_err(ours, r64), rel_err(r32, r64)
+        assert e32 < REL_TOL, f"tensor {i}: {e32:.3e} vs torch fp32 (vs fp64 {e64:.3e}; torch fp32 vs fp64 {ref_e:.3e})"
+        assert e64 < REL_TOL + ref_e, f"tensor {i}: {e64:.3e} vs fp64 (torch fp32 vs fp64 {ref_e:.3e})"
         off += k
     loss, _ = ref_ppo.ref_minibatch_loss(oracle, *cpu, perm[:2048].cpu().numpy(), ref_ppo.PPOArgs())
     loss.backward()

@@ -219,6 +219,21 @@ int main() {
         }
     printf("Q1 raw fp32 operands into kind::tf32: max|D - trunc model| = %.3e, max|D - rna model| = %.3e, max|D - fp32 exact| = %.3e\n",
            e_tr, e_rn, e_full);
+    // ---- Q4: how does the TMEM accumulator round when a small product is added to a large one?
+    {
+        std::vector<float> A2(TM * TK, 0.f), B2(TN * TK, 0.f), D2(TM * TN);
+        for (int m = 0; m < TM; ++m) { A2[m * TK + 0] = 4096.f; A2[m * TK + 8] = 1.5f; }
+        const float big[4] = {4096.f, -4096.f, -4096.f, 4096.f}, small[4] = {1.f, -1.f, 1.f, -1.f};
+        for (int n = 0; n < 4; ++n) { B2[n * TK + 0] = big[n]; B2[n * TK + 8] = small[n]; }
+        CK(cudaMemcpy(dA, A2.data(), A2.size() * 4, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(dB, B2.data(), B2.size() * 4, cudaMemcpyHostToDevice));
+        q1_kernel<<<1, 128, smem1>>>(dA, dB, dD);
+        CK(cudaDeviceSynchronize());
+        CK(cudaMemcpy(D2.data(), dD, D2.size() * 4, cudaMemcpyDeviceToHost));
+        printf("Q4 accumulator rounding (exact / got): %.1f / %.1f   %.1f / %.1f   %.1f / %.1f   %.1f / %.1f\n",
+               16777217.5, D2[0], -16777217.5, D2[1], -16777214.5, D2[2], 16777214.5, D2[3]);
+        printf("   (RN: 16777218 -16777218 -16777214 16777214; toward zero: 16777216 -16777216 -16777214 16777214; floor: 16777216 -16777218 -16777215 16777214)\n");
+    }
     // ---- Q2/Q3
     long long *dout, hout[8];
     CK(cudaMalloc(&dout, 64));
@@ -227,7 +242,7 @@ int main() {
     int dev_sms = 0;
     CK(cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, 0));
     const int niter = 2000;
-    const int cfgs[][2] = {{1, 3}, {1, 1}, {2, 3}, {4, 3}, {6, 3}, {3, 3}, {5, 3}, {7, 3}};
+    const int cfgs[][2] = {{1, 3}, {7, 3}};
     for (auto &c : cfgs) {
         for (int grid : {1, dev_sms}) {
             CK(cudaMemset(dout, 0, 64));
