@@ -42,7 +42,7 @@ def parse():
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--gae-sweep", default="4096,16384,65536")
-    p.add_argument("--gemm", default="fma", choices=["fma", "tc"],
+    p.add_argument("--gemm", default="tc", choices=["fma", "tc", "tc-fast"],
                    help="trunk GEMM engine: fp32 CUDA-core FMA or tcgen05 3xTF32 (fp32-grade)")
     return p.parse_args()
 
@@ -264,7 +264,7 @@ def run_b200(a):
     torch.cuda.set_device(dev)
     ocd.init_process_group(world, "nccl")
     lib = _abi.lib()
-    assert lib.ocppo_set_gemm_mode(1 if a.gemm == "tc" else 0) == 0
+    assert lib.ocppo_set_gemm_mode({"fma": 0, "tc": 1, "tc-fast": 2}[a.gemm]) == 0
     D, A = GAME_SHAPES[a.game]
     T, N = a.num_steps, a.num_envs
     pk = peaks()

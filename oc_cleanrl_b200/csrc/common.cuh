@@ -124,13 +124,15 @@ struct SgemmArgs {
     int64_t k_per_split;
     int splits;
     int dbg;                  // tc_gemm bring-up variant (0 in production)
+    int single_acc;           // tc_gemm: 1 = one TMEM accumulator per tile (faster, ~3x the rounding error)
 };
 
 int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);       // dispatches FMA / tensor
 int fma_gemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);    // sgemm.cu, fp32 CUDA cores
 bool tc_gemm_supported(SgemmMode mode, const SgemmArgs &a);                      // tc_gemm.cu, tcgen05 3xTF32
 int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);
-// 0: fp32 FMA kernels only; 1: tcgen05 3xTF32 wherever the shape fits (fp32-grade accuracy)
+// 0: fp32 FMA kernels only; 1: tcgen05 3xTF32 wherever the shape fits (fp32-grade accuracy; main and
+// correction products in separate TMEM accumulators); 2: same with a single, double-buffered accumulator
 extern int g_gemm_mode;
 
 int launch_gae(const float *rewards, const float *values, const float *dones,

@@ -8,6 +8,7 @@
 // Fixed accumulation order => run-to-run deterministic (the reference sets
 // torch.use_deterministic_algorithms(True), ppo_atari_oc.py:209).
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace ocppo {
 
@@ -192,7 +193,12 @@ int dispatch(const SgemmArgs &a, bool av, bool bv, dim3 grid, cudaStream_t s) {
 int g_gemm_mode = 0;
 
 int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream) {
-    if (g_gemm_mode == 1 && tc_gemm_supported(mode, a)) return tc_gemm_launch(mode, a, stream);
+    static const int ops_mask = getenv("OCPPO_TC_OPS") ? atoi(getenv("OCPPO_TC_OPS")) : 7;   // bring-up: bit per op
+    if (g_gemm_mode >= 1 && ((ops_mask >> (int)mode) & 1) && tc_gemm_supported(mode, a)) {
+        SgemmArgs b = a;
+        b.single_acc = g_gemm_mode == 2;
+        return tc_gemm_launch(mode, b, stream);
+    }
     return fma_gemm_launch(mode, a, stream);
 }
 

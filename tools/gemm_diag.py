@@ -22,11 +22,18 @@ def run(op, engine, M, N, K, splits=1, kind="randn", seed=0):
     def mk(*shape):
         if kind == "int":
             return torch.randint(-4, 5, shape, device=dev, generator=g).float()
+        if kind == "tiny":
+            return torch.randn(*shape, device=dev, generator=g) * 1e-7
+        if kind == "relu":          # post-ReLU-like: half exact zeros, large positive values
+            return torch.relu(torch.randn(*shape, device=dev, generator=g)) * 50.0
         return torch.randn(*shape, device=dev, generator=g)
     bias = mask = bias_part = None
     kp = -(-K // splits)
     kp = (kp + 31) // 32 * 32
     splits = -(-K // kp)
+    kindB = None
+    if "+" in kind:
+        kind, kindB = kind.split("+")
     if op == 0:
         A, B = mk(M, K), mk(N, K)
         bias = mk(N)
@@ -38,7 +45,10 @@ def run(op, engine, M, N, K, splits=1, kind="randn", seed=0):
         ref = (A.double() @ B.double()) * (mask > 0)
         C_ = torch.full((M, N), float("nan"), device=dev)
     else:
-        A, B = mk(K, M), mk(K, N)
+        A = mk(K, M)
+        if kindB:
+            kind = kindB
+        B = mk(K, N)
         ref = A.double().t() @ B.double()
         C_ = torch.full((splits, M, N), float("nan"), device=dev)
         bias_part = torch.full((splits, M), float("nan"), device=dev)
@@ -69,6 +79,14 @@ def run(op, engine, M, N, K, splits=1, kind="randn", seed=0):
     return msg
 
 
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "probe":
+    for e in (0, 1, 2):
+        for (op, M, N, K, S, kind) in [(2, 1024, 512, 8192, 9, "tiny+relu"), (2, 1024, 512, 4096, 9, "tiny+relu"),
+                                       (2, 512, 1024, 8192, 9, "tiny+relu"), (2, 512, 256, 8192, 32, "tiny+relu"),
+                                       (2, 512, 2048, 2048, 4, "tiny+relu"), (1, 8192, 1024, 512, 1, "tiny"),
+                                       (1, 2048, 2048, 512, 1, "tiny"), (1, 8192, 512, 1024, 1, "tiny")]:
+            print(run(op, e, M, N, K, S, kind)[:150], flush=True)
+    sys.exit(0)
 if __name__ == "__main__":
     engines = [int(x) for x in sys.argv[1:]] or [0, 1]
     cases = [
