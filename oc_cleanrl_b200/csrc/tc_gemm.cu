@@ -239,6 +239,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
     const int ncl = gridDim.x >> 1, cl = blockIdx.x >> 1;    // clusters in the grid, this cluster
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    // The TMEM accumulator adds with round-toward-zero (tools/tc_probe.cu Q4): every MMA chained into it costs
+    // about half an ulp of bias, and two of the three passes only add tiny correction products.  By default
+    // those go to a second accumulator (columns 256..511) that the epilogue adds in fp32 round-to-nearest:
+    // 3x less rounding error, at the price of the tile-to-tile accumulator double buffering.
+    const bool split_acc = !p.single_acc;
 
     if (tid == 0) {
         for (int s = 0; s < kNumStages; ++s) {
@@ -270,9 +275,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
         for (int tile = cl; tile < ntiles; tile += ncl) {
           const TileCoord t = tile_coord(p, tile, nt_n, nt_m);
           for (int kb0 = 0; kb0 < t.nk; kb0 += kSegStages, ++ai) {
-            const int acc = ai & 1;
+            const int nbuf = (split_acc || (p.dbg & 4)) ? 1 : 2, acc = ai % nbuf;
             const bool rmw = (MODE == SGEMM_WGRAD) && kb0 > 0;     // later k-segments add onto the first
-            mbar_wait(bar_tfull + 8 * acc, (uint32_t)((ai >> 1) & 1));
+            mbar_wait(bar_tfull + 8 * acc, (uint32_t)((ai / nbuf) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             float *Cb = p.C;
             if (MODE == SGEMM_WGRAD) Cb += (int64_t)t.split * p.M * p.N;
@@ -298,6 +303,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                 uint32_t v[32];
                 const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(acc * TN + cc * 32);
                 OCPPO_TMEM_LD32(v, taddr);
+                if (split_acc) {               // split accumulators: main in columns [0,256), corrections in [256,512)
+                    uint32_t w[32];
+                    OCPPO_TMEM_LD32(w, taddr + TN);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(w[j]));
+                }
                 if (MODE == SGEMM_DGRAD) {
 #pragma unroll
                     for (int i = 0; i < 8; ++i) mk[i] = mk_next[i];
@@ -354,8 +366,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
             for (int tile = cl; tile < ntiles; tile += ncl) {
               const TileCoord t = tile_coord(p, tile, nt_n, nt_m);
               for (int kb0 = 0; kb0 < t.nk; kb0 += kSegStages, ++ai) {
-                const int acc = ai & 1;
-                mbar_wait(bar_tempty + 8 * acc, (uint32_t)(((ai >> 1) & 1) ^ 1));
+                const int nbuf = (split_acc || (p.dbg & 4)) ? 1 : 2, acc = ai % nbuf;
+                mbar_wait(bar_tempty + 8 * acc, (uint32_t)(((ai / nbuf) & 1) ^ 1));
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t d_tmem = tmem_base + (uint32_t)(acc * TN);
                 const int kb1 = (t.nk - kb0 < kSegStages) ? t.nk : kb0 + kSegStages;
@@ -372,9 +384,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
 #pragma unroll
                     for (int ks = 0; ks < TK / 8; ++ks) {
                         const uint32_t acc0 = (kb > kb0 || ks > 0) ? 1u : 0u;
-                        umma_tf32(d_tmem, da_lo + ks * a_step, db_hi + ks * b_step, idesc, acc0);
-                        umma_tf32(d_tmem, da_hi + ks * a_step, db_lo + ks * b_step, idesc, 1u);
-                        umma_tf32(d_tmem, da_hi + ks * a_step, db_hi + ks * b_step, idesc, 1u);
+                        if (split_acc) {
+                            umma_tf32(d_tmem + TN, da_lo + ks * a_step, db_hi + ks * b_step, idesc, acc0);
+                            umma_tf32(d_tmem + TN, da_hi + ks * a_step, db_lo + ks * b_step, idesc, 1u);
+                            umma_tf32(d_tmem, da_hi + ks * a_step, db_hi + ks * b_step, idesc, acc0);
+                        } else {
+                            umma_tf32(d_tmem, da_lo + ks * a_step, db_hi + ks * b_step, idesc, acc0);
+                            umma_tf32(d_tmem, da_hi + ks * a_step, db_lo + ks * b_step, idesc, 1u);
+                            umma_tf32(d_tmem, da_hi + ks * a_step, db_hi + ks * b_step, idesc, 1u);
+                        }
                     }
                     umma_commit_pair(bar_empty + 8 * s);     // stage free (in both CTAs) once these MMAs have read it
                 }
