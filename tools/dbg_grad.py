@@ -41,3 +41,10 @@ for mode in (1, 2):
         got = [agent._grad_view(i).reshape(-1).double().cpu().numpy() for i, _ in enumerate(agent.parameters())]
         errs = [float(np.abs(g - w).max() / np.abs(w).max()) for g, w in zip(got, want)]
         print(f"mode {mode} rep {rep}: " + " ".join(f"{e:.1e}" for e in errs), flush=True)
+        shapes = [tuple(p.shape) for p in agent.parameters()]
+        for ti in (5, 4, 9):
+            d = np.abs(got[ti] - want[ti]) / np.abs(want[ti]).max()
+            top = np.argsort(-d)[:6]
+            cols = shapes[ti][1] if len(shapes[ti]) == 2 else 1
+            print(f"   tensor {ti} {shapes[ti]}: top errors " + ", ".join(f"({t // cols},{t % cols}):{d[t]:.1e}" for t in top)
+                  + f"  | entries > 1e-5: {(d > 1e-5).sum()} of {d.size}, median {np.median(d):.1e}")
