@@ -27,6 +27,9 @@ import torch  # noqa: E402
 
 ENC, DEC = (256, 512, 1024, 512), (512,)
 FRAMES = 4
+# dram__bytes_read.sum + dram__bytes_write.sum of one tc_gemm_kernel<FWD> launch (M=131072, N=512, K=1024) from the
+# ncu --set full capture summarised in profiles/ (algorithmic bytes of that launch: 807 MB)
+TRAFFIC_BYTES_PER_LAUNCH = None
 
 
 def parse():
@@ -211,7 +214,7 @@ def workload_config(a, world):
     return {"workload": f"synthetic {a.game}-shaped OCAtari obj rollouts, {a.num_envs} envs x {a.num_steps} steps per GPU, "
                         f"GAE + 4-epoch x 4-minibatch PPO update (BASELINE configs[1])",
             "num_envs_per_gpu": a.num_envs, "num_steps": a.num_steps, "update_epochs": 4, "num_minibatches": 4,
-            "encoder_dims": list(ENC), "decoder_dims": list(DEC), "world_size": world,
+            "encoder_dims": list(ENC), "decoder_dims": list(DEC), "world_size": world, "gemm_engine": a.gemm,
             "parallelism": f"env-sharded dp{world}, one flat-gradient NCCL allreduce per minibatch",
             "l2": "working set (>=1.3 GB activations per chunk, 50 MB obs) exceeds the 126 MB L2; no flush needed; "
                   "the isolated GAE timing rotates through >L2 worth of buffers"}
@@ -362,14 +365,25 @@ def run_b200(a):
     gemm_tflops = gemm_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
     fma = C_double()
     lib.ocppo_measure_fma_peak(fma, None)
+    tc = a.gemm != "fma"
     roofline = {"bound": "tensor", "achieved": gemm_tflops, "peak": pk["bf16_sustained"], "unit": "TFLOP/s",
-                "frac": gemm_tflops / pk["bf16_sustained"], "traffic": None,
-                "kernel": "sgemm_kernel (fp32 CUDA-core FMA; fwd+dgrad+wgrad launches of the trunk)",
+                "frac": gemm_tflops / pk["bf16_sustained"], "traffic": TRAFFIC_BYTES_PER_LAUNCH if tc else None,
+                "kernel": ("tc_gemm_kernel<FWD|DGRAD|WGRAD> (tcgen05.mma cta_group::2 kind::tf32, 3-pass split for fp32-grade "
+                           "accuracy, TMA-fed, TMEM accumulators) + the skinny first-layer/head kernels" if tc else
+                           "sgemm_kernel (fp32 CUDA-core FMA; fwd+dgrad+wgrad launches of the trunk)"),
                 "peak_source": pk["source"] + ", bf16 dense sustained",
                 "share_of_step": gemm_ms / ms_per_step,
                 "launches_per_step": (prof_n["sgemm_fwd"] + prof_n["sgemm_dgrad"] + prof_n["sgemm_wgrad"]) / a.steps,
                 "flops_per_step": gemm_flops,
-                "note": "fp32-exact FMA path: the tensor roofline is the ceiling a tcgen05 (3xTF32) trunk would be held to"}
+                "achieved_is": "ALGORITHMIC fp32-equivalent FLOPs (2*M*N*K per GEMM, SURVEY 8d) / CUDA-event time of the GEMM launches"}
+    if tc:
+        # every algorithmic MAC is issued three times at TF32 rate (= half the bf16 rate): 6 bf16-equivalent MACs
+        roofline["tensor_pipe"] = {"issued_tf32_tflops": 3.0 * gemm_tflops, "tf32_peak_est": pk["bf16_sustained"] / 2.0,
+                                   "frac_of_tf32_peak_est": 6.0 * gemm_tflops / pk["bf16_sustained"],
+                                   "note": "fp32-grade accuracy costs 3 TF32 passes; TF32 runs at half the bf16 rate, so "
+                                           "frac = achieved/peak is bounded by 1/6 = 0.167 at full tensor-pipe occupancy"}
+    else:
+        roofline["note"] = "fp32-exact FMA path: the tensor roofline is the ceiling the tcgen05 (3xTF32) trunk is held to"
     roofline_fma = {"bound": "fma", "achieved": gemm_tflops, "peak": fma.value, "unit": "TFLOP/s",
                     "frac": gemm_tflops / fma.value if fma.value else None,
                     "peak_source": "ocppo_measure_fma_peak micro-benchmark in this run"}

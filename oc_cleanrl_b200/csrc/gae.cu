@@ -72,8 +72,12 @@ gae_scan_kernel(const float *__restrict__ rewards, const float *__restrict__ val
         cp_async_commit();
     };
 
+    // A rollout of T <= kStages * kRows steps (the script's default 128) fits the ring entirely: put the whole
+    // slab in flight at once, so the kernel pays one DRAM round trip instead of two.
+    const bool all_upfront = n_chunks <= kStages;
 #pragma unroll
     for (int s = 0; s < kStages - 1; ++s) issue(s);
+    if (all_upfront) issue(kStages - 1);
 
     const int lane = tid & 31;
     const bool scanner = tid < 32;
@@ -86,7 +90,8 @@ gae_scan_kernel(const float *__restrict__ rewards, const float *__restrict__ val
     }
 
     for (int64_t chunk = 0; chunk < n_chunks; ++chunk) {
-        issue(chunk + kStages - 1);
+        if (!all_upfront) issue(chunk + kStages - 1);
+        else cp_async_commit();                   // keep the group count per iteration uniform
         cp_async_wait<kStages - 1>();
         __syncthreads();
         if (scanner) {
