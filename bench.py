@@ -224,7 +224,7 @@ def workload_config(a, world):
 # GPU arm
 # --------------------------------------------------------------------------
 def time_gae_isolated(dev, T, N, iters=200, min_bytes=192 << 20):
-    """Average GAE launch duration with CUDA events on the launch stream, rotating through
+    """Average GAE launch duration with CUDA events around a graph replay of `iters` launches, rotating through
     more than an L2's worth of distinct buffers so no launch finds its inputs in L2."""
     from oc_cleanrl_b200.learner import compute_gae
     per_set = gae_bytes(T, N)
@@ -241,13 +241,21 @@ def time_gae_isolated(dev, T, N, iters=200, min_bytes=192 << 20):
     for i in range(max(3, n_sets)):
         launch(sets[i % n_sets])
     torch.cuda.synchronize(dev)
+    # The launches are replayed from a CUDA graph: a Python+ctypes call costs more host time
+    # than the kernel runs for at N <= 16384, and a host-bound loop would time the host.
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        for i in range(iters):
+            launch(sets[i % n_sets])
+    graph.replay()
+    torch.cuda.synchronize(dev)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for i in range(iters):
-        launch(sets[i % n_sets])
+    graph.replay()
     e1.record()
     torch.cuda.synchronize(dev)
     us = e0.elapsed_time(e1) * 1e3 / iters
+    del graph
     del sets
     return us
 
