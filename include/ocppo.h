@@ -190,6 +190,12 @@ int ocppo_trunk_forward(ocppo_handle *h, const float *obs, int64_t B, float *hid
 int ocppo_trunk_backward(ocppo_handle *h, const float *obs, int64_t B, const float *d_hidden,
                          void *stream);
 
+/* Test hook: post-ReLU activation of trunk layer `layer` (0-based, encoder then decoder layers) as the LAST
+ * forward left it in the workspace -- (B*frames, width) for encoder layers, (B, width) for decoder layers.
+ * The backward pass takes its ReLU masks from exactly these buffers, so a parity test can hand the same
+ * masks to the reference (tests/test_gpu_parity.py: decisions within fp32 rounding of zero). */
+int ocppo_read_activation(const ocppo_handle *h, int32_t layer, int64_t B, float *out, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

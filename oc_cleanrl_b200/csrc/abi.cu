@@ -568,4 +568,16 @@ int ocppo_trunk_backward(ocppo_handle *h, const float *obs, int64_t B, const flo
     return trunk_backward(h, obs, B, 0, 0, s);
 }
 
+int ocppo_read_activation(const ocppo_handle *h, int32_t layer, int64_t B, float *out, void *stream) {
+    OCPPO_TRY(require_ready(h, false));
+    OCPPO_CHECK_ARG(out, "null pointer");
+    OCPPO_CHECK_ARG(layer >= 0 && layer < h->n_layers, "read_activation: layer %d not in [0,%d)", layer, h->n_layers);
+    OCPPO_CHECK_ARG(B >= 1 && B == h->last_forward_rows, "read_activation: B=%lld does not match last forward (%d)",
+                    (long long)B, h->last_forward_rows);
+    const Layer &L = h->layers[layer];
+    OCPPO_CUDA(cudaMemcpyAsync(out, h->act[layer], (size_t)B * L.row_mult * L.out_dim * sizeof(float),
+                               cudaMemcpyDeviceToDevice, as_stream(stream)));
+    return OCPPO_OK;
+}
+
 }  // extern "C"

@@ -241,6 +241,44 @@ def anneal_lr(optimizer, iteration, num_iterations, args: PPOArgs):
     return optimizer.param_groups[0]["lr"]
 
 
+class relu_decisions:
+    """Context manager over the trunk's ReLUs (test infrastructure).  Always records, per trunk layer, the
+    Linear input ``x``, the pre-activation ``z`` and the ReLU decision ``z > 0``.  With ``masks`` (one bool
+    tensor per trunk layer, broadcastable to ``z``) the ReLU output is replaced by ``z * mask``: the
+    reference network evaluated with somebody else's decisions.  A decision is a step function of ``z``; two
+    fp32 evaluations of the same dot product that differ in the last bit can decide a ``z`` at rounding
+    distance from zero differently, and the backward pass then differs by that sample's whole contribution
+    to the unit -- which no tolerance on the GEMM arithmetic can bound.  The GPU parity test therefore hands
+    the reference the decisions of the path under test and checks separately that every decision that
+    differs from the reference's own was within rounding of zero."""
+
+    def __init__(self, agent, masks=None):
+        self.agent, self.masks, self.records, self._hooks = agent, masks, [], []
+
+    def __enter__(self):
+        mods = list(self.agent.network)
+        layer = 0
+        for i, m in enumerate(mods):
+            if isinstance(m, nn.Linear) and i + 1 < len(mods) and isinstance(mods[i + 1], nn.ReLU):
+                rec = {"linear": m}
+                self.records.append(rec)
+                self._hooks.append(m.register_forward_hook(
+                    lambda mod, inp, out, rec=rec: rec.update(x=inp[0].detach(), z=out.detach())))
+                mask = None if self.masks is None else self.masks[layer]
+                def relu_hook(mod, inp, out, rec=rec, mask=mask):
+                    rec["decision"] = inp[0].detach() > 0
+                    if mask is not None:
+                        return inp[0] * mask.reshape(inp[0].shape).to(inp[0].dtype)
+                self._hooks.append(mods[i + 1].register_forward_hook(relu_hook))
+                layer += 1
+        return self
+
+    def __exit__(self, *exc):
+        for h in self._hooks:
+            h.remove()
+        return False
+
+
 def flat_grads(agent):
     return torch.cat([p.grad.reshape(-1) for p in agent.parameters()])
 
