@@ -96,7 +96,7 @@ int ocppo_measure_fma_peak(double *tflops, void *stream);
  * with a 3-pass TF32 split that keeps fp32-grade accuracy (mode 1, used wherever
  * the shape fits the 256x256x32 CTA-pair tile; other shapes stay on FMA).  Mode 2
  * is mode 1 with a single TMEM accumulator per tile: ~13 % faster, ~3x the rounding
- * error (the accumulator rounds toward zero). */
+ * error (the accumulator rounds toward zero).  Process-wide; default 1. */
 int ocppo_set_gemm_mode(int32_t mode);
 int ocppo_get_gemm_mode(void);
 /* One GEMM of the family.  op 0: C[M,N] = relu(A[M,K] B[N,K]^T + bias[N]);

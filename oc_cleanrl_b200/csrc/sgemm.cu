@@ -190,7 +190,7 @@ int dispatch(const SgemmArgs &a, bool av, bool bv, dim3 grid, cudaStream_t s) {
 
 }  // namespace
 
-int g_gemm_mode = 0;
+int g_gemm_mode = 1;   // tcgen05 3xTF32 with split accumulators; see ocppo_set_gemm_mode
 
 int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream) {
     static const int ops_mask = getenv("OCPPO_TC_OPS") ? atoi(getenv("OCPPO_TC_OPS")) : 7;   // bring-up: bit per op

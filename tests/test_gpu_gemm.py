@@ -35,5 +35,5 @@ def test_gemm_mode_switch_roundtrip(built_lib):
     assert built_lib.ocppo_set_gemm_mode(1) == 0 and built_lib.ocppo_get_gemm_mode() == 1
     assert built_lib.ocppo_set_gemm_mode(0) == 0 and built_lib.ocppo_get_gemm_mode() == 0
     assert built_lib.ocppo_set_gemm_mode(2) == 0 and built_lib.ocppo_get_gemm_mode() == 2
-    assert built_lib.ocppo_set_gemm_mode(0) == 0
+    assert built_lib.ocppo_set_gemm_mode(1) == 0
     assert built_lib.ocppo_set_gemm_mode(7) == -1

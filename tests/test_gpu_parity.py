@@ -32,7 +32,7 @@ def gemm_engine(request, built_lib):
     """Runs the test once per trunk GEMM engine: fp32 CUDA-core FMA and tcgen05 3xTF32."""
     assert built_lib.ocppo_set_gemm_mode(1 if request.param == "tc" else 0) == 0
     yield request.param
-    built_lib.ocppo_set_gemm_mode(0)
+    built_lib.ocppo_set_gemm_mode(1)
 
 
 def _stream(dev):
