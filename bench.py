@@ -345,10 +345,11 @@ def run_b200(a):
     if not a.no_e2e:
         h2d_keys = ("obs", "actions", "logprobs", "rewards", "dones", "values", "next_obs", "next_done")
         def step_e2e():
-            perm = make_permutations(T * N, largs.update_epochs)         # host shuffle, as the reference (:561)
             d = {k: host[k].to(dev, non_blocking=True) for k in h2d_keys}
             adv, ret = learner.compute_gae(d["rewards"], d["values"], d["dones"], d["next_obs"], d["next_done"])
-            return learner.update(d["obs"], d["actions"], d["logprobs"], adv, ret, d["values"], permutations=perm)  # D2H inside
+            # update() shuffles on the host as the reference does (:558-561), copies each epoch's order H2D, and
+            # reads the stats back (D2H) before returning
+            return learner.update(d["obs"], d["actions"], d["logprobs"], adv, ret, d["values"])
         step_e2e()
         barrier()
         s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -149,8 +149,69 @@ __global__ void exponential_kernel(float *__restrict__ out, int64_t numel, Philo
 
 namespace {
 
+// Per-sample PPO loss terms from (logit of this lane, value): returns d loss / d logit of this lane and d loss / d value,
+// adds the logged sums into acc[] on lane 0.
+__device__ __forceinline__ void ppo_sample_loss(const LossArgs &p, int64_t i, float z, float v, int lane, float inv_mb,
+                                                float mean, float stdv, float &dz, float &dv, double (&acc)[6]) {
+    const int A = p.A;
+    float ell, pk, Hh;
+    warp_categorical(z, lane, A, ell, pk, Hh);
+    const int a = p.action[i];
+    const float newlogp = __shfl_sync(kFull, ell, a & 31);
+    const float logratio = newlogp - p.logp_old[i];
+    const float ratio = expf(logratio);
+    float advn = p.adv[i];
+    if (p.norm_adv) advn = __fdiv_rn(advn - mean, stdv + 1e-8f);
+    // clipped surrogate (:581-583)
+    const float l1 = -advn * ratio;
+    const float rc = fminf(fmaxf(ratio, p.clip_lo), p.clip_hi);
+    const float l2 = -advn * rc;
+    const float pg = fmaxf(l1, l2);
+    const bool in_range = (ratio >= p.clip_lo) && (ratio <= p.clip_hi);
+    float g_ratio;                       // d pg / d ratio
+    if (l1 > l2) g_ratio = -advn;
+    else if (l2 > l1) g_ratio = in_range ? -advn : 0.f;
+    else g_ratio = 0.5f * (-advn) + (in_range ? 0.5f * (-advn) : 0.f);
+    // value loss (:585-597)
+    const float R = p.ret[i], Vold = p.val[i];
+    const float du = v - R;
+    const float u = du * du;
+    float vterm = u, g_v = du;           // d (0.5*vterm) / d v
+    if (p.clip_vloss) {
+        const float d = v - Vold;
+        const float dc = fminf(fmaxf(d, -p.clip_f), p.clip_f);
+        const float vc = Vold + dc;
+        const float dw = vc - R;
+        const float w = dw * dw;
+        const bool v_in = (d >= -p.clip_f) && (d <= p.clip_f);
+        const float gw = v_in ? dw : 0.f;
+        if (u > w) { vterm = u; g_v = du; }
+        else if (w > u) { vterm = w; g_v = gw; }
+        else { vterm = u; g_v = 0.5f * du + 0.5f * gw; }
+    }
+    // gradients wrt logits / value
+    const float coef_a = g_ratio * ratio * inv_mb;
+    const float coef_e = p.ent_coef * inv_mb;
+    dz = 0.f;
+    if (lane < A) dz = coef_a * ((lane == a ? 1.f : 0.f) - pk) + coef_e * pk * (ell + Hh);
+    dv = p.vf_coef * inv_mb * g_v;
+    if (lane < p.AP) p.gz[i * p.AP + lane] = lane < A ? dz : (lane == A ? dv : 0.f);
+    if (lane == 0) {
+        acc[0] += (double)pg;
+        acc[1] += (double)vterm;
+        acc[2] += (double)Hh;
+        acc[3] += (double)(-logratio);
+        acc[4] += (double)((ratio - 1.0f) - logratio);
+        acc[5] += (fabsf(ratio - 1.0f) > p.clip_f) ? 1.0 : 0.0;
+    }
+}
+
+// HV > 0: H == 128 * HV, the sample's hidden row lives in registers (HV float4 per lane, read once with 16-byte
+// loads, the next sample's row prefetched while this one is processed) and d(hidden) leaves as float4 stores: the
+// kernel then runs at HBM rate (8*H bytes per sample).  HV == 0: any H, scalar loops.
+template <int HV>
 __global__ void __launch_bounds__(kHeadThreads) loss_head_kernel(LossArgs p) {
-    extern __shared__ float sm[];
+    extern __shared__ __align__(16) float sm[];
     const int A = p.A, H = p.H;
     float *sW = sm, *sB = sm + (size_t)(A + 1) * H;
     stage_head_weights(sW, sB, p.Wa, p.ba, p.Wc, p.bc, A, H);
@@ -160,71 +221,84 @@ __global__ void __launch_bounds__(kHeadThreads) loss_head_kernel(LossArgs p) {
     if (p.norm_adv) { mean = p.adv_stat[0]; stdv = p.adv_stat[1]; }
 
     double acc[6] = {0, 0, 0, 0, 0, 0};   // pg, vmax, entropy, -logratio, (ratio-1)-logratio, clipped
-    for (int64_t i = (int64_t)blockIdx.x * kWarpsPerBlock + warp; i < p.rows; i += (int64_t)gridDim.x * kWarpsPerBlock) {
-        const float *h = p.hidden + i * H;
-        float z, v;
-        warp_head_forward(h, sW, sB, A, H, lane, z, v);
-        float ell, pk, Hh;
-        warp_categorical(z, lane, A, ell, pk, Hh);
-        const int a = p.action[i];
-        const float newlogp = __shfl_sync(kFull, ell, a & 31);
-        const float logratio = newlogp - p.logp_old[i];
-        const float ratio = expf(logratio);
-        float advn = p.adv[i];
-        if (p.norm_adv) advn = __fdiv_rn(advn - mean, stdv + 1e-8f);
-        // clipped surrogate (:581-583)
-        const float l1 = -advn * ratio;
-        const float rc = fminf(fmaxf(ratio, p.clip_lo), p.clip_hi);
-        const float l2 = -advn * rc;
-        const float pg = fmaxf(l1, l2);
-        const bool in_range = (ratio >= p.clip_lo) && (ratio <= p.clip_hi);
-        float g_ratio;                       // d pg / d ratio
-        if (l1 > l2) g_ratio = -advn;
-        else if (l2 > l1) g_ratio = in_range ? -advn : 0.f;
-        else g_ratio = 0.5f * (-advn) + (in_range ? 0.5f * (-advn) : 0.f);
-        // value loss (:585-597)
-        const float R = p.ret[i], Vold = p.val[i];
-        const float du = v - R;
-        const float u = du * du;
-        float vterm = u, g_v = du;           // d (0.5*vterm) / d v
-        if (p.clip_vloss) {
-            const float d = v - Vold;
-            const float dc = fminf(fmaxf(d, -p.clip_f), p.clip_f);
-            const float vc = Vold + dc;
-            const float dw = vc - R;
-            const float w = dw * dw;
-            const bool v_in = (d >= -p.clip_f) && (d <= p.clip_f);
-            const float gw = v_in ? dw : 0.f;
-            if (u > w) { vterm = u; g_v = du; }
-            else if (w > u) { vterm = w; g_v = gw; }
-            else { vterm = u; g_v = 0.5f * du + 0.5f * gw; }
+    const int64_t i0 = (int64_t)blockIdx.x * kWarpsPerBlock + warp, istep = (int64_t)gridDim.x * kWarpsPerBlock;
+    if (HV > 0) {
+        constexpr int NV = HV > 0 ? HV : 1;
+        float4 hn[NV];
+        if (i0 < p.rows) {
+#pragma unroll
+            for (int g = 0; g < NV; ++g) hn[g] = __ldcs(reinterpret_cast<const float4 *>(p.hidden + i0 * H + g * 128) + lane);
         }
-        // gradients wrt logits / value
-        const float coef_a = g_ratio * ratio * inv_mb;
-        const float coef_e = p.ent_coef * inv_mb;
-        float dz = 0.f;
-        if (lane < A) dz = coef_a * ((lane == a ? 1.f : 0.f) - pk) + coef_e * pk * (ell + Hh);
-        const float dv = p.vf_coef * inv_mb * g_v;
-        if (lane < p.AP) p.gz[i * p.AP + lane] = lane < A ? dz : (lane == A ? dv : 0.f);
-        // d hidden, masked by ReLU of the last trunk layer
-        // (warp-uniform trip count: the shuffles below need all 32 lanes, also when H % 32 != 0)
-        for (int j0 = 0; j0 < H; j0 += 32) {
-            const int j = j0 + lane;
-            const bool on = j < H;
-            float s = on ? dv * sW[A * H + j] : 0.f;
+        for (int64_t i = i0; i < p.rows; i += istep) {
+            float4 hv[NV];
+#pragma unroll
+            for (int g = 0; g < NV; ++g) hv[g] = hn[g];
+            if (i + istep < p.rows) {
+#pragma unroll
+                for (int g = 0; g < NV; ++g)
+                    hn[g] = __ldcs(reinterpret_cast<const float4 *>(p.hidden + (i + istep) * H + g * 128) + lane);
+            }
+            float z = 0.f, v = 0.f;
+            for (int k = 0; k <= A; ++k) {
+                float part = 0.f;
+#pragma unroll
+                for (int g = 0; g < NV; ++g) {
+                    const float4 w = *(reinterpret_cast<const float4 *>(sW + k * H + g * 128) + lane);
+                    part = fmaf(w.x, hv[g].x, part);
+                    part = fmaf(w.y, hv[g].y, part);
+                    part = fmaf(w.z, hv[g].z, part);
+                    part = fmaf(w.w, hv[g].w, part);
+                }
+                part = warp_sum(part) + sB[k];
+                if (k == A) v = part;
+                else if (lane == k) z = part;
+            }
+            float dz, dv;
+            ppo_sample_loss(p, i, z, v, lane, inv_mb, mean, stdv, dz, dv, acc);
+            // d hidden = dv * Wc + sum_k dz_k * Wa[k], masked by the ReLU of the last trunk layer
+            float4 s[NV];
+#pragma unroll
+            for (int g = 0; g < NV; ++g) {
+                const float4 w = *(reinterpret_cast<const float4 *>(sW + A * H + g * 128) + lane);
+                s[g] = make_float4(dv * w.x, dv * w.y, dv * w.z, dv * w.w);
+            }
             for (int k = 0; k < A; ++k) {
                 const float dzk = __shfl_sync(kFull, dz, k);
-                if (on) s = fmaf(dzk, sW[k * H + j], s);
+#pragma unroll
+                for (int g = 0; g < NV; ++g) {
+                    const float4 w = *(reinterpret_cast<const float4 *>(sW + k * H + g * 128) + lane);
+                    s[g].x = fmaf(dzk, w.x, s[g].x);
+                    s[g].y = fmaf(dzk, w.y, s[g].y);
+                    s[g].z = fmaf(dzk, w.z, s[g].z);
+                    s[g].w = fmaf(dzk, w.w, s[g].w);
+                }
             }
-            if (on) p.dh[i * H + j] = h[j] > 0.f ? s : 0.f;
+#pragma unroll
+            for (int g = 0; g < NV; ++g) {
+                const float4 o = make_float4(hv[g].x > 0.f ? s[g].x : 0.f, hv[g].y > 0.f ? s[g].y : 0.f,
+                                             hv[g].z > 0.f ? s[g].z : 0.f, hv[g].w > 0.f ? s[g].w : 0.f);
+                *(reinterpret_cast<float4 *>(p.dh + i * H + g * 128) + lane) = o;
+            }
         }
-        if (lane == 0) {
-            acc[0] += (double)pg;
-            acc[1] += (double)vterm;
-            acc[2] += (double)Hh;
-            acc[3] += (double)(-logratio);
-            acc[4] += (double)((ratio - 1.0f) - logratio);
-            acc[5] += (fabsf(ratio - 1.0f) > p.clip_f) ? 1.0 : 0.0;
+    } else {
+        for (int64_t i = i0; i < p.rows; i += istep) {
+            const float *h = p.hidden + i * H;
+            float z, v;
+            warp_head_forward(h, sW, sB, A, H, lane, z, v);
+            float dz, dv;
+            ppo_sample_loss(p, i, z, v, lane, inv_mb, mean, stdv, dz, dv, acc);
+            // d hidden, masked by ReLU of the last trunk layer
+            // (warp-uniform trip count: the shuffles below need all 32 lanes, also when H % 32 != 0)
+            for (int j0 = 0; j0 < H; j0 += 32) {
+                const int j = j0 + lane;
+                const bool on = j < H;
+                float s = on ? dv * sW[A * H + j] : 0.f;
+                for (int k = 0; k < A; ++k) {
+                    const float dzk = __shfl_sync(kFull, dz, k);
+                    if (on) s = fmaf(dzk, sW[k * H + j], s);
+                }
+                if (on) p.dh[i * H + j] = h[j] > 0.f ? s : 0.f;
+            }
         }
     }
     __shared__ double red[kWarpsPerBlock][6];
@@ -556,13 +630,19 @@ int launch_adv_stats(const ocppo_handle *h, const float *b_adv, const int64_t *i
 
 int launch_loss_head(const ocppo_handle *h, LossArgs a, int *blocks_used, int blocks_avail, cudaStream_t stream) {
     const int smem = head_smem_bytes(a.A, a.H);
-    OCPPO_TRY(ensure_head_smem((const void *)loss_head_kernel, smem));
+    const bool aligned = ((((uintptr_t)a.hidden | (uintptr_t)a.dh) & 15) == 0);
+    void (*kern)(LossArgs) = loss_head_kernel<0>;
+    if (aligned && a.H == 128) kern = loss_head_kernel<1>;
+    else if (aligned && a.H == 256) kern = loss_head_kernel<2>;
+    else if (aligned && a.H == 512) kern = loss_head_kernel<4>;
+    else if (aligned && a.H == 1024) kern = loss_head_kernel<8>;
+    OCPPO_TRY(ensure_head_smem((const void *)kern, smem));
     int cap = h->sm_count * 4;
     if (cap > blocks_avail) cap = blocks_avail;
     OCPPO_CHECK_ARG(cap >= 1, "loss head: out of partial-sum slots");
     const unsigned grid = grid_for(a.rows, kWarpsPerBlock, cap);
     ProfScope ps(KC_HEAD, 1, stream);
-    loss_head_kernel<<<grid, kHeadThreads, smem, stream>>>(a);
+    kern<<<grid, kHeadThreads, smem, stream>>>(a);
     OCPPO_LAUNCH_CHECK("loss_head_kernel");
     *blocks_used = (int)grid;
     return OCPPO_OK;

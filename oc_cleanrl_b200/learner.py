@@ -108,6 +108,7 @@ class PPOLearner:
         self.adam_step = 0                      # torch Adam's `step`, never reset
         self.chunk_rows = int(chunk_rows)
         self._stats = self._gn = None
+        self._perm_host = self._perm_dev = None
         self._ensure_slots(args.update_epochs * (args.num_minibatches + 1))
         self._hp = _abi.HParams(float(args.clip_coef), float(args.ent_coef), float(args.vf_coef),
                                 int(bool(args.norm_adv)), int(bool(args.clip_vloss)))
@@ -167,12 +168,26 @@ class PPOLearner:
                 returns.reshape(-1).contiguous(), values.reshape(-1).contiguous())
         if flat[1].dtype != torch.int64:
             raise _abi.OcppoError("actions must be int64 (torch.long), as in the reference buffers")
-        if permutations is None:
-            permutations = make_permutations(batch_size, a.update_epochs, self.np_rng)
-        perm_dev = permutations.to(self.device, non_blocking=True)
+        # Without given permutations the reference's order is produced here, one cumulative host shuffle per epoch
+        # (:558-561), each into its own pinned row and copied asynchronously: the shuffle of epoch e+1 runs on the
+        # host while the device is busy with epoch e.
+        lazy = permutations is None
+        if lazy:
+            if self._perm_host is None or tuple(self._perm_host.shape) != (a.update_epochs, batch_size):
+                self._perm_host = torch.empty((a.update_epochs, batch_size), dtype=torch.int64, pin_memory=True)
+                self._perm_dev = torch.empty((a.update_epochs, batch_size), dtype=torch.int64, device=self.device)
+            shuffle = np.random.shuffle if self.np_rng is None else self.np_rng.shuffle
+            b_inds = np.arange(batch_size)
+            perm_dev = self._perm_dev
+        else:
+            perm_dev = permutations.to(self.device, non_blocking=True)
         self._ensure_slots(a.update_epochs * (-(-batch_size // minibatch_size)))
         slot, epochs_run = 0, 0
         for epoch in range(a.update_epochs):
+            if lazy:
+                shuffle(b_inds)
+                self._perm_host[epoch].numpy()[:] = b_inds
+                perm_dev[epoch].copy_(self._perm_host[epoch], non_blocking=True)
             for start in range(0, batch_size, minibatch_size):
                 end = start + minibatch_size
                 idx = perm_dev[epoch, start:end]
