@@ -181,15 +181,16 @@ static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_
 }
 
 static void pick_split(const ocppo_handle *h, int M, int N, int64_t K, int *splits, int64_t *k_per) {
-    const bool tc = g_gemm_mode >= 1 && M % 128 == 0 && N % 256 == 0;
+    const int tn = tc_tile_n(g_gemm_mode == 2);
+    const bool tc = g_gemm_mode >= 1 && M % 128 == 0 && N % tn == 0;
     int64_t S;
     const int64_t s_cap0 = K / 256 > 1 ? K / 256 : 1;
     const int64_t s_cap = s_cap0 < kSplitMax ? s_cap0 : kSplitMax;
     if (tc) {
-        // persistent kernel, one CTA pair per 2 SMs, 256x256 tiles: the split count that fills the last wave best
+        // persistent kernel, one CTA pair per 2 SMs, 256 x tn tiles: the split count that fills the last wave best
         // (fewest splits on ties -- less partial traffic); accuracy does not depend on it, the kernel
         // drains its accumulator every 1024 rows.
-        const int64_t tiles = ceil_div(M, 256) * (N / 256), sms = h->sm_count / 2;   // 256x256 tiles, one per CTA pair
+        const int64_t tiles = ceil_div(M, 256) * (N / tn), sms = h->sm_count / 2;   // one tile per CTA pair at a time
         S = 1;
         double best = 0.0;
         for (int64_t c = 1; c <= s_cap; ++c) {

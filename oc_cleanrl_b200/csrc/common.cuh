@@ -131,6 +131,7 @@ int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);      
 int fma_gemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);    // sgemm.cu, fp32 CUDA cores
 bool tc_gemm_supported(SgemmMode mode, const SgemmArgs &a);                      // tc_gemm.cu, tcgen05 3xTF32
 int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);
+int tc_tile_n(bool single_acc);                                                   // N tile of the CTA pair: 128 (split accumulators) / 256
 // 0: fp32 FMA kernels only; 1: tcgen05 3xTF32 wherever the shape fits (fp32-grade accuracy; main and
 // correction products in separate TMEM accumulators); 2: same with a single, double-buffered accumulator
 extern int g_gemm_mode;

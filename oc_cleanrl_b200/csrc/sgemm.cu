@@ -194,10 +194,10 @@ int g_gemm_mode = 1;   // tcgen05 3xTF32 with split accumulators; see ocppo_set_
 
 int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream) {
     static const int ops_mask = getenv("OCPPO_TC_OPS") ? atoi(getenv("OCPPO_TC_OPS")) : 7;   // bring-up: bit per op
-    if (g_gemm_mode >= 1 && ((ops_mask >> (int)mode) & 1) && tc_gemm_supported(mode, a)) {
+    if (g_gemm_mode >= 1 && ((ops_mask >> (int)mode) & 1)) {
         SgemmArgs b = a;
         b.single_acc = g_gemm_mode == 2;
-        return tc_gemm_launch(mode, b, stream);
+        if (tc_gemm_supported(mode, b)) return tc_gemm_launch(mode, b, stream);
     }
     return fma_gemm_launch(mode, a, stream);
 }

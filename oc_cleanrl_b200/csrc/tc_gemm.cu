@@ -29,8 +29,21 @@ namespace ocppo {
 namespace {
 
 constexpr int TM = 128;                                     // rows of A (and of the accumulator) per CTA
-constexpr int TN = 256;                                     // accumulator columns (the pair's full N tile)
-constexpr int TBW = 128;                                    // columns of B staged per CTA
+// N tile of the CTA pair (= columns of one accumulator) and TMEM use, by accumulator scheme:
+//   SPLIT (mode 1): main accumulator in TMEM columns [0,256), corrections in [256,512): one tile in flight;
+//   single (mode 2): one 256-column accumulator per tile, two tiles in flight (epilogue overlaps the next tile).
+// A 128-column tile would let the split scheme double-buffer too, and was measured: 10-50 % SLOWER on every trunk
+// shape with K >= 512 -- at N = 128 the MMA re-reads its A operand from shared memory twice as often per flop
+// (SS mode: 128 B/cycle of operand traffic, the whole shared-memory bandwidth), so the kernel becomes smem-bound.
+template <bool SPLIT> struct Tile {
+    static constexpr int TN = 256;
+    static constexpr int TBW = TN / 2;                      // columns of B staged per CTA
+    static constexpr int kStageBytesB = TBW * 32 * 4;       // 16 KB
+    static constexpr int kStageBytes = 2 * (128 * 32 * 4 + kStageBytesB);   // hi + lo: 64 KB
+    static constexpr int kNumStages = 3;                    // 192 KB
+    static constexpr int kAccBufs = SPLIT ? 1 : 2;          // tiles whose accumulators fit in 512 TMEM columns
+    static constexpr int kAccStride = SPLIT ? 512 : 256;    // TMEM columns per tile
+};
 constexpr int TK = 32;
 constexpr int kPairM = 2 * TM;                              // 256-row tile per CTA pair
 constexpr int kEpiWarps = 4, kProdWarps = 8;
@@ -38,13 +51,12 @@ constexpr int kProdThreads = kProdWarps * 32;               // 256
 constexpr int kProdTid0 = 256;                              // warpgroups 2-3
 constexpr int kTcThreads = kProdTid0 + kProdThreads;        // 512 = 4 warpgroups (setmaxnreg is per warpgroup)
 constexpr int kStageBytesA = TM * TK * 4;                   // 16 KB
-constexpr int kStageBytesB = TBW * TK * 4;                  // 16 KB
-constexpr int kStageBytes = 2 * (kStageBytesA + kStageBytesB);   // hi + lo: 64 KB
-constexpr int kNumStages = 3;
-constexpr int kTmemCols = 512;                              // two 256-column accumulators
+constexpr int kRingBytes = 192 * 1024;                      // 3 x 64 KB or 4 x 48 KB
+constexpr int kMaxStages = 4;
+constexpr int kTmemCols = 512;                              // two tiles' accumulators
 constexpr int kEpiPadBytes = kEpiWarps * 32 * 33 * 4;       // per-warp 32 x 33 transpose pads
 constexpr int kBiasRedBytes = 8 * TM * 4;                   // WGRAD bias partials [8 k-lanes][128]
-constexpr int kTcSmemBytes = kNumStages * kStageBytes + kEpiPadBytes + kBiasRedBytes + 128 /*barriers*/ + 1024 /*align*/;
+constexpr int kTcSmemBytes = kRingBytes + kEpiPadBytes + kBiasRedBytes + 256 /*barriers*/ + 1024 /*align*/;
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -72,6 +84,7 @@ __device__ __forceinline__ void mbar_arrive_on(uint32_t bar, uint32_t cta) {
         ::"r"(bar), "r"(cta)
         : "memory");
 }
+// (A suspend-time hint on try_wait was measured: no gain on FWD/WGRAD, 10-15 % slower DGRAD -- later wake-ups.)
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     const long long t0 = clock64();
     uint32_t done = 0;
@@ -149,25 +162,37 @@ __device__ __forceinline__ int off_mnmajor(int p, int q) {
     const int mb = g >> 3, c = g & 7;
     return mb * 4096 + k * 128 + ((((c >> 1) ^ (k & 3)) << 5) | ((c & 1) << 4));
 }
-// One stage: read this thread's 8 raw chunks (A and B) first, then derive and store the lo chunks.
-template <bool A_MN, bool B_MN, bool SUM>
+// 64-column MN-major tile (2 chunks of [32 k][32 floats]): 16 threads per k-row, k-rows p / 16 + 16 q, q < 2.
+__device__ __forceinline__ int off_mnmajor64(int p, int q) {
+    const int g = p & 15, k = q * 16 + (p >> 4);
+    const int mb = g >> 3, c = g & 7;
+    return mb * 4096 + k * 128 + ((((c >> 1) ^ (k & 3)) << 5) | ((c & 1) << 4));
+}
+// One stage: read this thread's raw chunks (4 of A, BW/32 of B) first, then derive and store the lo chunks.
+// (A 64-row K-major B tile is the first two passes of off_kmajor.)
+template <bool A_MN, bool B_MN, bool SUM, int BW>
 __device__ __forceinline__ void convert_stage(const uint8_t *a_hi, uint8_t *a_lo, const uint8_t *b_hi, uint8_t *b_lo,
                                               int p, float4 &colsum) {
-    int oa[4], ob[4];
-    float4 va[4], vb[4];
+    constexpr int NB = BW / 32;
+    int oa[4], ob[NB];
+    float4 va[4], vb[NB];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
         oa[q] = A_MN ? off_mnmajor(p, q) : off_kmajor(p, q);
-        ob[q] = B_MN ? off_mnmajor(p, q) : off_kmajor(p, q);
         va[q] = *reinterpret_cast<const float4 *>(a_hi + oa[q]);
+    }
+#pragma unroll
+    for (int q = 0; q < NB; ++q) {
+        ob[q] = B_MN ? (BW == 128 ? off_mnmajor(p, q) : off_mnmajor64(p, q)) : off_kmajor(p, q);
         vb[q] = *reinterpret_cast<const float4 *>(b_hi + ob[q]);
     }
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
         if (SUM) { colsum.x += va[q].x; colsum.y += va[q].y; colsum.z += va[q].z; colsum.w += va[q].w; }
         *reinterpret_cast<float4 *>(a_lo + oa[q]) = lo4(va[q]);
-        *reinterpret_cast<float4 *>(b_lo + ob[q]) = lo4(vb[q]);
     }
+#pragma unroll
+    for (int q = 0; q < NB; ++q) *reinterpret_cast<float4 *>(b_lo + ob[q]) = lo4(vb[q]);
 }
 
 // ---- TMA ----------------------------------------------------------------------
@@ -189,14 +214,14 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *tm,
 
 struct TileCoord { int m0, n0, split; int64_t kbeg, kend; int nk; };
 
-__device__ __forceinline__ TileCoord tile_coord(const SgemmArgs &p, int tile, int nt_n, int nt_m) {
+__device__ __forceinline__ TileCoord tile_coord(const SgemmArgs &p, int tile, int nt_n, int nt_m, int tn) {
     TileCoord t;
     const int nb = tile % nt_n;
     const int rest = tile / nt_n;
     const int mb = rest % nt_m;
     t.split = rest / nt_m;
     t.m0 = mb * kPairM;
-    t.n0 = nb * TN;
+    t.n0 = nb * tn;
     t.kbeg = (int64_t)t.split * p.k_per_split;
     t.kend = (t.kbeg + p.k_per_split < p.K) ? t.kbeg + p.k_per_split : p.K;
     t.nk = (int)((t.kend - t.kbeg + TK - 1) / TK);
@@ -215,35 +240,48 @@ __device__ __forceinline__ TileCoord tile_coord(const SgemmArgs &p, int tile, in
         : "r"(taddr)                                                                                                \
         : "memory")
 
-template <int MODE>
+#define OCPPO_TMEM_LD16(v, taddr)                                                                                   \
+    asm volatile(                                                                                                   \
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "                                                                   \
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"                            \
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),           \
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])      \
+        : "r"(taddr)                                                                                                \
+        : "memory")
+
+template <int MODE, bool SPLIT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_gemm_kernel(SgemmArgs p, int nt_n, int nt_m, int ntiles, const __grid_constant__ CUtensorMap tmA,
                                                                                          const __grid_constant__ CUtensorMap tmB) {
     constexpr bool A_MN = (MODE == SGEMM_WGRAD);
     constexpr bool B_MN = (MODE != SGEMM_FWD);
+    constexpr int TN = Tile<SPLIT>::TN, TBW = Tile<SPLIT>::TBW, kStageBytesB = Tile<SPLIT>::kStageBytesB;
+    constexpr int kStageBytes = Tile<SPLIT>::kStageBytes, kNumStages = Tile<SPLIT>::kNumStages;
+    constexpr int kAccStride = Tile<SPLIT>::kAccStride, kAccBufs = Tile<SPLIT>::kAccBufs;
+    static_assert(kNumStages * kStageBytes <= kRingBytes && kNumStages <= kMaxStages, "stage ring");
     // The TMEM accumulator adds with truncation (measured: error grows linearly with the number of MMAs
     // chained into one accumulator), so WGRAD, whose contraction runs over >= 10^4 rows, is cut into
     // 1024-row segments; each is drained by the epilogue and summed in fp32 round-to-nearest in fixed order.
     constexpr int kSegStages = (MODE == SGEMM_WGRAD) ? 32 : (1 << 30);
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    float *epi_pad = reinterpret_cast<float *>(smem + kNumStages * kStageBytes);
-    float *bias_red = reinterpret_cast<float *>(smem + kNumStages * kStageBytes + kEpiPadBytes);
-    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kNumStages * kStageBytes + kEpiPadBytes + kBiasRedBytes);
-    // bars[0..2] full (used in the leader CTA), [3..5] empty, [6..7] tmem_full, [8..9] tmem_empty (leader),
-    // [10..12] tma (raw tile landed, per CTA)
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 13);
-    const uint32_t bar_tma = smem_u32(&bars[10]);
-    const uint32_t bar_full = smem_u32(&bars[0]), bar_empty = smem_u32(&bars[3]);
-    const uint32_t bar_tfull = smem_u32(&bars[6]), bar_tempty = smem_u32(&bars[8]);
+    float *epi_pad = reinterpret_cast<float *>(smem + kRingBytes);
+    float *bias_red = reinterpret_cast<float *>(smem + kRingBytes + kEpiPadBytes);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kRingBytes + kEpiPadBytes + kBiasRedBytes);
+    // bars[0..3] full (used in the leader CTA), [4..7] empty, [8..9] tmem_full, [10..11] tmem_empty (leader),
+    // [12..15] tma (raw tile landed, per CTA)
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 16);
+    const uint32_t bar_tma = smem_u32(&bars[12]);
+    const uint32_t bar_full = smem_u32(&bars[0]), bar_empty = smem_u32(&bars[4]);
+    const uint32_t bar_tfull = smem_u32(&bars[8]), bar_tempty = smem_u32(&bars[10]);
     const uint32_t cta_rank = cluster_ctarank();             // 0 = leader of the pair
     const int ncl = gridDim.x >> 1, cl = blockIdx.x >> 1;    // clusters in the grid, this cluster
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     // The TMEM accumulator adds with round-toward-zero (tools/tc_probe.cu Q4): every MMA chained into it costs
-    // about half an ulp of bias, and two of the three passes only add tiny correction products.  By default
-    // those go to a second accumulator (columns 256..511) that the epilogue adds in fp32 round-to-nearest:
-    // 3x less rounding error, at the price of the tile-to-tile accumulator double buffering.
-    const bool split_acc = !p.single_acc;
+    // about half an ulp of bias, and two of the three passes only add tiny correction products.  With SPLIT
+    // those go to a second accumulator (the tile's columns [TN, 2 TN)) that the epilogue adds in fp32
+    // round-to-nearest: 3x less rounding error.
+    constexpr bool split_acc = SPLIT;
 
     if (tid == 0) {
         for (int s = 0; s < kNumStages; ++s) {
@@ -273,9 +311,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
         float *pad = epi_pad + warp * 32 * 33;
         int ai = 0;                           // accumulator passes handled so far (tile x k-segment)
         for (int tile = cl; tile < ntiles; tile += ncl) {
-          const TileCoord t = tile_coord(p, tile, nt_n, nt_m);
+          const TileCoord t = tile_coord(p, tile, nt_n, nt_m, TN);
           for (int kb0 = 0; kb0 < t.nk; kb0 += kSegStages, ++ai) {
-            const int nbuf = (split_acc || (p.dbg & 4)) ? 1 : 2, acc = ai % nbuf;
+            const int nbuf = (p.dbg & 4) ? 1 : kAccBufs, acc = ai % nbuf;
             const bool rmw = (MODE == SGEMM_WGRAD) && kb0 > 0;     // later k-segments add onto the first
             mbar_wait(bar_tfull + 8 * acc, (uint32_t)((ai / nbuf) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -301,14 +339,26 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
 #pragma unroll 1
             for (int cc = 0; cc < TN / 32; ++cc) {
                 uint32_t v[32];
-                const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(acc * TN + cc * 32);
+                const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(acc * kAccStride + cc * 32);
                 OCPPO_TMEM_LD32(v, taddr);
-                if (split_acc) {               // split accumulators: main in columns [0,256), corrections in [256,512)
-                    uint32_t w[32];
-                    OCPPO_TMEM_LD32(w, taddr + TN);
-                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (split_acc) {               // main in the tile's columns [0,TN), corrections in [TN,2TN)
+                    if (MODE == SGEMM_DGRAD) {   // two halves: the mask prefetch leaves no room for 32 more registers
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(w[j]));
+                        for (int hh = 0; hh < 2; ++hh) {
+                            uint32_t w[16];
+                            OCPPO_TMEM_LD16(w, taddr + TN + hh * 16);
+                            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                            for (int j = 0; j < 16; ++j)
+                                v[hh * 16 + j] = __float_as_uint(__uint_as_float(v[hh * 16 + j]) + __uint_as_float(w[j]));
+                        }
+                    } else {
+                        uint32_t w[32];
+                        OCPPO_TMEM_LD32(w, taddr + TN);
+                        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(w[j]));
+                    }
                 }
                 if (MODE == SGEMM_DGRAD) {
 #pragma unroll
@@ -364,12 +414,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
             constexpr uint64_t a_step = (A_MN ? 1024 : 32) >> 4, b_step = (B_MN ? 1024 : 32) >> 4;
             int stage = 0, sphase = 0, ai = 0;
             for (int tile = cl; tile < ntiles; tile += ncl) {
-              const TileCoord t = tile_coord(p, tile, nt_n, nt_m);
+              const TileCoord t = tile_coord(p, tile, nt_n, nt_m, TN);
               for (int kb0 = 0; kb0 < t.nk; kb0 += kSegStages, ++ai) {
-                const int nbuf = (split_acc || (p.dbg & 4)) ? 1 : 2, acc = ai % nbuf;
+                const int nbuf = (p.dbg & 4) ? 1 : kAccBufs, acc = ai % nbuf;
                 mbar_wait(bar_tempty + 8 * acc, (uint32_t)(((ai / nbuf) & 1) ^ 1));
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * TN);
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * kAccStride);
                 const int kb1 = (t.nk - kb0 < kSegStages) ? t.nk : kb0 + kSegStages;
                 for (int kb = kb0; kb < kb1; ++kb) {
                     const int s = stage;
@@ -406,7 +456,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
             const int rank_m = (int)cta_rank * TM, rank_n = (int)cta_rank * TBW;
             int stage = 0, sphase = 0;
             for (int tile = cl; tile < ntiles; tile += ncl) {
-                const TileCoord t = tile_coord(p, tile, nt_n, nt_m);
+                const TileCoord t = tile_coord(p, tile, nt_n, nt_m, TN);
                 for (int kb = 0; kb < t.nk; ++kb) {
                     const int s = stage;
                     mbar_wait(bar_empty + 8 * s, (uint32_t)(sphase ^ 1));
@@ -430,7 +480,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
         int stage = 0, sphase = 0;
         const int rank_m = (int)cta_rank * TM;
         for (int tile = cl; tile < ntiles; tile += ncl) {
-            const TileCoord t = tile_coord(p, tile, nt_n, nt_m);
+            const TileCoord t = tile_coord(p, tile, nt_n, nt_m, TN);
             const bool do_bias = (MODE == SGEMM_WGRAD) && t.n0 == 0 && p.bias_part != nullptr;
             float4 bsum = make_float4(0.f, 0.f, 0.f, 0.f);
             for (int kb = 0; kb < t.nk; ++kb) {
@@ -438,8 +488,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                 mbar_wait(bar_tma + 8 * s, (uint32_t)sphase);           // raw tile landed (TMA complete_tx)
                 uint8_t *st = smem + s * kStageBytes;
                 uint8_t *a_hi = st, *a_lo = st + kStageBytesA, *b_hi = st + 2 * kStageBytesA, *b_lo = b_hi + kStageBytesB;
-                if (A_MN && do_bias) convert_stage<A_MN, B_MN, true>(a_hi, a_lo, b_hi, b_lo, pt, bsum);
-                else convert_stage<A_MN, B_MN, false>(a_hi, a_lo, b_hi, b_lo, pt, bsum);
+                if (A_MN && do_bias) convert_stage<A_MN, B_MN, true, TBW>(a_hi, a_lo, b_hi, b_lo, pt, bsum);
+                else convert_stage<A_MN, B_MN, false, TBW>(a_hi, a_lo, b_hi, b_lo, pt, bsum);
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
                 if (pwarp_lane0) mbar_arrive_on(bar_full + 8 * s, 0);      // the leader CTA's barrier
@@ -474,9 +524,11 @@ inline bool al16(const void *p) { return (((uintptr_t)p) & 15) == 0; }
 }  // namespace
 
 // Shapes the tensor-core kernel takes; everything else stays on the FMA kernel.
+int tc_tile_n(bool single_acc) { return single_acc ? Tile<false>::TN : Tile<true>::TN; }   // both 256 today
+
 bool tc_gemm_supported(SgemmMode mode, const SgemmArgs &a) {
     if (a.M <= 0 || a.N <= 0 || a.K <= 0) return false;
-    if (a.N % TN != 0) return false;
+    if (a.N % tc_tile_n(a.single_acc != 0) != 0) return false;
     if ((a.lda & 3) || (a.ldb & 3) || (a.ldc & 3) || !al16(a.A) || !al16(a.B) || !al16(a.C)) return false;
     if (mode == SGEMM_WGRAD) {
         if (a.M % TM != 0) return false;
@@ -507,24 +559,24 @@ EncodeTiledFn encode_fn() {
     return fn;
 }
 
-// K-major operand [rows, K] (row stride ld floats): 2-D map {K, rows}, box 32 x 128, SWIZZLE_128B.
-// MN-major operand [K, cols]: 3-D map {32, K, cols/32}, box 32 x 32 x 4 -> smem [chunk][k][32 floats],
+// K-major operand [rows, K] (row stride ld floats): 2-D map {K, rows}, box 32 x box_mn, SWIZZLE_128B.
+// MN-major operand [K, cols]: 3-D map {32, K, cols/32}, box 32 x 32 x box_mn/32 -> smem [chunk][k][32 floats],
 // SWIZZLE_128B_ATOM_32B (the TMA name of UMMA's SWIZZLE_128B_BASE32B).
-int make_map(CUtensorMap *tm, const float *base, bool mn_major, int64_t rows_or_cols, int64_t K, int64_t ld) {
+int make_map(CUtensorMap *tm, const float *base, bool mn_major, int64_t rows_or_cols, int64_t K, int64_t ld, int box_mn) {
     EncodeTiledFn fn = encode_fn();
     if (fn == nullptr) { set_error("cuTensorMapEncodeTiled entry point not available"); return OCPPO_ECUDA; }
     CUresult r;
     if (!mn_major) {
         const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows_or_cols};
         const cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
-        const cuuint32_t box[2] = {32, 128}, estr[2] = {1, 1};
+        const cuuint32_t box[2] = {32, (cuuint32_t)box_mn}, estr[2] = {1, 1};
         r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), dims, strides, box, estr,
                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     } else {
         const cuuint64_t dims[3] = {32, (cuuint64_t)K, (cuuint64_t)(rows_or_cols / 32)};
         const cuuint64_t strides[2] = {(cuuint64_t)ld * 4, 128};
-        const cuuint32_t box[3] = {32, 32, 4}, estr[3] = {1, 1, 1};
+        const cuuint32_t box[3] = {32, 32, (cuuint32_t)(box_mn / 32)}, estr[3] = {1, 1, 1};
         r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float *>(base), dims, strides, box, estr,
                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -541,27 +593,32 @@ int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
     a.dbg = dbg;
     OCPPO_CHECK_ARG(tc_gemm_supported(mode, a), "tc_gemm: unsupported shape M=%d N=%d K=%lld", a.M, a.N, (long long)a.K);
     const int splits = mode == SGEMM_WGRAD ? a.splits : 1;
-    const int nt_n = a.N / TN, nt_m = (int)ceil_div(a.M, kPairM);
+    const bool split = a.single_acc == 0;
+    const int tn = tc_tile_n(!split);
+    const int nt_n = a.N / tn, nt_m = (int)ceil_div(a.M, kPairM);
     const int64_t ntiles64 = (int64_t)nt_n * nt_m * splits;
     OCPPO_CHECK_ARG(ntiles64 < (1LL << 31), "tc_gemm: too many tiles");
     const int ntiles = (int)ntiles64;
+    typedef void (*Kern)(SgemmArgs, int, int, int, const CUtensorMap, const CUtensorMap);
+    static const Kern kerns[2][3] = {
+        {tc_gemm_kernel<SGEMM_FWD, false>, tc_gemm_kernel<SGEMM_DGRAD, false>, tc_gemm_kernel<SGEMM_WGRAD, false>},
+        {tc_gemm_kernel<SGEMM_FWD, true>, tc_gemm_kernel<SGEMM_DGRAD, true>, tc_gemm_kernel<SGEMM_WGRAD, true>}};
     static int sms = 0;
     if (sms == 0) {
         int dev = 0;
         OCPPO_CUDA(cudaGetDevice(&dev));
         OCPPO_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        OCPPO_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<SGEMM_FWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
-        OCPPO_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<SGEMM_DGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
-        OCPPO_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<SGEMM_WGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
+        for (int i = 0; i < 2; ++i)
+            for (int j = 0; j < 3; ++j)
+                OCPPO_CUDA(cudaFuncSetAttribute(kerns[i][j], cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
     }
     const int grid = 2 * (ntiles < sms / 2 ? ntiles : sms / 2);     // CTA pairs
     CUtensorMap tmA, tmB;
-    OCPPO_TRY(make_map(&tmA, a.A, mode == SGEMM_WGRAD, a.M, a.K, a.lda));
-    OCPPO_TRY(make_map(&tmB, a.B, mode != SGEMM_FWD, a.N, a.K, a.ldb));
+    OCPPO_TRY(make_map(&tmA, a.A, mode == SGEMM_WGRAD, a.M, a.K, a.lda, TM));
+    OCPPO_TRY(make_map(&tmB, a.B, mode != SGEMM_FWD, a.N, a.K, a.ldb, tn / 2));
+    const int mi = mode == SGEMM_FWD ? 0 : (mode == SGEMM_DGRAD ? 1 : 2);
     ProfScope ps(mode == SGEMM_FWD ? KC_SGEMM_FWD : (mode == SGEMM_DGRAD ? KC_SGEMM_DGRAD : KC_SGEMM_WGRAD), 1, stream);
-    if (mode == SGEMM_FWD) tc_gemm_kernel<SGEMM_FWD><<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles, tmA, tmB);
-    else if (mode == SGEMM_DGRAD) tc_gemm_kernel<SGEMM_DGRAD><<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles, tmA, tmB);
-    else tc_gemm_kernel<SGEMM_WGRAD><<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles, tmA, tmB);
+    kerns[split ? 1 : 0][mi]<<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles, tmA, tmB);
     OCPPO_LAUNCH_CHECK("tc_gemm_kernel");
     return OCPPO_OK;
 }

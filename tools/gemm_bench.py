@@ -49,7 +49,7 @@ def bench(op, engine, M, N, K, splits, iters):
 if __name__ == "__main__":
     engine = int(sys.argv[1]) if len(sys.argv) > 1 else 1
     iters = int(sys.argv[2]) if len(sys.argv) > 2 else 5
-    R = 32768
+    R = int(sys.argv[3]) if len(sys.argv) > 3 else 32768
     shapes = [(0, 4 * R, 512, 256, 1), (0, 4 * R, 1024, 512, 1), (0, 4 * R, 512, 1024, 1), (0, R, 512, 2048, 1),
               (1, 4 * R, 256, 512, 1), (1, 4 * R, 512, 1024, 1), (1, 4 * R, 1024, 512, 1), (1, R, 2048, 512, 1),
               (2, 512, 256, 4 * R, 32), (2, 1024, 512, 4 * R, 9), (2, 512, 1024, 4 * R, 9), (2, 512, 2048, R, 9)]
