@@ -114,6 +114,8 @@ static int64_t carve(ocppo_handle *h, void *base, int64_t R, int training, bool 
         const Layer &L = h->layers[l];
         const int64_t n = R * L.row_mult * L.out_dim;
         t->act[l] = cv.take<float>(n);
+        t->relu_bits[l] = (training && L.out_dim % 32 == 0) ? cv.take<uint32_t>(n / 32) : nullptr;
+        t->relu_bits_valid[l] = 0;
         if (n > max_act) max_act = n;
         if ((int64_t)L.out_dim * L.in_dim > max_w) max_w = (int64_t)L.out_dim * L.in_dim;
         if (L.out_dim > max_out) max_out = L.out_dim;
@@ -173,6 +175,8 @@ static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_
         a.bias = h->params + L.b_off;
         a.M = (int)(B * L.row_mult); a.N = L.out_dim; a.K = L.in_dim;
         a.k_per_split = round_up(L.in_dim, 8); a.splits = 1;
+        a.relu_bits = h->training ? h->relu_bits[l] : nullptr;
+        h->relu_bits_valid[l] = a.relu_bits != nullptr && sgemm_uses_tc(SGEMM_FWD, a);
         OCPPO_TRY(sgemm_launch(SGEMM_FWD, a, s));
         in = h->act[l];
     }
@@ -253,6 +257,9 @@ static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, i
             a.mask = h->act[l - 1];
             a.M = (int)rows; a.N = L.in_dim; a.K = L.out_dim;
             a.k_per_split = round_up(L.out_dim, 8); a.splits = 1;
+            // the layer below left its ReLU decisions as one bit per element (same row-major element order, so the
+            // encoder -> decoder flatten does not matter): the tensor-core dgrad reads those instead of the activations
+            if (h->relu_bits_valid[l - 1] && L.in_dim % 256 == 0) a.relu_bits = h->relu_bits[l - 1];
             OCPPO_TRY(sgemm_launch(SGEMM_DGRAD, a, s));
             cur ^= 1;
         }

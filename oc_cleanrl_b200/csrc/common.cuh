@@ -93,6 +93,8 @@ struct ocppo_handle {
     int training;
     float *x0;                          // gathered observations [max_rows*frames, obs_dim]
     float *act[2 * OCPPO_MAX_LAYERS];   // post-ReLU activations per trunk layer
+    uint32_t *relu_bits[2 * OCPPO_MAX_LAYERS];   // their ReLU decisions, one bit each (training workspaces)
+    int relu_bits_valid[2 * OCPPO_MAX_LAYERS];   // written by the last forward (tensor-core engine only)
     float *gbuf[2];                     // ping-pong gradient buffers
     float *gz;                          // head gradients [max_rows, AP]
     int32_t *mb_action;
@@ -118,6 +120,8 @@ struct SgemmArgs {
     float *C; int64_t ldc;
     const float *bias;        // FWD: [N]
     const float *mask;        // DGRAD: same layout as C; C = mask > 0 ? acc : 0
+    uint32_t *relu_bits;      // optional, [M, N/32] words, bit j of word w = (element 32 w + j > 0).  FWD on the tensor-core
+                              // engine writes them next to C; DGRAD reads them INSTEAD of `mask` (1/32 of the bytes)
     float *bias_part;         // WGRAD: [splits, M] column sums of A
     int M, N;
     int64_t K;                // contraction length (rows for WGRAD)
@@ -131,6 +135,7 @@ int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);      
 int fma_gemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);    // sgemm.cu, fp32 CUDA cores
 bool tc_gemm_supported(SgemmMode mode, const SgemmArgs &a);                      // tc_gemm.cu, tcgen05 3xTF32
 int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);
+bool sgemm_uses_tc(SgemmMode mode, const SgemmArgs &a);                          // what sgemm_launch will pick
 int tc_tile_n(bool single_acc);                                                   // N tile of the CTA pair: 128 (split accumulators) / 256
 // 0: fp32 FMA kernels only; 1: tcgen05 3xTF32 wherever the shape fits (fp32-grade accuracy; main and
 // correction products in separate TMEM accumulators); 2: same with a single, double-buffered accumulator

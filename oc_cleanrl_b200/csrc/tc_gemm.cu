@@ -54,9 +54,11 @@ constexpr int kStageBytesA = TM * TK * 4;                   // 16 KB
 constexpr int kRingBytes = 192 * 1024;                      // 3 x 64 KB or 4 x 48 KB
 constexpr int kMaxStages = 4;
 constexpr int kTmemCols = 512;                              // two tiles' accumulators
-constexpr int kEpiPadBytes = kEpiWarps * 32 * 33 * 4;       // per-warp 32 x 33 transpose pads
-constexpr int kBiasRedBytes = 8 * TM * 4;                   // WGRAD bias partials [8 k-lanes][128]
-constexpr int kTcSmemBytes = kRingBytes + kEpiPadBytes + kBiasRedBytes + 256 /*barriers*/ + 1024 /*align*/;
+constexpr int kEpiChunkBytes = 32 * 32 * 4;                 // one warp's 32 rows x 32 columns, SWIZZLE_128B
+constexpr int kEpiPadBytes = 2 * kEpiWarps * kEpiChunkBytes; // per warp: outgoing chunk + incoming aux chunk (32 KB)
+constexpr int kBiasRedBytes = 8 * TM * 2;                   // WGRAD bias partials [4 k-lane pairs][128] (2 KB)
+constexpr int kTcSmemBytes = kRingBytes + kEpiPadBytes + kBiasRedBytes + 256 /*barriers*/;   // base is 1024-aligned
+static_assert(kTcSmemBytes <= 232448, "shared memory budget (227 KB per CTA)");
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -212,6 +214,21 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *tm,
         : "memory");
 }
 
+// epilogue side: a finished 32 x 32 chunk leaves through a swizzled 4 KB smem tile and one bulk tensor store
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap *tm, uint32_t src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(reinterpret_cast<uint64_t>(tm)), "r"(src), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap *tm, int c0, int c1) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];"
+                 ::"l"(reinterpret_cast<uint64_t>(tm)), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 struct TileCoord { int m0, n0, split; int64_t kbeg, kend; int nk; };
 
 __device__ __forceinline__ TileCoord tile_coord(const SgemmArgs &p, int tile, int nt_n, int nt_m, int tn) {
@@ -251,7 +268,9 @@ __device__ __forceinline__ TileCoord tile_coord(const SgemmArgs &p, int tile, in
 
 template <int MODE, bool SPLIT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_gemm_kernel(SgemmArgs p, int nt_n, int nt_m, int ntiles, const __grid_constant__ CUtensorMap tmA,
-                                                                                         const __grid_constant__ CUtensorMap tmB) {
+                                                                                         const __grid_constant__ CUtensorMap tmB,
+                                                                                         const __grid_constant__ CUtensorMap tmC,
+                                                                                         const __grid_constant__ CUtensorMap tmX) {
     constexpr bool A_MN = (MODE == SGEMM_WGRAD);
     constexpr bool B_MN = (MODE != SGEMM_FWD);
     constexpr int TN = Tile<SPLIT>::TN, TBW = Tile<SPLIT>::TBW, kStageBytesB = Tile<SPLIT>::kStageBytesB;
@@ -262,14 +281,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
     // chained into one accumulator), so WGRAD, whose contraction runs over >= 10^4 rows, is cut into
     // 1024-row segments; each is drained by the epilogue and summed in fp32 round-to-nearest in fixed order.
     constexpr int kSegStages = (MODE == SGEMM_WGRAD) ? 32 : (1 << 30);
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    extern __shared__ __align__(1024) uint8_t smem[];       // SWIZZLE_128B tiles need 1024-byte aligned bases
+    if ((smem_u32(smem) & 1023u) != 0) __trap();
     float *epi_pad = reinterpret_cast<float *>(smem + kRingBytes);
     float *bias_red = reinterpret_cast<float *>(smem + kRingBytes + kEpiPadBytes);
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kRingBytes + kEpiPadBytes + kBiasRedBytes);
     // bars[0..3] full (used in the leader CTA), [4..7] empty, [8..9] tmem_full, [10..11] tmem_empty (leader),
-    // [12..15] tma (raw tile landed, per CTA)
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 16);
+    // [12..15] tma (raw tile landed, per CTA), [16..19] aux chunk landed (one per epilogue warp)
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 20);
+    const uint32_t bar_aux = smem_u32(&bars[16]);
     const uint32_t bar_tma = smem_u32(&bars[12]);
     const uint32_t bar_full = smem_u32(&bars[0]), bar_empty = smem_u32(&bars[4]);
     const uint32_t bar_tfull = smem_u32(&bars[8]), bar_tempty = smem_u32(&bars[10]);
@@ -289,6 +309,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
             mbar_init(bar_empty + 8 * s, 1);
             mbar_init(bar_tma + 8 * s, 1);
         }
+        for (int w = 0; w < kEpiWarps; ++w) mbar_init(bar_aux + 8 * w, 1);
         for (int a = 0; a < 2; ++a) {
             mbar_init(bar_tfull + 8 * a, 1);
             mbar_init(bar_tempty + 8 * a, 2 * kEpiWarps);    // both CTAs' epilogue warps
@@ -308,64 +329,83 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
 
     if (warp < kEpiWarps) {
         // ===================== epilogue =====================
-        float *pad = epi_pad + warp * 32 * 33;
+        // Per 32-column chunk: tcgen05.ld (lane = row, 32 consecutive columns in registers), bias/ReLU | ReLU mask |
+        // k-segment accumulate, 8 x STS.128 into this warp's SWIZZLE_128B tile (conflict-free: the 8 lanes of a
+        // quarter-warp hit 8 different 16-byte columns), one bulk tensor store.  Nothing waits for the store: the
+        // tile is only re-used after cp.async.bulk.wait_group.read.  The DGRAD mask / WGRAD running partial ("aux")
+        // arrives the same way in the other direction, one chunk ahead, after an L2 prefetch of the tile's rows
+        // issued before the accumulator is even complete.
+        uint8_t *out_tile = reinterpret_cast<uint8_t *>(epi_pad) + warp * kEpiChunkBytes;
+        uint8_t *aux_tile = reinterpret_cast<uint8_t *>(epi_pad) + (kEpiWarps + warp) * kEpiChunkBytes;
+        const uint32_t out_s = smem_u32(out_tile), aux_s = smem_u32(aux_tile), my_aux_bar = bar_aux + 8 * warp;
+        const int swz = lane & 7;
+        uint32_t aux_phase = 0;
         int ai = 0;                           // accumulator passes handled so far (tile x k-segment)
         for (int tile = cl; tile < ntiles; tile += ncl) {
           const TileCoord t = tile_coord(p, tile, nt_n, nt_m, TN);
           for (int kb0 = 0; kb0 < t.nk; kb0 += kSegStages, ++ai) {
             const int nbuf = (p.dbg & 4) ? 1 : kAccBufs, acc = ai % nbuf;
             const bool rmw = (MODE == SGEMM_WGRAD) && kb0 > 0;     // later k-segments add onto the first
+            const bool bits = (MODE == SGEMM_DGRAD) && p.relu_bits != nullptr;   // ReLU decisions as packed words
+            const bool aux = ((MODE == SGEMM_DGRAD) && !bits) || rmw;
+            const int m_loc = t.m0 + (int)cta_rank * TM + warp * 32;        // first of this warp's 32 rows
+            // WGRAD partial tiles are stacked [split][M][N] in one map: rows past M belong to the next split
+            const bool live = (MODE != SGEMM_WGRAD) || m_loc < p.M;
+            const int row0 = (MODE == SGEMM_WGRAD ? t.split * p.M : 0) + m_loc;
+            const CUtensorMap *tmAux = (MODE == SGEMM_DGRAD) ? &tmX : &tmC;
+            if (aux && live && lane == 0) {
+                if (rmw) {
+                    bulk_wait_all0();          // this warp's stores of the previous k-segment have landed
+                    asm volatile("fence.proxy.async;" ::: "memory");
+                } else {
+#pragma unroll
+                    for (int cc = 0; cc < TN / 32; ++cc) tma_prefetch_2d(tmAux, t.n0 + cc * 32, row0);
+                }
+                mbar_expect_tx(my_aux_bar, kEpiChunkBytes);
+                tma_load_2d(aux_s, tmAux, t.n0, row0, my_aux_bar);
+            }
+            // packed ReLU decisions of this lane's row: the tile's 256 columns are 8 words = 32 bytes, fetched before
+            // the accumulator is complete (DGRAD), or written chunk by chunk (FWD)
+            uint4 rb0 = make_uint4(0u, 0u, 0u, 0u), rb1 = rb0;
+            const int64_t rb_off = (int64_t)(m_loc + lane) * (p.N >> 5) + (t.n0 >> 5);
+            if (bits && m_loc + lane < p.M) {
+                rb0 = __ldg(reinterpret_cast<const uint4 *>(p.relu_bits + rb_off));
+                rb1 = __ldg(reinterpret_cast<const uint4 *>(p.relu_bits + rb_off) + 1);
+            }
             mbar_wait(bar_tfull + 8 * acc, (uint32_t)((ai / nbuf) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            float *Cb = p.C;
-            if (MODE == SGEMM_WGRAD) Cb += (int64_t)t.split * p.M * p.N;
-            const int m0c = t.m0 + (int)cta_rank * TM;          // this CTA's rows of the pair tile
-            const int r_sub = lane >> 3, col = (lane & 7) * 4;
-            // DGRAD: the ReLU mask of chunk cc+1 is fetched while chunk cc is drained (8 independent
-            // LDG.128 per lane in flight instead of one DRAM round trip per row group).  WGRAD k-segments
-            // after the first fetch the running partial the same way (written by this very thread).
-            float4 mk[8], mk_next[8];
-            auto load_mask = [&](int cc, float4 (&dst)[8]) {
-                const int n = t.n0 + cc * 32 + col;
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int m = m0c + warp * 32 + i * 4 + r_sub;
-                    if (m >= p.M) dst[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    else if (MODE == SGEMM_DGRAD) dst[i] = __ldg(reinterpret_cast<const float4 *>(p.mask + (int64_t)m * p.ldc + n));
-                    else dst[i] = __ldcg(reinterpret_cast<const float4 *>(Cb + (int64_t)m * p.ldc + n));
-                }
-            };
-            if (MODE == SGEMM_DGRAD) load_mask(0, mk_next);
+            if (!live) {
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive_on(bar_tempty + 8 * acc, 0);
+                continue;
+            }
 #pragma unroll 1
             for (int cc = 0; cc < TN / 32; ++cc) {
                 uint32_t v[32];
                 const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(acc * kAccStride + cc * 32);
                 OCPPO_TMEM_LD32(v, taddr);
-                if (split_acc) {               // main in the tile's columns [0,TN), corrections in [TN,2TN)
-                    if (MODE == SGEMM_DGRAD) {   // two halves: the mask prefetch leaves no room for 32 more registers
+                uint32_t w[32];
+                if (split_acc) OCPPO_TMEM_LD32(w, taddr + TN);      // main in columns [0,TN), corrections in [TN,2TN)
+                float4 ax[8];
+                if (aux) {
+                    mbar_wait(my_aux_bar, aux_phase);
+                    aux_phase ^= 1;
 #pragma unroll
-                        for (int hh = 0; hh < 2; ++hh) {
-                            uint32_t w[16];
-                            OCPPO_TMEM_LD16(w, taddr + TN + hh * 16);
-                            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    for (int c = 0; c < 8; ++c)
+                        ax[c] = *reinterpret_cast<const float4 *>(aux_tile + lane * 128 + ((c ^ swz) << 4));
+                    // The next chunk may only overwrite the tile once every lane's LDS has RETURNED (a bare __syncwarp
+                    // lets the bulk copy land while loads still sit in the LSU queue -- seen as stale mask words in
+                    // the last 16-byte column when the MMAs keep shared memory busy): make the issue depend on the data.
+                    uint32_t seen = 0;
 #pragma unroll
-                            for (int j = 0; j < 16; ++j)
-                                v[hh * 16 + j] = __float_as_uint(__uint_as_float(v[hh * 16 + j]) + __uint_as_float(w[j]));
-                        }
-                    } else {
-                        uint32_t w[32];
-                        OCPPO_TMEM_LD32(w, taddr + TN);
-                        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(w[j]));
+                    for (int c = 0; c < 8; ++c)
+                        seen |= __float_as_uint(ax[c].x) | __float_as_uint(ax[c].y) | __float_as_uint(ax[c].z) | __float_as_uint(ax[c].w);
+                    const uint32_t all_seen = __ballot_sync(0xffffffffu, seen != 0x7fc00001u);
+                    if (lane == 0 && all_seen != 0 && cc + 1 < TN / 32) {
+                        mbar_expect_tx(my_aux_bar, kEpiChunkBytes);
+                        tma_load_2d(aux_s, tmAux, t.n0 + (cc + 1) * 32, row0, my_aux_bar);
                     }
-                }
-                if (MODE == SGEMM_DGRAD) {
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) mk[i] = mk_next[i];
-                    if (cc + 1 < TN / 32) load_mask(cc + 1, mk_next);
-                } else if (rmw) {
-                    load_mask(cc, mk);         // L2-resident partial; single-buffered to stay within 128 registers
                 }
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                 if (cc == TN / 32 - 1) {       // accumulator drained: hand it back to the MMA warp
@@ -373,35 +413,53 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                     __syncwarp();
                     if (lane == 0) mbar_arrive_on(bar_tempty + 8 * acc, 0);
                 }
+                if (split_acc) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) pad[lane * 33 + j] = __uint_as_float(v[j]);
-                __syncwarp();
-                const int n = t.n0 + cc * 32 + col;
-                float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (MODE == SGEMM_FWD) bb = __ldg(reinterpret_cast<const float4 *>(p.bias + n));
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int row = i * 4 + r_sub;
-                    const int m = m0c + warp * 32 + row;
-                    const float *src = pad + row * 33 + col;
-                    float4 o = make_float4(src[0], src[1], src[2], src[3]);
-                    if (m < p.M && !(p.dbg & 2)) {
-                        if (MODE == SGEMM_FWD) {
-                            o.x = fmaxf(o.x + bb.x, 0.f); o.y = fmaxf(o.y + bb.y, 0.f);
-                            o.z = fmaxf(o.z + bb.z, 0.f); o.w = fmaxf(o.w + bb.w, 0.f);
-                        } else if (MODE == SGEMM_DGRAD) {
-                            o.x = mk[i].x > 0.f ? o.x : 0.f; o.y = mk[i].y > 0.f ? o.y : 0.f;
-                            o.z = mk[i].z > 0.f ? o.z : 0.f; o.w = mk[i].w > 0.f ? o.w : 0.f;
-                        } else if (rmw) {
-                            o.x += mk[i].x; o.y += mk[i].y; o.z += mk[i].z; o.w += mk[i].w;
-                        }
-                        *reinterpret_cast<float4 *>(Cb + (int64_t)m * p.ldc + n) = o;
-                    }
+                    for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(w[j]));
                 }
+                if (lane == 0) bulk_wait_read0();          // the previous chunk's store has read the tile
                 __syncwarp();
+                const int n = t.n0 + cc * 32;
+                uint32_t word = 0;
+                if (bits) {
+                    const uint4 q = cc < 4 ? rb0 : rb1;
+                    word = (cc & 2) ? ((cc & 1) ? q.w : q.z) : ((cc & 1) ? q.y : q.x);
+                }
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    float4 o = make_float4(__uint_as_float(v[4 * c]), __uint_as_float(v[4 * c + 1]),
+                                           __uint_as_float(v[4 * c + 2]), __uint_as_float(v[4 * c + 3]));
+                    if (MODE == SGEMM_FWD) {
+                        const float4 bb = __ldg(reinterpret_cast<const float4 *>(p.bias + n) + c);
+                        o.x = fmaxf(o.x + bb.x, 0.f); o.y = fmaxf(o.y + bb.y, 0.f);
+                        o.z = fmaxf(o.z + bb.z, 0.f); o.w = fmaxf(o.w + bb.w, 0.f);
+                        if (p.relu_bits != nullptr)
+                            word |= ((o.x > 0.f ? 1u : 0u) | (o.y > 0.f ? 2u : 0u) | (o.z > 0.f ? 4u : 0u) | (o.w > 0.f ? 8u : 0u)) << (4 * c);
+                    } else if (MODE == SGEMM_DGRAD) {
+                        if (bits) {
+                            const uint32_t nib = word >> (4 * c);
+                            o.x = (nib & 1u) ? o.x : 0.f; o.y = (nib & 2u) ? o.y : 0.f;
+                            o.z = (nib & 4u) ? o.z : 0.f; o.w = (nib & 8u) ? o.w : 0.f;
+                        } else {
+                            o.x = ax[c].x > 0.f ? o.x : 0.f; o.y = ax[c].y > 0.f ? o.y : 0.f;
+                            o.z = ax[c].z > 0.f ? o.z : 0.f; o.w = ax[c].w > 0.f ? o.w : 0.f;
+                        }
+                    } else if (rmw) {
+                        o.x += ax[c].x; o.y += ax[c].y; o.z += ax[c].z; o.w += ax[c].w;
+                    }
+                    *reinterpret_cast<float4 *>(out_tile + lane * 128 + ((c ^ swz) << 4)) = o;
+                }
+                if (MODE == SGEMM_FWD && p.relu_bits != nullptr && m_loc + lane < p.M) p.relu_bits[rb_off + cc] = word;
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (lane == 0 && !(p.dbg & 2)) {
+                    tma_store_2d(&tmC, out_s, n, row0);
+                    bulk_commit();
+                }
             }
           }
         }
+        if (lane == 0) bulk_wait_all0();       // all stores of this warp complete before the CTA may exit
     } else if (warp < 2 * kEpiWarps) {
         // ===================== MMA issuer (warp 4; warps 5-7 idle) =====================
         if (warp == kEpiWarps && lane == 0 && cta_rank == 0) {
@@ -497,13 +555,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
             }
             if (MODE == SGEMM_WGRAD) {
                 if (do_bias) {           // tile-uniform across the producer warps
-                    // [8 k-lanes][128 columns]; thread pt holds columns (pt % 32) * 4.. of k-lane pt / 32
-                    *reinterpret_cast<float4 *>(bias_red + (pt >> 5) * TM + (pt & 31) * 4) = bsum;
+                    // thread pt holds columns (pt % 32) * 4.. of k-lane pt / 32; [4][128] floats: k-lanes 4-7 first,
+                    // k-lanes 0-3 add onto them
+                    float4 *slot = reinterpret_cast<float4 *>(bias_red + ((pt >> 5) & 3) * TM + (pt & 31) * 4);
+                    if ((pt >> 5) >= 4) *slot = bsum;
+                    asm volatile("bar.sync 1, %0;" ::"n"(kProdThreads) : "memory");
+                    if ((pt >> 5) < 4) {
+                        const float4 o = *slot;
+                        *slot = make_float4(o.x + bsum.x, o.y + bsum.y, o.z + bsum.z, o.w + bsum.w);
+                    }
                     asm volatile("bar.sync 1, %0;" ::"n"(kProdThreads) : "memory");
                     if (pt < TM) {
                         float sum = 0.f;
 #pragma unroll
-                        for (int kr = 0; kr < 8; ++kr) sum += bias_red[kr * TM + pt];
+                        for (int kr = 0; kr < 4; ++kr) sum += bias_red[kr * TM + pt];
                         if (t.m0 + rank_m + pt < p.M) p.bias_part[(int64_t)t.split * p.M + t.m0 + rank_m + pt] = sum;
                     }
                     asm volatile("bar.sync 1, %0;" ::"n"(kProdThreads) : "memory");
@@ -585,6 +650,21 @@ int make_map(CUtensorMap *tm, const float *base, bool mn_major, int64_t rows_or_
     return OCPPO_OK;
 }
 
+// Output (and aux: DGRAD mask, WGRAD running partial) [rows, cols] row-major: 2-D map {cols, rows}, box 32 x 32,
+// SWIZZLE_128B -- one epilogue warp's chunk.  Rows past `rows` are clipped on store and zero-filled on load.
+int make_map_c(CUtensorMap *tm, const float *base, int64_t rows, int64_t cols, int64_t ld) {
+    EncodeTiledFn fn = encode_fn();
+    if (fn == nullptr) { set_error("cuTensorMapEncodeTiled entry point not available"); return OCPPO_ECUDA; }
+    const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+    const cuuint32_t box[2] = {32, 32}, estr[2] = {1, 1};
+    const CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (output map) failed (%d)", (int)r); return OCPPO_ECUDA; }
+    return OCPPO_OK;
+}
+
 }  // namespace
 
 int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
@@ -599,7 +679,7 @@ int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
     const int64_t ntiles64 = (int64_t)nt_n * nt_m * splits;
     OCPPO_CHECK_ARG(ntiles64 < (1LL << 31), "tc_gemm: too many tiles");
     const int ntiles = (int)ntiles64;
-    typedef void (*Kern)(SgemmArgs, int, int, int, const CUtensorMap, const CUtensorMap);
+    typedef void (*Kern)(SgemmArgs, int, int, int, const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap);
     static const Kern kerns[2][3] = {
         {tc_gemm_kernel<SGEMM_FWD, false>, tc_gemm_kernel<SGEMM_DGRAD, false>, tc_gemm_kernel<SGEMM_WGRAD, false>},
         {tc_gemm_kernel<SGEMM_FWD, true>, tc_gemm_kernel<SGEMM_DGRAD, true>, tc_gemm_kernel<SGEMM_WGRAD, true>}};
@@ -613,12 +693,15 @@ int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
                 OCPPO_CUDA(cudaFuncSetAttribute(kerns[i][j], cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
     }
     const int grid = 2 * (ntiles < sms / 2 ? ntiles : sms / 2);     // CTA pairs
-    CUtensorMap tmA, tmB;
+    CUtensorMap tmA, tmB, tmC, tmX;
     OCPPO_TRY(make_map(&tmA, a.A, mode == SGEMM_WGRAD, a.M, a.K, a.lda, TM));
     OCPPO_TRY(make_map(&tmB, a.B, mode != SGEMM_FWD, a.N, a.K, a.ldb, tn / 2));
+    OCPPO_TRY(make_map_c(&tmC, a.C, (int64_t)a.M * splits, a.N, a.ldc));
+    if (mode == SGEMM_DGRAD) OCPPO_TRY(make_map_c(&tmX, a.mask, a.M, a.N, a.ldc));
+    else tmX = tmC;
     const int mi = mode == SGEMM_FWD ? 0 : (mode == SGEMM_DGRAD ? 1 : 2);
     ProfScope ps(mode == SGEMM_FWD ? KC_SGEMM_FWD : (mode == SGEMM_DGRAD ? KC_SGEMM_DGRAD : KC_SGEMM_WGRAD), 1, stream);
-    kerns[split ? 1 : 0][mi]<<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles, tmA, tmB);
+    kerns[split ? 1 : 0][mi]<<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles, tmA, tmB, tmC, tmX);
     OCPPO_LAUNCH_CHECK("tc_gemm_kernel");
     return OCPPO_OK;
 }
