@@ -280,7 +280,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
     // The TMEM accumulator adds with truncation (measured: error grows linearly with the number of MMAs
     // chained into one accumulator), so WGRAD, whose contraction runs over >= 10^4 rows, is cut into
     // 1024-row segments; each is drained by the epilogue and summed in fp32 round-to-nearest in fixed order.
-    constexpr int kSegStages = (MODE == SGEMM_WGRAD) ? 32 : (1 << 30);
+    constexpr int kSegStages = (MODE == SGEMM_WGRAD) ? 64 : (1 << 30);
     extern __shared__ __align__(1024) uint8_t smem[];       // SWIZZLE_128B tiles need 1024-byte aligned bases
     if ((smem_u32(smem) & 1023u) != 0) __trap();
     float *epi_pad = reinterpret_cast<float *>(smem + kRingBytes);
