@@ -46,17 +46,19 @@ template <bool SPLIT> struct Tile {
 };
 constexpr int TK = 32;
 constexpr int kPairM = 2 * TM;                              // 256-row tile per CTA pair
-constexpr int kEpiWarps = 4, kProdWarps = 8;
-constexpr int kProdThreads = kProdWarps * 32;               // 256
-constexpr int kProdTid0 = 256;                              // warpgroups 2-3
-constexpr int kTcThreads = kProdTid0 + kProdThreads;        // 512 = 4 warpgroups (setmaxnreg is per warpgroup)
+// 16 warps: 0-7 epilogue (two per TMEM lane quarter, each half of the tile's columns), 8 MMA issuer, 9 TMA issuer,
+// 10-11 idle, 12-15 lo-tile producers
+constexpr int kEpiWarps = 8, kProdWarps = 4;
+constexpr int kProdThreads = kProdWarps * 32;               // 128
+constexpr int kProdTid0 = 384;
+constexpr int kTcThreads = kProdTid0 + kProdThreads;        // 512
 constexpr int kStageBytesA = TM * TK * 4;                   // 16 KB
 constexpr int kRingBytes = 192 * 1024;                      // 3 x 64 KB or 4 x 48 KB
 constexpr int kMaxStages = 4;
 constexpr int kTmemCols = 512;                              // two tiles' accumulators
 constexpr int kEpiChunkBytes = 32 * 32 * 4;                 // one warp's 32 rows x 32 columns, SWIZZLE_128B
-constexpr int kEpiPadBytes = 2 * kEpiWarps * kEpiChunkBytes; // per warp: outgoing chunk + incoming aux chunk (32 KB)
-constexpr int kBiasRedBytes = 8 * TM * 2;                   // WGRAD bias partials [4 k-lane pairs][128] (2 KB)
+constexpr int kEpiPadBytes = kEpiWarps * kEpiChunkBytes;    // per warp: one chunk, incoming aux then outgoing result (32 KB)
+constexpr int kBiasRedBytes = kProdWarps * TM * 4;          // WGRAD bias partials [4 k-lanes][128] (2 KB)
 constexpr int kTcSmemBytes = kRingBytes + kEpiPadBytes + kBiasRedBytes + 256 /*barriers*/;   // base is 1024-aligned
 static_assert(kTcSmemBytes <= 232448, "shared memory budget (227 KB per CTA)");
 
@@ -152,49 +154,42 @@ __device__ __forceinline__ float4 lo4(const float4 &v) {
     return make_float4(lo_of(v.x), lo_of(v.y), lo_of(v.z), lo_of(v.w));
 }
 // offsets of the 4 chunks thread p owns in a 16 KB operand tile
-// K-major tile of 128 rows x 32 floats (SWIZZLE_128B): 8 threads per row, 32 rows per pass.
+// K-major tile of 128 rows x 32 floats (SWIZZLE_128B): 8 threads per row, 16 rows per pass.
 __device__ __forceinline__ int off_kmajor(int p, int q) {
-    const int row = q * 32 + (p >> 3), c = p & 7;
+    const int row = q * 16 + (p >> 3), c = p & 7;
     return row * 128 + ((c ^ (row & 7)) << 4);
 }
 // MN-major tile of 32 k-rows x 128 floats (4 chunks of [32 k][32 floats], SWIZZLE_128B_BASE32B).  Thread p
-// owns the 4 columns (p % 32) * 4.. in k-rows p / 32 + 8 q (so its values sum into one float4 of column sums).
+// owns the 4 columns (p % 32) * 4.. in k-rows p / 32 + 4 q (so its values sum into one float4 of column sums).
 __device__ __forceinline__ int off_mnmajor(int p, int q) {
-    const int g = p & 31, k = q * 8 + (p >> 5);
+    const int g = p & 31, k = q * 4 + (p >> 5);
     const int mb = g >> 3, c = g & 7;
     return mb * 4096 + k * 128 + ((((c >> 1) ^ (k & 3)) << 5) | ((c & 1) << 4));
 }
-// 64-column MN-major tile (2 chunks of [32 k][32 floats]): 16 threads per k-row, k-rows p / 16 + 16 q, q < 2.
-__device__ __forceinline__ int off_mnmajor64(int p, int q) {
-    const int g = p & 15, k = q * 16 + (p >> 4);
-    const int mb = g >> 3, c = g & 7;
-    return mb * 4096 + k * 128 + ((((c >> 1) ^ (k & 3)) << 5) | ((c & 1) << 4));
-}
-// One stage: read this thread's raw chunks (4 of A, BW/32 of B) first, then derive and store the lo chunks.
-// (A 64-row K-major B tile is the first two passes of off_kmajor.)
+// One stage: this thread's 8 raw chunks of A, then of B: read, derive lo, store (two batches of 8 loads in flight).
 template <bool A_MN, bool B_MN, bool SUM, int BW>
 __device__ __forceinline__ void convert_stage(const uint8_t *a_hi, uint8_t *a_lo, const uint8_t *b_hi, uint8_t *b_lo,
                                               int p, float4 &colsum) {
-    constexpr int NB = BW / 32;
-    int oa[4], ob[NB];
-    float4 va[4], vb[NB];
+    static_assert(BW == 128, "B tile width");
+    int o[8];
+    float4 v[8];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        oa[q] = A_MN ? off_mnmajor(p, q) : off_kmajor(p, q);
-        va[q] = *reinterpret_cast<const float4 *>(a_hi + oa[q]);
+    for (int q = 0; q < 8; ++q) {
+        o[q] = A_MN ? off_mnmajor(p, q) : off_kmajor(p, q);
+        v[q] = *reinterpret_cast<const float4 *>(a_hi + o[q]);
     }
 #pragma unroll
-    for (int q = 0; q < NB; ++q) {
-        ob[q] = B_MN ? (BW == 128 ? off_mnmajor(p, q) : off_mnmajor64(p, q)) : off_kmajor(p, q);
-        vb[q] = *reinterpret_cast<const float4 *>(b_hi + ob[q]);
+    for (int q = 0; q < 8; ++q) {
+        if (SUM) { colsum.x += v[q].x; colsum.y += v[q].y; colsum.z += v[q].z; colsum.w += v[q].w; }
+        *reinterpret_cast<float4 *>(a_lo + o[q]) = lo4(v[q]);
     }
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        if (SUM) { colsum.x += va[q].x; colsum.y += va[q].y; colsum.z += va[q].z; colsum.w += va[q].w; }
-        *reinterpret_cast<float4 *>(a_lo + oa[q]) = lo4(va[q]);
+    for (int q = 0; q < 8; ++q) {
+        o[q] = B_MN ? off_mnmajor(p, q) : off_kmajor(p, q);
+        v[q] = *reinterpret_cast<const float4 *>(b_hi + o[q]);
     }
 #pragma unroll
-    for (int q = 0; q < NB; ++q) *reinterpret_cast<float4 *>(b_lo + ob[q]) = lo4(vb[q]);
+    for (int q = 0; q < 8; ++q) *reinterpret_cast<float4 *>(b_lo + o[q]) = lo4(v[q]);
 }
 
 // ---- TMA ----------------------------------------------------------------------
@@ -287,8 +282,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
     float *bias_red = reinterpret_cast<float *>(smem + kRingBytes + kEpiPadBytes);
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kRingBytes + kEpiPadBytes + kBiasRedBytes);
     // bars[0..3] full (used in the leader CTA), [4..7] empty, [8..9] tmem_full, [10..11] tmem_empty (leader),
-    // [12..15] tma (raw tile landed, per CTA), [16..19] aux chunk landed (one per epilogue warp)
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 20);
+    // [12..15] tma (raw tile landed, per CTA), [16..23] aux chunk landed (one per epilogue warp)
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 24);
     const uint32_t bar_aux = smem_u32(&bars[16]);
     const uint32_t bar_tma = smem_u32(&bars[12]);
     const uint32_t bar_full = smem_u32(&bars[0]), bar_empty = smem_u32(&bars[4]);
@@ -329,15 +324,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
 
     if (warp < kEpiWarps) {
         // ===================== epilogue =====================
-        // Per 32-column chunk: tcgen05.ld (lane = row, 32 consecutive columns in registers), bias/ReLU | ReLU mask |
-        // k-segment accumulate, 8 x STS.128 into this warp's SWIZZLE_128B tile (conflict-free: the 8 lanes of a
-        // quarter-warp hit 8 different 16-byte columns), one bulk tensor store.  Nothing waits for the store: the
-        // tile is only re-used after cp.async.bulk.wait_group.read.  The DGRAD mask / WGRAD running partial ("aux")
-        // arrives the same way in the other direction, one chunk ahead, after an L2 prefetch of the tile's rows
-        // issued before the accumulator is even complete.
+        // Warp w drains TMEM lanes 32 (w % 4).. (its rows) of the column half w / 4, one 32-column chunk at a time:
+        // tcgen05.ld (lane = row, 32 consecutive columns in registers), bias/ReLU | ReLU decision bits | k-segment
+        // accumulate, 8 x STS.128 into the warp's SWIZZLE_128B tile (conflict-free: the 8 lanes of a quarter-warp hit
+        // 8 different 16-byte columns), one bulk tensor store.  Nothing waits for a store; the tile is re-used after
+        // cp.async.bulk.wait_group.read.  Two warps share each SM sub-partition and hide each other's latencies.
+        // "aux" = fp32 ReLU mask (DGRAD without decision bits) or the running partial (WGRAD k-segments after the
+        // first): it arrives by TMA in the same tile, is read to registers, and the result overwrites it.
+        const int quarter = warp & 3, chalf = warp >> 2;
+        constexpr int kChunks = TN / 64;                     // chunks per warp
         uint8_t *out_tile = reinterpret_cast<uint8_t *>(epi_pad) + warp * kEpiChunkBytes;
-        uint8_t *aux_tile = reinterpret_cast<uint8_t *>(epi_pad) + (kEpiWarps + warp) * kEpiChunkBytes;
-        const uint32_t out_s = smem_u32(out_tile), aux_s = smem_u32(aux_tile), my_aux_bar = bar_aux + 8 * warp;
+        const uint32_t out_s = smem_u32(out_tile), my_aux_bar = bar_aux + 8 * warp;
         const int swz = lane & 7;
         uint32_t aux_phase = 0;
         int ai = 0;                           // accumulator passes handled so far (tile x k-segment)
@@ -348,7 +345,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
             const bool rmw = (MODE == SGEMM_WGRAD) && kb0 > 0;     // later k-segments add onto the first
             const bool bits = (MODE == SGEMM_DGRAD) && p.relu_bits != nullptr;   // ReLU decisions as packed words
             const bool aux = ((MODE == SGEMM_DGRAD) && !bits) || rmw;
-            const int m_loc = t.m0 + (int)cta_rank * TM + warp * 32;        // first of this warp's 32 rows
+            const int m_loc = t.m0 + (int)cta_rank * TM + quarter * 32;     // first of this warp's 32 rows
+            const int n_loc = t.n0 + chalf * (TN / 2);                      // first of this warp's columns
             // WGRAD partial tiles are stacked [split][M][N] in one map: rows past M belong to the next split
             const bool live = (MODE != SGEMM_WGRAD) || m_loc < p.M;
             const int row0 = (MODE == SGEMM_WGRAD ? t.split * p.M : 0) + m_loc;
@@ -358,20 +356,18 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                     bulk_wait_all0();          // this warp's stores of the previous k-segment have landed
                     asm volatile("fence.proxy.async;" ::: "memory");
                 } else {
+                    bulk_wait_read0();
 #pragma unroll
-                    for (int cc = 0; cc < TN / 32; ++cc) tma_prefetch_2d(tmAux, t.n0 + cc * 32, row0);
+                    for (int cc = 1; cc < kChunks; ++cc) tma_prefetch_2d(tmAux, n_loc + cc * 32, row0);
                 }
                 mbar_expect_tx(my_aux_bar, kEpiChunkBytes);
-                tma_load_2d(aux_s, tmAux, t.n0, row0, my_aux_bar);
+                tma_load_2d(out_s, tmAux, n_loc, row0, my_aux_bar);
             }
-            // packed ReLU decisions of this lane's row: the tile's 256 columns are 8 words = 32 bytes, fetched before
+            // packed ReLU decisions of this lane's row: the warp's 128 columns are 4 words = 16 bytes, fetched before
             // the accumulator is complete (DGRAD), or written chunk by chunk (FWD)
-            uint4 rb0 = make_uint4(0u, 0u, 0u, 0u), rb1 = rb0;
-            const int64_t rb_off = (int64_t)(m_loc + lane) * (p.N >> 5) + (t.n0 >> 5);
-            if (bits && m_loc + lane < p.M) {
-                rb0 = __ldg(reinterpret_cast<const uint4 *>(p.relu_bits + rb_off));
-                rb1 = __ldg(reinterpret_cast<const uint4 *>(p.relu_bits + rb_off) + 1);
-            }
+            uint4 rb = make_uint4(0u, 0u, 0u, 0u);
+            const int64_t rb_off = (int64_t)(m_loc + lane) * (p.N >> 5) + (n_loc >> 5);
+            if (bits && m_loc + lane < p.M) rb = __ldg(reinterpret_cast<const uint4 *>(p.relu_bits + rb_off));
             mbar_wait(bar_tfull + 8 * acc, (uint32_t)((ai / nbuf) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             if (!live) {
@@ -381,9 +377,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                 continue;
             }
 #pragma unroll 1
-            for (int cc = 0; cc < TN / 32; ++cc) {
+            for (int cc = 0; cc < kChunks; ++cc) {
                 uint32_t v[32];
-                const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(acc * kAccStride + cc * 32);
+                const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) +
+                                       (uint32_t)(acc * kAccStride + chalf * (TN / 2) + cc * 32);
                 OCPPO_TMEM_LD32(v, taddr);
                 uint32_t w[32];
                 if (split_acc) OCPPO_TMEM_LD32(w, taddr + TN);      // main in columns [0,TN), corrections in [TN,2TN)
@@ -393,22 +390,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                     aux_phase ^= 1;
 #pragma unroll
                     for (int c = 0; c < 8; ++c)
-                        ax[c] = *reinterpret_cast<const float4 *>(aux_tile + lane * 128 + ((c ^ swz) << 4));
-                    // The next chunk may only overwrite the tile once every lane's LDS has RETURNED (a bare __syncwarp
-                    // lets the bulk copy land while loads still sit in the LSU queue -- seen as stale mask words in
-                    // the last 16-byte column when the MMAs keep shared memory busy): make the issue depend on the data.
-                    uint32_t seen = 0;
-#pragma unroll
-                    for (int c = 0; c < 8; ++c)
-                        seen |= __float_as_uint(ax[c].x) | __float_as_uint(ax[c].y) | __float_as_uint(ax[c].z) | __float_as_uint(ax[c].w);
-                    const uint32_t all_seen = __ballot_sync(0xffffffffu, seen != 0x7fc00001u);
-                    if (lane == 0 && all_seen != 0 && cc + 1 < TN / 32) {
-                        mbar_expect_tx(my_aux_bar, kEpiChunkBytes);
-                        tma_load_2d(aux_s, tmAux, t.n0 + (cc + 1) * 32, row0, my_aux_bar);
-                    }
+                        ax[c] = *reinterpret_cast<const float4 *>(out_tile + lane * 128 + ((c ^ swz) << 4));
+                } else if (lane == 0) {
+                    bulk_wait_read0();         // the previous chunk's store has read the tile
                 }
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                if (cc == TN / 32 - 1) {       // accumulator drained: hand it back to the MMA warp
+                if (cc == kChunks - 1) {       // accumulator drained: hand it back to the MMA warp
                     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                     __syncwarp();
                     if (lane == 0) mbar_arrive_on(bar_tempty + 8 * acc, 0);
@@ -417,14 +404,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(w[j]));
                 }
-                if (lane == 0) bulk_wait_read0();          // the previous chunk's store has read the tile
                 __syncwarp();
-                const int n = t.n0 + cc * 32;
+                const int n = n_loc + cc * 32;
                 uint32_t word = 0;
-                if (bits) {
-                    const uint4 q = cc < 4 ? rb0 : rb1;
-                    word = (cc & 2) ? ((cc & 1) ? q.w : q.z) : ((cc & 1) ? q.y : q.x);
-                }
+                if (bits) word = (cc & 2) ? ((cc & 1) ? rb.w : rb.z) : ((cc & 1) ? rb.y : rb.x);
+                // each lane reads (aux) and writes only its own row of the tile, and every value written depends on
+                // the aux value read from the same place, so no lane can overwrite data that is still to be read
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
                     float4 o = make_float4(__uint_as_float(v[4 * c]), __uint_as_float(v[4 * c + 1]),
@@ -452,16 +437,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                 if (MODE == SGEMM_FWD && p.relu_bits != nullptr && m_loc + lane < p.M) p.relu_bits[rb_off + cc] = word;
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
-                if (lane == 0 && !(p.dbg & 2)) {
-                    tma_store_2d(&tmC, out_s, n, row0);
-                    bulk_commit();
+                if (lane == 0) {
+                    if (!(p.dbg & 2)) {
+                        tma_store_2d(&tmC, out_s, n, row0);
+                        bulk_commit();
+                    }
+                    if (aux && cc + 1 < kChunks) {           // next aux chunk, once the store has read the tile
+                        bulk_wait_read0();
+                        mbar_expect_tx(my_aux_bar, kEpiChunkBytes);
+                        tma_load_2d(out_s, tmAux, n + 32, row0, my_aux_bar);
+                    }
                 }
             }
           }
         }
         if (lane == 0) bulk_wait_all0();       // all stores of this warp complete before the CTA may exit
-    } else if (warp < 2 * kEpiWarps) {
-        // ===================== MMA issuer (warp 4; warps 5-7 idle) =====================
+    } else if (warp < kEpiWarps + 4) {
+        // ===================== MMA issuer (warp 8; warps 10-11 idle) =====================
         if (warp == kEpiWarps && lane == 0 && cta_rank == 0) {
             constexpr uint32_t idesc = make_idesc(kPairM, TN, A_MN, B_MN);   // M = 256 across the pair
             // K-major: SBO = 8-row group stride (1024 B), LBO unused.  MN-major: LBO = stride between
@@ -509,7 +501,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
             }
         }
         else if (warp == kEpiWarps + 1 && lane == 0) {
-            // ===================== TMA issuer (warp 5, both CTAs) =====================
+            // ===================== TMA issuer (warp 9, both CTAs) =====================
             // raw fp32 tiles of this CTA's A rows / B columns, straight into the hi slots of the stage ring
             const int rank_m = (int)cta_rank * TM, rank_n = (int)cta_rank * TBW;
             int stage = 0, sphase = 0;
@@ -555,20 +547,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
             }
             if (MODE == SGEMM_WGRAD) {
                 if (do_bias) {           // tile-uniform across the producer warps
-                    // thread pt holds columns (pt % 32) * 4.. of k-lane pt / 32; [4][128] floats: k-lanes 4-7 first,
-                    // k-lanes 0-3 add onto them
-                    float4 *slot = reinterpret_cast<float4 *>(bias_red + ((pt >> 5) & 3) * TM + (pt & 31) * 4);
-                    if ((pt >> 5) >= 4) *slot = bsum;
-                    asm volatile("bar.sync 1, %0;" ::"n"(kProdThreads) : "memory");
-                    if ((pt >> 5) < 4) {
-                        const float4 o = *slot;
-                        *slot = make_float4(o.x + bsum.x, o.y + bsum.y, o.z + bsum.z, o.w + bsum.w);
-                    }
+                    // [4 k-lanes][128 columns]; thread pt holds columns (pt % 32) * 4.. of k-lane pt / 32
+                    *reinterpret_cast<float4 *>(bias_red + (pt >> 5) * TM + (pt & 31) * 4) = bsum;
                     asm volatile("bar.sync 1, %0;" ::"n"(kProdThreads) : "memory");
                     if (pt < TM) {
                         float sum = 0.f;
 #pragma unroll
-                        for (int kr = 0; kr < 4; ++kr) sum += bias_red[kr * TM + pt];
+                        for (int kr = 0; kr < kProdWarps; ++kr) sum += bias_red[kr * TM + pt];
                         if (t.m0 + rank_m + pt < p.M) p.bias_part[(int64_t)t.split * p.M + t.m0 + rank_m + pt] = sum;
                     }
                     asm volatile("bar.sync 1, %0;" ::"n"(kProdThreads) : "memory");
