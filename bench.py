@@ -46,8 +46,9 @@ def parse():
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--gae-sweep", default="4096,16384,65536")
-    p.add_argument("--gemm", default="tc", choices=["fma", "tc", "tc-fast"],
-                   help="trunk GEMM engine: fp32 CUDA-core FMA or tcgen05 3xTF32 (fp32-grade)")
+    p.add_argument("--gemm", default="tc", choices=["fma", "tc", "tc-3xtf32", "tc-fast"],
+                   help="trunk GEMM engine: fp32 CUDA-core FMA | tcgen05 TF32 main product + two BF16 correction products "
+                        "(library default) | tcgen05 3xTF32 | 3xTF32 with a single accumulator")
     return p.parse_args()
 
 
@@ -276,7 +277,7 @@ def run_b200(a):
     torch.cuda.set_device(dev)
     ocd.init_process_group(world, "nccl")
     lib = _abi.lib()
-    assert lib.ocppo_set_gemm_mode({"fma": 0, "tc": 1, "tc-fast": 2}[a.gemm]) == 0
+    assert lib.ocppo_set_gemm_mode({"fma": 0, "tc": 3, "tc-3xtf32": 1, "tc-fast": 2}[a.gemm]) == 0
     D, A = GAME_SHAPES[a.game]
     T, N = a.num_steps, a.num_envs
     pk = peaks()

@@ -91,12 +91,16 @@ int ocppo_profile_read(double *ms_by_class, int64_t *timed_by_class, int32_t n_c
 int ocppo_measure_fma_peak(double *tflops, void *stream);
 
 /* ---- GEMM engine selection + raw GEMM (tests / measurement) -------------- */
-/* The trunk GEMMs (nn.Linear forward, dgrad, wgrad of architectures/ppo.py:70-84)
- * run either on fp32 CUDA-core FMA kernels (mode 0) or on tcgen05 tensor cores
- * with a 3-pass TF32 split that keeps fp32-grade accuracy (mode 1, used wherever
- * the shape fits the 256x256x32 CTA-pair tile; other shapes stay on FMA).  Mode 2
- * is mode 1 with a single TMEM accumulator per tile: ~13 % faster, ~3x the rounding
- * error (the accumulator rounds toward zero).  Process-wide; default 1. */
+/* The trunk GEMMs (nn.Linear forward, dgrad, wgrad of architectures/ppo.py:70-84) run on one of four engines
+ * (process-wide switch; shapes outside the 256x256x32 CTA-pair tile grid always use engine 0):
+ *   0  fp32 CUDA-core FMA kernels (exact fp32 products);
+ *   1  tcgen05 tensor cores, 3xTF32: x = hi + lo, hi.hi + hi.lo + lo.hi, fp32 accumulate in TMEM, main and correction
+ *      products in separate accumulators (the TMEM accumulator rounds toward zero);
+ *   2  as 1 with a single accumulator per tile: ~10 % faster, ~3x the rounding error;
+ *   3  (default) as 1, but the two correction products run as BF16 MMAs at twice the TF32 rate:
+ *      trunc_tf32(a).trunc_tf32(b) + bf16(a - trunc_tf32(a)).bf16(b) + bf16(a).bf16(b - trunc_tf32(b)).
+ *      Per-product error <= 2^-19, zero-mean, measured 1.4e-6 .. 4.6e-6 of the result's max-norm on the trunk shapes
+ *      (engine 1: 5e-6 .. 6e-6, both dominated by the accumulator); every parity test holds the same 1e-4 bar. */
 int ocppo_set_gemm_mode(int32_t mode);
 int ocppo_get_gemm_mode(void);
 /* One GEMM of the family.  op 0: C[M,N] = relu(A[M,K] B[N,K]^T + bias[N]);

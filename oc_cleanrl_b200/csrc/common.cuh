@@ -129,6 +129,7 @@ struct SgemmArgs {
     int splits;
     int dbg;                  // tc_gemm bring-up variant (0 in production)
     int single_acc;           // tc_gemm: 1 = one TMEM accumulator per tile (faster, ~3x the rounding error)
+    int corr_bf16;            // tc_gemm: 1 = the two correction products run as BF16 MMAs (split accumulators only)
 };
 
 int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);       // dispatches FMA / tensor

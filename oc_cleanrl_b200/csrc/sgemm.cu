@@ -190,7 +190,7 @@ int dispatch(const SgemmArgs &a, bool av, bool bv, dim3 grid, cudaStream_t s) {
 
 }  // namespace
 
-int g_gemm_mode = 1;   // tcgen05 3xTF32 with split accumulators; see ocppo_set_gemm_mode
+int g_gemm_mode = 3;   // tcgen05: TF32 main product + two BF16 correction products; see ocppo_set_gemm_mode
 
 static int tc_ops_mask() {
     static const int ops_mask = getenv("OCPPO_TC_OPS") ? atoi(getenv("OCPPO_TC_OPS")) : 7;   // bring-up: bit per op
@@ -201,6 +201,7 @@ bool sgemm_uses_tc(SgemmMode mode, const SgemmArgs &a) {
     if (g_gemm_mode < 1 || !((tc_ops_mask() >> (int)mode) & 1)) return false;
     SgemmArgs b = a;
     b.single_acc = g_gemm_mode == 2;
+    b.corr_bf16 = g_gemm_mode == 3;
     return tc_gemm_supported(mode, b);
 }
 
@@ -208,6 +209,7 @@ int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream) {
     if (sgemm_uses_tc(mode, a)) {
         SgemmArgs b = a;
         b.single_acc = g_gemm_mode == 2;
+        b.corr_bf16 = g_gemm_mode == 3;
         return tc_gemm_launch(mode, b, stream);
     }
     OCPPO_CHECK_ARG(mode != SGEMM_DGRAD || a.mask != nullptr, "sgemm: the FMA dgrad kernel needs the fp32 mask");

@@ -134,6 +134,20 @@ __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint6
         ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// kind::f16 instruction descriptor with BF16 A/B and F32 accumulate (K = 16 per instruction)
+__host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, bool a_mn_major, bool b_mn_major) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn_major ? 1u : 0u) << 15) | ((b_mn_major ? 1u : 0u) << 16) |
+           ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 // arrives (count 1) on the barrier at this smem offset in BOTH CTAs once all prior MMAs have completed
 __device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
@@ -190,6 +204,45 @@ __device__ __forceinline__ void convert_stage(const uint8_t *a_hi, uint8_t *a_lo
     }
 #pragma unroll
     for (int q = 0; q < 8; ++q) *reinterpret_cast<float4 *>(b_lo + o[q]) = lo4(v[q]);
+}
+
+// ---- BF16 correction operands -----------------------------------------------------------------------------
+// The two correction products only have to be good to 2^-9 of THEIR magnitude (2^-11 of the main product's):
+//   a.b ~= trunc_tf32(a).trunc_tf32(b)  [kind::tf32 on the raw tile]  +  bf16(a - trunc_tf32(a)).bf16(b)
+//        + bf16(a).bf16(b - trunc_tf32(b))                               [kind::f16, twice the TF32 rate],
+// worst-case 2^-19, typically 3e-7 relative per product with zero mean -- about fp32's own dot-product error
+// (tests/test_gpu_gemm.py holds it to 2e-5 of the result's max-norm at every trunk shape).
+// Tiles: K-major [128 rows][32 k] bf16 = 64-byte rows, SWIZZLE_64B (16-byte unit u of row r at u ^ ((r >> 1) & 3));
+// MN-major [2 chunks][32 k][64 bf16] = 128-byte rows, SWIZZLE_128B (unit u of k-row k at u ^ (k & 7)).
+__device__ __forceinline__ uint32_t pack_bf16(float lo_elem, float hi_elem) {
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi_elem), "f"(lo_elem));
+    return r;
+}
+__device__ __forceinline__ float resid_tf32(float x) { return x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
+// byte offset of this thread's 4 consecutive elements (8 bytes) in the bf16 tile, for the raw chunk (p, q)
+__device__ __forceinline__ int off16_kmajor(int p, int q) {
+    const int row = q * 16 + (p >> 3), c = p & 7;
+    return row * 64 + ((((c >> 1) ^ (row >> 1)) & 3) << 4) + ((c & 1) << 3);
+}
+__device__ __forceinline__ int off16_mnmajor(int p, int q) {
+    const int g = p & 31, k = q * 4 + (p >> 5);
+    const int e = g * 4;                                   // first MN element of the chunk, 0..124
+    return (e >> 6) * 4096 + k * 128 + (((((e & 63) >> 3) ^ (k & 7))) << 4) + (((e >> 2) & 1) << 3);
+}
+template <bool MN, bool SUM>
+__device__ __forceinline__ void convert_operand_bf16(const uint8_t *raw, uint8_t *full16, uint8_t *lo16, int p, float4 &colsum) {
+    float4 v[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) v[q] = *reinterpret_cast<const float4 *>(raw + (MN ? off_mnmajor(p, q) : off_kmajor(p, q)));
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        if (SUM) { colsum.x += v[q].x; colsum.y += v[q].y; colsum.z += v[q].z; colsum.w += v[q].w; }
+        const int o = MN ? off16_mnmajor(p, q) : off16_kmajor(p, q);
+        *reinterpret_cast<uint2 *>(full16 + o) = make_uint2(pack_bf16(v[q].x, v[q].y), pack_bf16(v[q].z, v[q].w));
+        *reinterpret_cast<uint2 *>(lo16 + o) = make_uint2(pack_bf16(resid_tf32(v[q].x), resid_tf32(v[q].y)),
+                                                          pack_bf16(resid_tf32(v[q].z), resid_tf32(v[q].w)));
+    }
 }
 
 // ---- TMA ----------------------------------------------------------------------
@@ -261,7 +314,7 @@ __device__ __forceinline__ TileCoord tile_coord(const SgemmArgs &p, int tile, in
         : "r"(taddr)                                                                                                \
         : "memory")
 
-template <int MODE, bool SPLIT>
+template <int MODE, bool SPLIT, bool CORR16>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_gemm_kernel(SgemmArgs p, int nt_n, int nt_m, int ntiles, const __grid_constant__ CUtensorMap tmA,
                                                                                          const __grid_constant__ CUtensorMap tmB,
                                                                                          const __grid_constant__ CUtensorMap tmC,
@@ -271,6 +324,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
     constexpr int TN = Tile<SPLIT>::TN, TBW = Tile<SPLIT>::TBW, kStageBytesB = Tile<SPLIT>::kStageBytesB;
     constexpr int kStageBytes = Tile<SPLIT>::kStageBytes, kNumStages = Tile<SPLIT>::kNumStages;
     constexpr int kAccStride = Tile<SPLIT>::kAccStride, kAccBufs = Tile<SPLIT>::kAccBufs;
+    // stage layout.  3xTF32: [A raw = hi 16K][A lo 16K][B raw = hi 16K][B lo 16K];
+    // CORR16:  [A raw 16K][B raw 16K][A bf16 8K][A lo bf16 8K][B bf16 8K][B lo bf16 8K]
+    constexpr int kOffA = 0, kOffB = CORR16 ? kStageBytesA : 2 * kStageBytesA;
+    constexpr int kOffALo = CORR16 ? 2 * kStageBytesA + kStageBytesA / 2 : kStageBytesA;
+    constexpr int kOffBLo = CORR16 ? 3 * kStageBytesA + kStageBytesB / 2 : 2 * kStageBytesA + kStageBytesB;
+    constexpr int kOffA16 = 2 * kStageBytesA, kOffB16 = 3 * kStageBytesA;     // CORR16 only
+    static_assert(!CORR16 || SPLIT, "bf16 corrections go to their own accumulator");
     static_assert(kNumStages * kStageBytes <= kRingBytes && kNumStages <= kMaxStages, "stage ring");
     // The TMEM accumulator adds with truncation (measured: error grows linearly with the number of MMAs
     // chained into one accumulator), so WGRAD, whose contraction runs over >= 10^4 rows, is cut into
@@ -477,10 +537,32 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                     if (++stage == kNumStages) { stage = 0; sphase ^= 1; }
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     uint8_t *st = smem + s * kStageBytes;
-                    const uint32_t a_hi = smem_u32(st), a_lo = a_hi + kStageBytesA;
-                    const uint32_t b_hi = a_hi + 2 * kStageBytesA, b_lo = b_hi + kStageBytesB;
-                    const uint64_t da_hi = make_desc(a_hi, a_lbo, a_sbo, a_ty), da_lo = make_desc(a_lo, a_lbo, a_sbo, a_ty);
-                    const uint64_t db_hi = make_desc(b_hi, b_lbo, b_sbo, b_ty), db_lo = make_desc(b_lo, b_lbo, b_sbo, b_ty);
+                    const uint32_t a_hi = smem_u32(st) + kOffA, a_lo = smem_u32(st) + kOffALo;
+                    const uint32_t b_hi = smem_u32(st) + kOffB, b_lo = smem_u32(st) + kOffBLo;
+                    const uint64_t da_hi = make_desc(a_hi, a_lbo, a_sbo, a_ty), db_hi = make_desc(b_hi, b_lbo, b_sbo, b_ty);
+                    if (CORR16) {
+                        // bf16 tiles: K-major SWIZZLE_64B (8-row groups 512 B apart, k-step of 16 = 32 B inside the row);
+                        // MN-major SWIZZLE_128B (64-element chunks 4096 B apart, 8-k-row groups 1024 B, k-step = 2048 B)
+                        constexpr uint32_t a16_lbo = A_MN ? 4096 : 16, a16_sbo = A_MN ? 1024 : 512, a16_ty = A_MN ? 2 : 4;
+                        constexpr uint32_t b16_lbo = B_MN ? 4096 : 16, b16_sbo = B_MN ? 1024 : 512, b16_ty = B_MN ? 2 : 4;
+                        constexpr uint64_t a16_step = (A_MN ? 2048 : 32) >> 4, b16_step = (B_MN ? 2048 : 32) >> 4;
+                        constexpr uint32_t idesc16 = make_idesc_bf16(kPairM, TN, A_MN, B_MN);
+                        const uint64_t da16 = make_desc(smem_u32(st) + kOffA16, a16_lbo, a16_sbo, a16_ty);
+                        const uint64_t db16 = make_desc(smem_u32(st) + kOffB16, b16_lbo, b16_sbo, b16_ty);
+                        const uint64_t da16lo = make_desc(a_lo, a16_lbo, a16_sbo, a16_ty);
+                        const uint64_t db16lo = make_desc(b_lo, b16_lbo, b16_sbo, b16_ty);
+#pragma unroll
+                        for (int ks = 0; ks < TK / 8; ++ks)
+                            umma_tf32(d_tmem, da_hi + ks * a_step, db_hi + ks * b_step, idesc, (kb > kb0 || ks > 0) ? 1u : 0u);
+#pragma unroll
+                        for (int k2 = 0; k2 < TK / 16; ++k2) {
+                            umma_bf16(d_tmem + TN, da16lo + k2 * a16_step, db16 + k2 * b16_step, idesc16, (kb > kb0 || k2 > 0) ? 1u : 0u);
+                            umma_bf16(d_tmem + TN, da16 + k2 * a16_step, db16lo + k2 * b16_step, idesc16, 1u);
+                        }
+                        umma_commit_pair(bar_empty + 8 * s);
+                        continue;
+                    }
+                    const uint64_t da_lo = make_desc(a_lo, a_lbo, a_sbo, a_ty), db_lo = make_desc(b_lo, b_lbo, b_sbo, b_ty);
 #pragma unroll
                     for (int ks = 0; ks < TK / 8; ++ks) {
                         const uint32_t acc0 = (kb > kb0 || ks > 0) ? 1u : 0u;
@@ -510,7 +592,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                 for (int kb = 0; kb < t.nk; ++kb) {
                     const int s = stage;
                     mbar_wait(bar_empty + 8 * s, (uint32_t)(sphase ^ 1));
-                    const uint32_t a_hi = smem_u32(smem + s * kStageBytes), b_hi = a_hi + 2 * kStageBytesA;
+                    const uint32_t a_hi = smem_u32(smem + s * kStageBytes) + kOffA, b_hi = smem_u32(smem + s * kStageBytes) + kOffB;
                     const uint32_t bar = bar_tma + 8 * s;
                     const int k0 = (int)(t.kbeg + (int64_t)kb * TK);
                     mbar_expect_tx(bar, kStageBytesA + kStageBytesB);
@@ -537,8 +619,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                 const int s = stage;
                 mbar_wait(bar_tma + 8 * s, (uint32_t)sphase);           // raw tile landed (TMA complete_tx)
                 uint8_t *st = smem + s * kStageBytes;
-                uint8_t *a_hi = st, *a_lo = st + kStageBytesA, *b_hi = st + 2 * kStageBytesA, *b_lo = b_hi + kStageBytesB;
-                if (A_MN && do_bias) convert_stage<A_MN, B_MN, true, TBW>(a_hi, a_lo, b_hi, b_lo, pt, bsum);
+                uint8_t *a_hi = st + kOffA, *a_lo = st + kOffALo, *b_hi = st + kOffB, *b_lo = st + kOffBLo;
+                if (CORR16) {
+                    if (A_MN && do_bias) convert_operand_bf16<A_MN, true>(a_hi, st + kOffA16, a_lo, pt, bsum);
+                    else convert_operand_bf16<A_MN, false>(a_hi, st + kOffA16, a_lo, pt, bsum);
+                    convert_operand_bf16<B_MN, false>(b_hi, st + kOffB16, b_lo, pt, bsum);
+                } else if (A_MN && do_bias) convert_stage<A_MN, B_MN, true, TBW>(a_hi, a_lo, b_hi, b_lo, pt, bsum);
                 else convert_stage<A_MN, B_MN, false, TBW>(a_hi, a_lo, b_hi, b_lo, pt, bsum);
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
@@ -665,15 +751,16 @@ int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
     OCPPO_CHECK_ARG(ntiles64 < (1LL << 31), "tc_gemm: too many tiles");
     const int ntiles = (int)ntiles64;
     typedef void (*Kern)(SgemmArgs, int, int, int, const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap);
-    static const Kern kerns[2][3] = {
-        {tc_gemm_kernel<SGEMM_FWD, false>, tc_gemm_kernel<SGEMM_DGRAD, false>, tc_gemm_kernel<SGEMM_WGRAD, false>},
-        {tc_gemm_kernel<SGEMM_FWD, true>, tc_gemm_kernel<SGEMM_DGRAD, true>, tc_gemm_kernel<SGEMM_WGRAD, true>}};
+    static const Kern kerns[3][3] = {
+        {tc_gemm_kernel<SGEMM_FWD, false, false>, tc_gemm_kernel<SGEMM_DGRAD, false, false>, tc_gemm_kernel<SGEMM_WGRAD, false, false>},
+        {tc_gemm_kernel<SGEMM_FWD, true, false>, tc_gemm_kernel<SGEMM_DGRAD, true, false>, tc_gemm_kernel<SGEMM_WGRAD, true, false>},
+        {tc_gemm_kernel<SGEMM_FWD, true, true>, tc_gemm_kernel<SGEMM_DGRAD, true, true>, tc_gemm_kernel<SGEMM_WGRAD, true, true>}};
     static int sms = 0;
     if (sms == 0) {
         int dev = 0;
         OCPPO_CUDA(cudaGetDevice(&dev));
         OCPPO_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        for (int i = 0; i < 2; ++i)
+        for (int i = 0; i < 3; ++i)
             for (int j = 0; j < 3; ++j)
                 OCPPO_CUDA(cudaFuncSetAttribute(kerns[i][j], cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
     }
@@ -686,7 +773,7 @@ int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
     else tmX = tmC;
     const int mi = mode == SGEMM_FWD ? 0 : (mode == SGEMM_DGRAD ? 1 : 2);
     ProfScope ps(mode == SGEMM_FWD ? KC_SGEMM_FWD : (mode == SGEMM_DGRAD ? KC_SGEMM_DGRAD : KC_SGEMM_WGRAD), 1, stream);
-    kerns[split ? 1 : 0][mi]<<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles, tmA, tmB, tmC, tmX);
+    kerns[split ? (a.corr_bf16 ? 2 : 1) : 0][mi]<<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles, tmA, tmB, tmC, tmX);
     OCPPO_LAUNCH_CHECK("tc_gemm_kernel");
     return OCPPO_OK;
 }

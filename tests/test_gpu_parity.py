@@ -27,12 +27,13 @@ def dev(built_lib):
     return torch.device("cuda:0")
 
 
-@pytest.fixture(params=["fma", "tc"])
+@pytest.fixture(params=["fma", "tc", "tc16"])
 def gemm_engine(request, built_lib):
-    """Runs the test once per trunk GEMM engine: fp32 CUDA-core FMA and tcgen05 3xTF32."""
-    assert built_lib.ocppo_set_gemm_mode(1 if request.param == "tc" else 0) == 0
-    yield request.param
-    built_lib.ocppo_set_gemm_mode(1)
+    """Runs the test once per trunk GEMM engine: fp32 CUDA-core FMA, tcgen05 3xTF32, tcgen05 TF32 + BF16 corrections."""
+    default = built_lib.ocppo_get_gemm_mode()
+    assert built_lib.ocppo_set_gemm_mode({"fma": 0, "tc": 1, "tc16": 3}[request.param]) == 0
+    yield "tc" if request.param == "tc16" else request.param
+    built_lib.ocppo_set_gemm_mode(default)
 
 
 def _stream(dev):
