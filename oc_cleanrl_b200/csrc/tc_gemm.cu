@@ -105,6 +105,9 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     }
 }
 
+// (nanosleep back-off in the long waits was measured too: the eight epilogue warps polling tmem_full issue 95 % of
+// the kernel's instructions, yet sleeping between polls changes nothing, and 32 ns in the TMA issuer's wait costs
+// DGRAD 10 % -- the mainloop is bound by the latency of the empty -> TMA -> convert -> full loop, not by issue slots.)
 // 64-bit shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout).
 // layout_type: 2 = SWIZZLE_128B (K-major tiles), 1 = SWIZZLE_128B_BASE32B -- the only
 // layout the hardware takes for MN-major 32-bit (tf32) operands.
@@ -342,8 +345,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
     float *bias_red = reinterpret_cast<float *>(smem + kRingBytes + kEpiPadBytes);
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kRingBytes + kEpiPadBytes + kBiasRedBytes);
     // bars[0..3] full (used in the leader CTA), [4..7] empty, [8..9] tmem_full, [10..11] tmem_empty (leader),
-    // [12..15] tma (raw tile landed, per CTA), [16..23] aux chunk landed (one per epilogue warp)
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 24);
+    // [12..15] tma (raw tile landed, per CTA), [16..23] aux chunk landed (one per epilogue warp),
+    // [24..27] raw_full (leader: raw tiles of BOTH CTAs landed -- the main product needs nothing else)
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 28);
+    const uint32_t bar_rawfull = smem_u32(&bars[24]);
     const uint32_t bar_aux = smem_u32(&bars[16]);
     const uint32_t bar_tma = smem_u32(&bars[12]);
     const uint32_t bar_full = smem_u32(&bars[0]), bar_empty = smem_u32(&bars[4]);
@@ -363,6 +368,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
             mbar_init(bar_full + 8 * s, 2 * kProdWarps);     // both CTAs' producer warps
             mbar_init(bar_empty + 8 * s, 1);
             mbar_init(bar_tma + 8 * s, 1);
+            mbar_init(bar_rawfull + 8 * s, 2);               // one forwarder per CTA
         }
         for (int w = 0; w < kEpiWarps; ++w) mbar_init(bar_aux + 8 * w, 1);
         for (int a = 0; a < 2; ++a) {
@@ -532,8 +538,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                 const uint32_t d_tmem = tmem_base + (uint32_t)(acc * kAccStride);
                 const int kb1 = (t.nk - kb0 < kSegStages) ? t.nk : kb0 + kSegStages;
                 for (int kb = kb0; kb < kb1; ++kb) {
-                    const int s = stage;
-                    mbar_wait(bar_full + 8 * s, (uint32_t)sphase);
+                    // The main product reads only the raw tiles: it starts as soon as both CTAs' TMA loads have landed
+                    // and runs while the producers are still deriving the correction operands of the same stage.
+                    const int s = stage, fphase = sphase;
+                    mbar_wait(bar_rawfull + 8 * s, (uint32_t)fphase);
                     if (++stage == kNumStages) { stage = 0; sphase ^= 1; }
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     uint8_t *st = smem + s * kStageBytes;
@@ -554,6 +562,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
 #pragma unroll
                         for (int ks = 0; ks < TK / 8; ++ks)
                             umma_tf32(d_tmem, da_hi + ks * a_step, db_hi + ks * b_step, idesc, (kb > kb0 || ks > 0) ? 1u : 0u);
+                        mbar_wait(bar_full + 8 * s, (uint32_t)fphase);      // the producers' bf16 tiles
+                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
                         for (int k2 = 0; k2 < TK / 16; ++k2) {
                             umma_bf16(d_tmem + TN, da16lo + k2 * a16_step, db16 + k2 * b16_step, idesc16, (kb > kb0 || k2 > 0) ? 1u : 0u);
@@ -564,17 +574,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                     }
                     const uint64_t da_lo = make_desc(a_lo, a_lbo, a_sbo, a_ty), db_lo = make_desc(b_lo, b_lbo, b_sbo, b_ty);
 #pragma unroll
+                    for (int ks = 0; ks < TK / 8; ++ks)
+                        umma_tf32(d_tmem, da_hi + ks * a_step, db_hi + ks * b_step, idesc, (kb > kb0 || ks > 0) ? 1u : 0u);
+                    mbar_wait(bar_full + 8 * s, (uint32_t)fphase);          // the producers' lo tiles
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t d_corr = split_acc ? d_tmem + TN : d_tmem;
+#pragma unroll
                     for (int ks = 0; ks < TK / 8; ++ks) {
-                        const uint32_t acc0 = (kb > kb0 || ks > 0) ? 1u : 0u;
-                        if (split_acc) {
-                            umma_tf32(d_tmem + TN, da_lo + ks * a_step, db_hi + ks * b_step, idesc, acc0);
-                            umma_tf32(d_tmem + TN, da_hi + ks * a_step, db_lo + ks * b_step, idesc, 1u);
-                            umma_tf32(d_tmem, da_hi + ks * a_step, db_hi + ks * b_step, idesc, acc0);
-                        } else {
-                            umma_tf32(d_tmem, da_lo + ks * a_step, db_hi + ks * b_step, idesc, acc0);
-                            umma_tf32(d_tmem, da_hi + ks * a_step, db_lo + ks * b_step, idesc, 1u);
-                            umma_tf32(d_tmem, da_hi + ks * a_step, db_hi + ks * b_step, idesc, 1u);
-                        }
+                        umma_tf32(d_corr, da_lo + ks * a_step, db_hi + ks * b_step, idesc, (!split_acc || kb > kb0 || ks > 0) ? 1u : 0u);
+                        umma_tf32(d_corr, da_hi + ks * a_step, db_lo + ks * b_step, idesc, 1u);
                     }
                     umma_commit_pair(bar_empty + 8 * s);     // stage free (in both CTAs) once these MMAs have read it
                 }
@@ -600,6 +608,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                     else tma_load_2d(a_hi, &tmA, k0, t.m0 + rank_m, bar);
                     if (B_MN) tma_load_3d(b_hi, &tmB, 0, k0, (t.n0 + rank_n) >> 5, bar);
                     else tma_load_2d(b_hi, &tmB, k0, t.n0 + rank_n, bar);
+                    if (++stage == kNumStages) { stage = 0; sphase ^= 1; }
+                }
+            }
+        }
+        else if (warp == kEpiWarps + 2 && lane == 0) {
+            // ===================== raw-tile forwarder (warp 10, both CTAs) =====================
+            // tells the leader's MMA issuer that this CTA's raw tiles of a stage have landed
+            int stage = 0, sphase = 0;
+            for (int tile = cl; tile < ntiles; tile += ncl) {
+                const TileCoord t = tile_coord(p, tile, nt_n, nt_m, TN);
+                for (int kb = 0; kb < t.nk; ++kb) {
+                    mbar_wait(bar_tma + 8 * stage, (uint32_t)sphase);
+                    mbar_arrive_on(bar_rawfull + 8 * stage, 0);
                     if (++stage == kNumStages) { stage = 0; sphase ^= 1; }
                 }
             }
