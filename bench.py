@@ -28,9 +28,9 @@ import torch  # noqa: E402
 
 ENC, DEC = (256, 512, 1024, 512), (512,)
 FRAMES = 4
-# dram__bytes_read.sum + dram__bytes_write.sum of one tc_gemm_kernel<FWD> launch (M=131072, N=512, K=1024) from the
-# ncu --set full capture summarised in profiles/ (algorithmic bytes of that launch: 807 MB)
-TRAFFIC_BYTES_PER_LAUNCH = None
+# dram__bytes_read.sum + dram__bytes_write.sum of one tc_gemm_kernel<FWD> launch (M=524288, N=512, K=1024) from the
+# ncu --set full capture profiles/r01_tc3_ncu_full.txt (algorithmic bytes of that launch: 3.22 GB)
+TRAFFIC_BYTES_PER_LAUNCH = 3196000000
 
 
 def parse():
@@ -379,20 +379,24 @@ def run_b200(a):
     tc = a.gemm != "fma"
     roofline = {"bound": "tensor", "achieved": gemm_tflops, "peak": pk["bf16_sustained"], "unit": "TFLOP/s",
                 "frac": gemm_tflops / pk["bf16_sustained"], "traffic": TRAFFIC_BYTES_PER_LAUNCH if tc else None,
-                "kernel": ("tc_gemm_kernel<FWD|DGRAD|WGRAD> (tcgen05.mma cta_group::2 kind::tf32, 3-pass split for fp32-grade "
-                           "accuracy, TMA-fed, TMEM accumulators) + the skinny first-layer/head kernels" if tc else
-                           "sgemm_kernel (fp32 CUDA-core FMA; fwd+dgrad+wgrad launches of the trunk)"),
+                "kernel": ("tc_gemm_kernel<FWD|DGRAD|WGRAD> (tcgen05.mma cta_group::2: TF32 main product + " +
+                           ("two BF16 correction products" if a.gemm == "tc" else "two TF32 correction products") +
+                           ", TMA-fed, TMEM accumulators, bulk-tensor-store epilogue) + the skinny first-layer/head kernels"
+                           if tc else "sgemm_kernel (fp32 CUDA-core FMA; fwd+dgrad+wgrad launches of the trunk)"),
                 "peak_source": pk["source"] + ", bf16 dense sustained",
                 "share_of_step": gemm_ms / ms_per_step,
                 "launches_per_step": (prof_n["sgemm_fwd"] + prof_n["sgemm_dgrad"] + prof_n["sgemm_wgrad"]) / a.steps,
                 "flops_per_step": gemm_flops,
                 "achieved_is": "ALGORITHMIC fp32-equivalent FLOPs (2*M*N*K per GEMM, SURVEY 8d) / CUDA-event time of the GEMM launches"}
     if tc:
-        # every algorithmic MAC is issued three times at TF32 rate (= half the bf16 rate): 6 bf16-equivalent MACs
-        roofline["tensor_pipe"] = {"issued_tf32_tflops": 3.0 * gemm_tflops, "tf32_peak_est": pk["bf16_sustained"] / 2.0,
-                                   "frac_of_tf32_peak_est": 6.0 * gemm_tflops / pk["bf16_sustained"],
-                                   "note": "fp32-grade accuracy costs 3 TF32 passes; TF32 runs at half the bf16 rate, so "
-                                           "frac = achieved/peak is bounded by 1/6 = 0.167 at full tensor-pipe occupancy"}
+        # bf16-equivalent MMA work issued per algorithmic MAC: a TF32 pass costs 2 (half the bf16 rate), a BF16 pass 1
+        units = 4.0 if a.gemm == "tc" else 6.0
+        roofline["tensor_pipe"] = {"bf16_equivalent_tflops_issued": units * gemm_tflops, "peak": pk["bf16_sustained"],
+                                   "frac_of_peak": units * gemm_tflops / pk["bf16_sustained"],
+                                   "note": ("fp32-grade accuracy costs one TF32 pass (2 bf16-equivalents) plus " +
+                                            ("two BF16 correction passes" if a.gemm == "tc" else "two TF32 correction passes") +
+                                            f": {units:.0f} bf16-equivalent MACs per algorithmic MAC, so frac = achieved/peak is "
+                                            f"bounded by 1/{units:.0f} = {1.0 / units:.3f} at full tensor-pipe occupancy")}
     else:
         roofline["note"] = "fp32-exact FMA path: the tensor roofline is the ceiling the tcgen05 (3xTF32) trunk is held to"
     roofline_fma = {"bound": "fma", "achieved": gemm_tflops, "peak": fma.value, "unit": "TFLOP/s",
