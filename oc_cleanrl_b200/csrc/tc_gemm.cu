@@ -1,25 +1,25 @@
-// fp32-grade GEMM on the 5th-gen tensor cores: tcgen05.mma kind::tf32, three passes
-// (a_lo*b_hi + a_hi*b_lo + a_hi*b_hi, with a = a_hi + a_lo split to TF32 precision),
-// fp32 accumulation in TMEM.  Same three contractions as sgemm.cu:
+// fp32-grade GEMM on the 5th-gen tensor cores (tcgen05.mma, fp32 accumulation in TMEM).  Every operand is split
+// x = hi + lo with hi = trunc_tf32(x); the product is hi.hi (kind::tf32, straight from the raw fp32 tile: the hardware
+// truncates) plus two correction products -- as BF16 MMAs (engine 3, default: bf16(a-hi_a).bf16(b) + bf16(a).bf16(b-hi_b))
+// or as TF32 MMAs (engines 1, 2: lo.hi + hi.lo).  Same three contractions as sgemm.cu:
 //   FWD   : Y[M,N]  = relu(X[M,K] . W[N,K]^T + b[N])      A K-major,  B K-major
 //   DGRAD : dX[M,N] = (mask > 0) * (dY[M,K] . W[K,N])      A K-major,  B MN-major
 //   WGRAD : dW[M,N] = dY[K,M]^T . X[K,N]  (split-K)        A MN-major, B MN-major
 //
 // Persistent, warp-specialised, CTA-pair kernel: a cluster of two CTAs (one SM each, same TPC) walks
 // 256 x 256 output tiles with tcgen05.mma.cta_group::2.  Each CTA stages its own 128 rows of A and its own
-// 128 columns of B (so the pair fetches every operand byte once), and holds the 128 x 256 fp32 accumulator of
-// its rows in its own TMEM.  Per CTA:
-//   warps 0-3   epilogue : tcgen05.ld the finished accumulator, bias/ReLU or ReLU-mask, transpose
-//                          through a per-warp smem pad, 128 B-coalesced STG
-//   warp  4     MMA      : one thread of the LEADER CTA issues the pair's MMAs; accumulators are
-//                          double-buffered in TMEM (2 x 256 columns) so the epilogue of tile i overlaps
-//                          the mainloop of tile i+1
-//   warps 5-7   idle (pad the MMA warp to a warpgroup so setmaxnreg can move registers to the producers)
-//   warps 8-15  producers: LDG.128 -> registers (two k-blocks in flight) -> hi/lo split -> STS into
-//                          the canonical UMMA layouts (K-major: SWIZZLE_128B, MN-major tf32:
-//                          SWIZZLE_128B_BASE32B), 3 stages x 64 KB
-// Hand-offs are mbarriers: full (leader CTA; both CTAs' producers arrive, the peer's remotely) / empty per
-// smem stage and tmem_full / tmem_empty per accumulator; tcgen05.commit multicasts to both CTAs.
+// 128 columns of B (so the pair fetches every operand byte once), and holds the 128 x 256 fp32 accumulators of
+// its rows in its own TMEM (main product in columns 0-255, corrections in 256-511).  Per CTA, 16 warps:
+//   warps 0-7   epilogue : two per TMEM lane quarter; tcgen05.ld, main + corrections, bias/ReLU | ReLU decision |
+//                          k-segment accumulate, STS into a swizzled 4 KB tile, one bulk tensor store per 32 x 32 chunk
+//   warp  8     MMA      : one thread of the LEADER CTA issues the pair's MMAs: the main product as soon as the raw
+//                          tiles of both CTAs have landed, the corrections when the producers are done
+//   warp  9     TMA      : one thread per CTA loads the raw fp32 tiles (2-D maps for K-major operands, 3-D maps with
+//                          SWIZZLE_128B_ATOM_32B for MN-major ones: nothing is ever transposed in memory)
+//   warp  10    forwarder: tells the leader that this CTA's raw tiles have landed
+//   warps 12-15 producers: read the raw tiles back and write the correction operands in the canonical UMMA layouts
+// Three 64 KB stages.  Hand-offs are mbarriers: tma (per CTA), raw_full / full (leader; both CTAs arrive, the peer
+// remotely), empty (tcgen05.commit multicast to both CTAs), tmem_full / tmem_empty per accumulator.
 #include "common.cuh"
 #include <cuda.h>
 #include <stdlib.h>
@@ -105,6 +105,8 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     }
 }
 
+// (Releasing the raw tiles of a stage to the TMA right after the main product -- half a stage earlier than the
+// converted tiles -- was measured as well: no gain.)
 // (nanosleep back-off in the long waits was measured too: the eight epilogue warps polling tmem_full issue 95 % of
 // the kernel's instructions, yet sleeping between polls changes nothing, and 32 ns in the TMA issuer's wait costs
 // DGRAD 10 % -- the mainloop is bound by the latency of the empty -> TMA -> convert -> full loop, not by issue slots.)
