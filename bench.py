@@ -262,6 +262,24 @@ def time_gae_isolated(dev, T, N, iters=200, min_bytes=192 << 20):
     return us
 
 
+def time_policy_step(agent, dev, D, n_envs, iters=10):
+    """Rollout inference (ppo_atari_oc.py:505-509): one fused trunk + head + Philox sample call over `n_envs`
+    observations already on the device; average ms per call with CUDA events."""
+    obs = torch.randint(0, 200, (n_envs, FRAMES, D), device=dev).float()
+    torch.cuda.manual_seed(1)
+    with torch.no_grad():
+        for _ in range(3):
+            agent.get_action_and_value(obs)
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            agent.get_action_and_value(obs)
+        e1.record()
+        torch.cuda.synchronize(dev)
+    return e0.elapsed_time(e1) / iters
+
+
 def run_b200(a):
     from oc_cleanrl_b200 import _abi
     from oc_cleanrl_b200 import distributed as ocd
@@ -414,6 +432,16 @@ def run_b200(a):
         roofline_gae = {"bound": "hbm", "achieved": own["GB/s"], "peak": pk["hbm"], "unit": "GB/s", "frac": own["frac"],
                         "traffic": None, "kernel": "gae_scan_kernel", "peak_source": pk["source"], "sweep": sweep}
     kernel_ms = {k: v / a.steps for k, v in prof_ms.items() if v > 0}
+    # rollout inference over the same sweep (BASELINE configs[4]); the trunk is 11.55 MFLOP per observation against
+    # 116 bytes in and out, so it is held to the tensor roofline like the update, not to HBM
+    inference = []
+    units = 4.0 if a.gemm == "tc" else (6.0 if tc else None)
+    for n in [int(x) for x in a.gae_sweep.split(",") if x]:
+        ms = time_policy_step(agent, dev, D, n)
+        tf = 2.0 * trunk_macs(D) * n / (ms * 1e-3) / 1e12
+        inference.append({"num_envs": n, "ms_per_call": ms, "obs_per_s": n / (ms * 1e-3), "TFLOP/s": tf,
+                          "frac_of_bf16_peak": tf / pk["bf16_sustained"],
+                          "tensor_pipe_frac": units * tf / pk["bf16_sustained"] if units else None})
 
     cpu_baseline = None
     if world.world_size == 1 and not a.no_cpu_baseline:
@@ -427,7 +455,7 @@ def run_b200(a):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(a, world.world_size),
         "roofline": roofline, "roofline_fma": roofline_fma, "roofline_gae": roofline_gae,
-        "kernel_ms_per_step": kernel_ms, "cpu_baseline": cpu_baseline, "e2e": e2e,
+        "inference": inference, "kernel_ms_per_step": kernel_ms, "cpu_baseline": cpu_baseline, "e2e": e2e,
         "gpu_launches": int(launches), "clocks": clocks,
         "last_stats": {k: last[k] for k in ("loss", "pg_loss", "v_loss", "entropy", "approx_kl", "grad_norm")},
         "impl": "b200",

@@ -87,18 +87,52 @@ __device__ __forceinline__ void warp_head_forward(const float *__restrict__ h, c
     }
 }
 
+// HV > 0: H == 128 * HV, the hidden row is read once with 16-byte loads (next row prefetched); HV == 0: any H.
+template <int HV>
 __global__ void __launch_bounds__(kHeadThreads)
 policy_head_kernel(const float *__restrict__ hidden, int64_t B, int H, int A, const float *Wa, const float *ba,
                    const float *Wc, const float *bc, PhiloxLayout L, int64_t row_base,
                    const int64_t *__restrict__ given, int64_t *__restrict__ action, float *__restrict__ logp,
                    float *__restrict__ entropy, float *__restrict__ value, int want_policy) {
-    extern __shared__ float sm[];
+    extern __shared__ __align__(16) float sm[];
     float *sW = sm, *sB = sm + (size_t)(A + 1) * H;
     stage_head_weights(sW, sB, Wa, ba, Wc, bc, A, H);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int64_t i = (int64_t)blockIdx.x * kWarpsPerBlock + warp; i < B; i += (int64_t)gridDim.x * kWarpsPerBlock) {
-        float z, v;
-        warp_head_forward(hidden + i * H, sW, sB, A, H, lane, z, v);
+    const int64_t i0 = (int64_t)blockIdx.x * kWarpsPerBlock + warp, istep = (int64_t)gridDim.x * kWarpsPerBlock;
+    constexpr int NV = HV > 0 ? HV : 1;
+    float4 hn[NV];
+    if (HV > 0 && i0 < B) {
+#pragma unroll
+        for (int g = 0; g < NV; ++g) hn[g] = __ldcs(reinterpret_cast<const float4 *>(hidden + i0 * H + g * 128) + lane);
+    }
+    for (int64_t i = i0; i < B; i += istep) {
+        float z = 0.f, v = 0.f;
+        if (HV > 0) {
+            float4 hv[NV];
+#pragma unroll
+            for (int g = 0; g < NV; ++g) hv[g] = hn[g];
+            if (i + istep < B) {
+#pragma unroll
+                for (int g = 0; g < NV; ++g)
+                    hn[g] = __ldcs(reinterpret_cast<const float4 *>(hidden + (i + istep) * H + g * 128) + lane);
+            }
+            for (int k = want_policy ? 0 : A; k <= A; ++k) {
+                float part = 0.f;
+#pragma unroll
+                for (int g = 0; g < NV; ++g) {
+                    const float4 w = *(reinterpret_cast<const float4 *>(sW + k * H + g * 128) + lane);
+                    part = fmaf(w.x, hv[g].x, part);
+                    part = fmaf(w.y, hv[g].y, part);
+                    part = fmaf(w.z, hv[g].z, part);
+                    part = fmaf(w.w, hv[g].w, part);
+                }
+                part = warp_sum(part) + sB[k];
+                if (k == A) v = part;
+                else if (lane == k) z = part;
+            }
+        } else {
+            warp_head_forward(hidden + i * H, sW, sB, A, H, lane, z, v);
+        }
         if (value != nullptr && lane == 0) value[i] = v;
         if (!want_policy) continue;
         float ell, p, Hh;
@@ -564,10 +598,16 @@ int launch_policy_head(const ocppo_handle *h, const float *hidden, int64_t B, in
     const int A = h->cfg.n_actions, H = h->hidden;
     PhiloxLayout L{seed, offset, torch_philox_grid(total_B * A, h->sm_count, h->max_threads_per_sm) * 256};
     const int smem = head_smem_bytes(A, H);
-    OCPPO_TRY(ensure_head_smem((const void *)policy_head_kernel, smem));
+    const bool aligned = (((uintptr_t)hidden & 15) == 0);
+    auto kern = policy_head_kernel<0>;
+    if (aligned && H == 128) kern = policy_head_kernel<1>;
+    else if (aligned && H == 256) kern = policy_head_kernel<2>;
+    else if (aligned && H == 512) kern = policy_head_kernel<4>;
+    else if (aligned && H == 1024) kern = policy_head_kernel<8>;
+    OCPPO_TRY(ensure_head_smem((const void *)kern, smem));
     const unsigned grid = grid_for(B, kWarpsPerBlock, h->sm_count * 4);
     ProfScope ps(KC_HEAD, 1, stream);
-    policy_head_kernel<<<grid, kHeadThreads, smem, stream>>>(
+    kern<<<grid, kHeadThreads, smem, stream>>>(
         hidden, B, H, A, h->params + h->actor.w_off, h->params + h->actor.b_off, h->params + h->critic.w_off,
         h->params + h->critic.b_off, L, row_base, given, action, logp, entropy, value, want_policy);
     OCPPO_LAUNCH_CHECK("policy_head_kernel");
