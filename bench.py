@@ -21,7 +21,16 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries the one JSON line only
+# stdout carries the ONE JSON line only: everything any library writes to fd 1 (NCCL prints its version banner there
+# with printf) is sent to stderr, and the line itself goes to a private duplicate of the original stdout.
+_JSON_FD = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    os.write(_JSON_FD, (json.dumps(line) + "\n").encode())
+
 
 import numpy as np  # noqa: E402
 import torch  # noqa: E402
@@ -209,7 +218,7 @@ def run_reference(a):
         "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(a, world):
@@ -460,7 +469,7 @@ def run_b200(a):
         "last_stats": {k: last[k] for k in ("loss", "pg_loss", "v_loss", "entropy", "approx_kl", "grad_norm")},
         "impl": "b200",
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world.distributed:
         torch.distributed.destroy_process_group()
 
