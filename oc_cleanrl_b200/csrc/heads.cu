@@ -87,6 +87,42 @@ __device__ __forceinline__ void warp_head_forward(const float *__restrict__ h, c
     }
 }
 
+// Head forward from a hidden row held in registers (NV float4 per lane): rows k_first..A of sW, eight at a time with
+// independent accumulators so that the shared-memory loads, FMA chains and shuffle reductions of different rows overlap
+// (one row after the other was a 250-cycle dependent chain per row).  Lane k keeps logit k; v is broadcast.
+template <int NV>
+__device__ __forceinline__ void head_forward_vec(const float4 (&hv)[NV], const float *sW, const float *sB, int A, int H,
+                                                 int lane, int k_first, float &z, float &v) {
+    for (int k0 = k_first; k0 <= A; k0 += 8) {
+        float part[8];
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk) part[kk] = 0.f;
+#pragma unroll
+        for (int g = 0; g < NV; ++g) {
+#pragma unroll
+            for (int kk = 0; kk < 8; ++kk) {
+                const int k = k0 + kk <= A ? k0 + kk : A;            // rows past A repeat row A and are ignored
+                const float4 w = *(reinterpret_cast<const float4 *>(sW + k * H + g * 128) + lane);
+                part[kk] = fmaf(w.x, hv[g].x, part[kk]);
+                part[kk] = fmaf(w.y, hv[g].y, part[kk]);
+                part[kk] = fmaf(w.z, hv[g].z, part[kk]);
+                part[kk] = fmaf(w.w, hv[g].w, part[kk]);
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+            for (int kk = 0; kk < 8; ++kk) part[kk] += __shfl_xor_sync(kFull, part[kk], o);
+        }
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk) {
+            const int k = k0 + kk;
+            if (k == A) v = part[kk] + sB[A];
+            else if (k < A && lane == k) z = part[kk] + sB[k];
+        }
+    }
+}
+
 // HV > 0: H == 128 * HV, the hidden row is read once with 16-byte loads (next row prefetched); HV == 0: any H.
 template <int HV>
 __global__ void __launch_bounds__(kHeadThreads)
@@ -116,20 +152,7 @@ policy_head_kernel(const float *__restrict__ hidden, int64_t B, int H, int A, co
                 for (int g = 0; g < NV; ++g)
                     hn[g] = __ldcs(reinterpret_cast<const float4 *>(hidden + (i + istep) * H + g * 128) + lane);
             }
-            for (int k = want_policy ? 0 : A; k <= A; ++k) {
-                float part = 0.f;
-#pragma unroll
-                for (int g = 0; g < NV; ++g) {
-                    const float4 w = *(reinterpret_cast<const float4 *>(sW + k * H + g * 128) + lane);
-                    part = fmaf(w.x, hv[g].x, part);
-                    part = fmaf(w.y, hv[g].y, part);
-                    part = fmaf(w.z, hv[g].z, part);
-                    part = fmaf(w.w, hv[g].w, part);
-                }
-                part = warp_sum(part) + sB[k];
-                if (k == A) v = part;
-                else if (lane == k) z = part;
-            }
+            head_forward_vec<NV>(hv, sW, sB, A, H, lane, want_policy ? 0 : A, z, v);
         } else {
             warp_head_forward(hidden + i * H, sW, sB, A, H, lane, z, v);
         }
@@ -185,16 +208,28 @@ namespace {
 
 // Per-sample PPO loss terms from (logit of this lane, value): returns d loss / d logit of this lane and d loss / d value,
 // adds the logged sums into acc[] on lane 0.
-__device__ __forceinline__ void ppo_sample_loss(const LossArgs &p, int64_t i, float z, float v, int lane, float inv_mb,
+// The sample's five gathered scalars, one per lane (0 action, 1 old logp, 2 advantage, 3 return, 4 old value): a single
+// coalesced-ish load per sample that the vector kernel issues one sample ahead (as five dependent scalar loads they were
+// 20 % of the kernel's stall samples).
+__device__ __forceinline__ float load_sample_scalar(const LossArgs &p, int64_t i, int lane) {
+    if (lane == 0) return __int_as_float(p.action[i]);
+    if (lane == 1) return p.logp_old[i];
+    if (lane == 2) return p.adv[i];
+    if (lane == 3) return p.ret[i];
+    if (lane == 4) return p.val[i];
+    return 0.f;
+}
+
+__device__ __forceinline__ void ppo_sample_loss(const LossArgs &p, int64_t i, float sc, float z, float v, int lane, float inv_mb,
                                                 float mean, float stdv, float &dz, float &dv, double (&acc)[6]) {
     const int A = p.A;
     float ell, pk, Hh;
     warp_categorical(z, lane, A, ell, pk, Hh);
-    const int a = p.action[i];
+    const int a = __float_as_int(__shfl_sync(kFull, sc, 0));
     const float newlogp = __shfl_sync(kFull, ell, a & 31);
-    const float logratio = newlogp - p.logp_old[i];
+    const float logratio = newlogp - __shfl_sync(kFull, sc, 1);
     const float ratio = expf(logratio);
-    float advn = p.adv[i];
+    float advn = __shfl_sync(kFull, sc, 2);
     if (p.norm_adv) advn = __fdiv_rn(advn - mean, stdv + 1e-8f);
     // clipped surrogate (:581-583)
     const float l1 = -advn * ratio;
@@ -207,7 +242,7 @@ __device__ __forceinline__ void ppo_sample_loss(const LossArgs &p, int64_t i, fl
     else if (l2 > l1) g_ratio = in_range ? -advn : 0.f;
     else g_ratio = 0.5f * (-advn) + (in_range ? 0.5f * (-advn) : 0.f);
     // value loss (:585-597)
-    const float R = p.ret[i], Vold = p.val[i];
+    const float R = __shfl_sync(kFull, sc, 3), Vold = __shfl_sync(kFull, sc, 4);
     const float du = v - R;
     const float u = du * du;
     float vterm = u, g_v = du;           // d (0.5*vterm) / d v
@@ -259,36 +294,27 @@ __global__ void __launch_bounds__(kHeadThreads) loss_head_kernel(LossArgs p) {
     if (HV > 0) {
         constexpr int NV = HV > 0 ? HV : 1;
         float4 hn[NV];
+        float sc_next = 0.f;
         if (i0 < p.rows) {
 #pragma unroll
             for (int g = 0; g < NV; ++g) hn[g] = __ldcs(reinterpret_cast<const float4 *>(p.hidden + i0 * H + g * 128) + lane);
+            sc_next = load_sample_scalar(p, i0, lane);
         }
         for (int64_t i = i0; i < p.rows; i += istep) {
             float4 hv[NV];
 #pragma unroll
             for (int g = 0; g < NV; ++g) hv[g] = hn[g];
+            const float sc = sc_next;
             if (i + istep < p.rows) {
 #pragma unroll
                 for (int g = 0; g < NV; ++g)
                     hn[g] = __ldcs(reinterpret_cast<const float4 *>(p.hidden + (i + istep) * H + g * 128) + lane);
+                sc_next = load_sample_scalar(p, i + istep, lane);
             }
             float z = 0.f, v = 0.f;
-            for (int k = 0; k <= A; ++k) {
-                float part = 0.f;
-#pragma unroll
-                for (int g = 0; g < NV; ++g) {
-                    const float4 w = *(reinterpret_cast<const float4 *>(sW + k * H + g * 128) + lane);
-                    part = fmaf(w.x, hv[g].x, part);
-                    part = fmaf(w.y, hv[g].y, part);
-                    part = fmaf(w.z, hv[g].z, part);
-                    part = fmaf(w.w, hv[g].w, part);
-                }
-                part = warp_sum(part) + sB[k];
-                if (k == A) v = part;
-                else if (lane == k) z = part;
-            }
+            head_forward_vec<NV>(hv, sW, sB, A, H, lane, 0, z, v);
             float dz, dv;
-            ppo_sample_loss(p, i, z, v, lane, inv_mb, mean, stdv, dz, dv, acc);
+            ppo_sample_loss(p, i, sc, z, v, lane, inv_mb, mean, stdv, dz, dv, acc);
             // d hidden = dv * Wc + sum_k dz_k * Wa[k], masked by the ReLU of the last trunk layer
             float4 s[NV];
 #pragma unroll
@@ -296,15 +322,19 @@ __global__ void __launch_bounds__(kHeadThreads) loss_head_kernel(LossArgs p) {
                 const float4 w = *(reinterpret_cast<const float4 *>(sW + A * H + g * 128) + lane);
                 s[g] = make_float4(dv * w.x, dv * w.y, dv * w.z, dv * w.w);
             }
-            for (int k = 0; k < A; ++k) {
-                const float dzk = __shfl_sync(kFull, dz, k);
+            for (int k0 = 0; k0 < A; k0 += 4) {      // four head rows at a time: their loads are issued together
 #pragma unroll
-                for (int g = 0; g < NV; ++g) {
-                    const float4 w = *(reinterpret_cast<const float4 *>(sW + k * H + g * 128) + lane);
-                    s[g].x = fmaf(dzk, w.x, s[g].x);
-                    s[g].y = fmaf(dzk, w.y, s[g].y);
-                    s[g].z = fmaf(dzk, w.z, s[g].z);
-                    s[g].w = fmaf(dzk, w.w, s[g].w);
+                for (int kk = 0; kk < 4; ++kk) {
+                    const int k = k0 + kk < A ? k0 + kk : A - 1;
+                    const float dzk = k0 + kk < A ? __shfl_sync(kFull, dz, k) : 0.f;     // (uniform condition)
+#pragma unroll
+                    for (int g = 0; g < NV; ++g) {
+                        const float4 w = *(reinterpret_cast<const float4 *>(sW + k * H + g * 128) + lane);
+                        s[g].x = fmaf(dzk, w.x, s[g].x);
+                        s[g].y = fmaf(dzk, w.y, s[g].y);
+                        s[g].z = fmaf(dzk, w.z, s[g].z);
+                        s[g].w = fmaf(dzk, w.w, s[g].w);
+                    }
                 }
             }
 #pragma unroll
@@ -320,7 +350,7 @@ __global__ void __launch_bounds__(kHeadThreads) loss_head_kernel(LossArgs p) {
             float z, v;
             warp_head_forward(h, sW, sB, A, H, lane, z, v);
             float dz, dv;
-            ppo_sample_loss(p, i, z, v, lane, inv_mb, mean, stdv, dz, dv, acc);
+            ppo_sample_loss(p, i, load_sample_scalar(p, i, lane), z, v, lane, inv_mb, mean, stdv, dz, dv, acc);
             // d hidden, masked by ReLU of the last trunk layer
             // (warp-uniform trip count: the shuffles below need all 32 lanes, also when H % 32 != 0)
             for (int j0 = 0; j0 < H; j0 += 32) {
