@@ -153,3 +153,44 @@ def test_oracle_model_equals_reference_model():
             for u, v in zip(ref.get_action_and_value(x, act), ours.get_action_and_value(x, act)):
                 assert torch.equal(u, v)
             assert torch.equal(ref.get_value(x), ours.get_value(x))
+
+
+def test_relu_decisions_context_reproduces_and_overrides():
+    """oracle/ref_ppo.py::relu_decisions (the hook the GPU parity test uses to hand the oracle the device path's ReLU
+    decisions): with the network's OWN decisions the loss and every gradient are bit-identical to the plain
+    evaluation; flipping one decision of a unit whose pre-activation is far from zero changes that unit's row."""
+    torch.manual_seed(0)
+    F, D, A = 4, 6, 6
+    agent = ref_ppo.make_agent(F, D, A, (32, 64), (32,), seed=3)
+    rs = np.random.RandomState(0)
+    n = 64
+    batch = (torch.as_tensor(rs.randint(0, 200, (n, F, D)), dtype=torch.float32), torch.as_tensor(rs.randint(0, A, n)),
+             torch.as_tensor(-1.79 + 0.05 * rs.randn(n), dtype=torch.float32),
+             torch.as_tensor(rs.randn(n), dtype=torch.float32), torch.as_tensor(rs.randn(n), dtype=torch.float32),
+             torch.as_tensor(rs.randn(n), dtype=torch.float32))
+    idx = np.arange(n)
+    loss, _ = ref_ppo.ref_minibatch_loss(agent, *batch, idx, ref_ppo.PPOArgs())
+    loss.backward()
+    plain = ref_ppo.flat_grads(agent).clone()
+    with ref_ppo.relu_decisions(agent) as rd:
+        ref_ppo.ref_minibatch_loss(agent, *batch, idx, ref_ppo.PPOArgs())
+    own = [r["decision"].clone() for r in rd.records]
+    assert len(own) == 3 and own[0].shape == (n, F, 32) and own[-1].shape == (n, 32)
+    for p in agent.parameters():
+        p.grad = None
+    with ref_ppo.relu_decisions(agent, own):
+        loss2, _ = ref_ppo.ref_minibatch_loss(agent, *batch, idx, ref_ppo.PPOArgs())
+    loss2.backward()
+    assert torch.equal(loss2, loss) and torch.equal(ref_ppo.flat_grads(agent), plain)
+    # switch off every decision of unit 5 of the last trunk layer: only then does its weight-gradient row vanish
+    flipped = [m.clone() for m in own]
+    flipped[-1][:, 5] = False
+    for p in agent.parameters():
+        p.grad = None
+    with ref_ppo.relu_decisions(agent, flipped):
+        loss3, _ = ref_ppo.ref_minibatch_loss(agent, *batch, idx, ref_ppo.PPOArgs())
+    loss3.backward()
+    last_linear = [m for m in agent.network if isinstance(m, torch.nn.Linear)][-1]
+    assert torch.count_nonzero(last_linear.weight.grad[5]) == 0
+    if own[-1][:, 5].any():
+        assert not torch.equal(ref_ppo.flat_grads(agent), plain)
