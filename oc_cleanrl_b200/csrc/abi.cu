@@ -185,7 +185,7 @@ static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_
 }
 
 static void pick_split(const ocppo_handle *h, int M, int N, int64_t K, int *splits, int64_t *k_per) {
-    const int tn = tc_tile_n(g_gemm_mode == 2);
+    const int tn = tc_tile_n(g_gemm_mode == 2 || g_gemm_mode == 4);
     const bool tc = g_gemm_mode >= 1 && M % 128 == 0 && N % tn == 0;
     int64_t S;
     const int64_t s_cap0 = K / 256 > 1 ? K / 256 : 1;
@@ -283,7 +283,7 @@ int64_t ocppo_launch_count(void) {
 }
 
 int ocppo_set_gemm_mode(int32_t mode) {
-    OCPPO_CHECK_ARG(mode >= 0 && mode <= 3, "gemm mode must be 0 (fp32 FMA), 1 (tcgen05 3xTF32), 2 (3xTF32, single accumulator) or 3 (TF32 + BF16 corrections)");
+    OCPPO_CHECK_ARG(mode >= 0 && mode <= 4, "gemm mode must be 0 (fp32 FMA), 1 (tcgen05 3xTF32), 2 (3xTF32, single accumulator) or 3 (TF32 + BF16 corrections)");
     g_gemm_mode = mode;
     return OCPPO_OK;
 }
@@ -292,13 +292,13 @@ int ocppo_get_gemm_mode(void) { return g_gemm_mode; }
 int ocppo_gemm(int32_t op, int32_t engine, int32_t M, int32_t N, int64_t K, const float *A, int64_t lda,
                const float *B, int64_t ldb, float *C, int64_t ldc, const float *bias, const float *mask,
                float *bias_part, int32_t splits, int64_t k_per_split, void *stream) {
-    OCPPO_CHECK_ARG(op >= 0 && op <= 2 && engine >= 0 && engine <= 3, "bad op/engine");
+    OCPPO_CHECK_ARG(op >= 0 && op <= 2 && engine >= 0 && engine <= 4, "bad op/engine");
     OCPPO_CHECK_ARG(A && B && C, "null pointer");
     SgemmArgs a{};
     a.A = A; a.lda = lda; a.B = B; a.ldb = ldb; a.C = C; a.ldc = ldc; a.bias = bias; a.mask = mask;
     a.bias_part = bias_part; a.M = M; a.N = N; a.K = K; a.splits = splits < 1 ? 1 : splits;
     a.k_per_split = k_per_split > 0 ? k_per_split : round_up(K, 32);
-    if (engine >= 1) { a.single_acc = engine == 2; a.corr_bf16 = engine == 3; return tc_gemm_launch((SgemmMode)op, a, as_stream(stream)); }
+    if (engine >= 1) { a.single_acc = engine == 2 || engine == 4; a.corr_bf16 = engine >= 3; return tc_gemm_launch((SgemmMode)op, a, as_stream(stream)); }
     return fma_gemm_launch((SgemmMode)op, a, as_stream(stream));
 }
 

@@ -200,16 +200,16 @@ static int tc_ops_mask() {
 bool sgemm_uses_tc(SgemmMode mode, const SgemmArgs &a) {
     if (g_gemm_mode < 1 || !((tc_ops_mask() >> (int)mode) & 1)) return false;
     SgemmArgs b = a;
-    b.single_acc = g_gemm_mode == 2;
-    b.corr_bf16 = g_gemm_mode == 3;
+    b.single_acc = g_gemm_mode == 2 || g_gemm_mode == 4;
+    b.corr_bf16 = g_gemm_mode >= 3;
     return tc_gemm_supported(mode, b);
 }
 
 int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream) {
     if (sgemm_uses_tc(mode, a)) {
         SgemmArgs b = a;
-        b.single_acc = g_gemm_mode == 2;
-        b.corr_bf16 = g_gemm_mode == 3;
+        b.single_acc = g_gemm_mode == 2 || g_gemm_mode == 4;
+        b.corr_bf16 = g_gemm_mode >= 3;
         return tc_gemm_launch(mode, b, stream);
     }
     OCPPO_CHECK_ARG(mode != SGEMM_DGRAD || a.mask != nullptr, "sgemm: the FMA dgrad kernel needs the fp32 mask");
