@@ -1,0 +1,119 @@
+"""Rollout-step plumbing: the collector against the reference's own per-step data flow
+(cleanrl/ppo_atari_oc.py:500-514) driven through the public agent API, on a deterministic host environment."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref_ppo
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev(built_lib):
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return torch.device("cuda:0")
+
+
+class ToyVecEnv:
+    """Deterministic stand-in for the SubprocVecEnv of the script: integer-valued object vectors, sparse rewards,
+    occasional episode ends; everything a function of (step counter, actions)."""
+
+    def __init__(self, n, frames, obs_dim, seed=0):
+        self.n, self.frames, self.obs_dim, self.t = n, frames, obs_dim, 0
+        self.state = np.random.RandomState(seed).randint(0, 160, (n, frames, obs_dim)).astype(np.float64)
+
+    def reset(self):
+        self.t = 0
+        return self.state.copy()
+
+    def step(self, actions):
+        assert actions.dtype == np.int64 and actions.shape == (self.n,)
+        self.t += 1
+        self.state = np.roll(self.state, 1, axis=1)
+        self.state[:, 0] = np.clip(self.state[:, 1] + (actions[:, None] - 2) + (self.t % 3), 0, 209)
+        reward = np.where(actions == self.t % 6, 1.0, 0.0) - 0.25 * (actions == 0)
+        done = (actions == (self.t * 7) % 6) & (np.arange(self.n) % 5 == self.t % 5)
+        return self.state.copy(), reward, done, [{}] * self.n
+
+
+def reference_style_rollout(agent, env, dev, T, N, iterations, seed):
+    """ppo_atari_oc.py:451-466 and :500-514, statement for statement, with the drop-in agent."""
+    F, D = agent._frames, agent._obs_dim
+    obs = torch.zeros((T, N, F, D), dtype=torch.float32, device=dev)
+    actions = torch.zeros((T, N), dtype=torch.long, device=dev)
+    logprobs = torch.zeros((T, N), dtype=torch.float32, device=dev)
+    rewards = torch.zeros((T, N), dtype=torch.float32, device=dev)
+    dones = torch.zeros((T, N), dtype=torch.float32, device=dev)
+    values = torch.zeros((T, N), dtype=torch.float32, device=dev)
+    torch.cuda.manual_seed(seed)
+    next_obs = torch.tensor(env.reset(), dtype=torch.float32, device=dev)
+    next_done = torch.zeros(N, dtype=torch.float32, device=dev)
+    snaps = []
+    for _ in range(iterations):
+        for step in range(T):
+            obs[step] = next_obs
+            dones[step] = next_done
+            with torch.no_grad():
+                action, logprob, _, value = agent.get_action_and_value(next_obs)
+                values[step] = value.flatten()
+            actions[step] = action
+            logprobs[step] = logprob
+            next_obs_np, reward_np, next_done_np, _ = env.step(action.detach().cpu().numpy())
+            rewards[step] = torch.tensor(reward_np, dtype=torch.float32, device=dev).view(-1)
+            next_obs = torch.tensor(next_obs_np, dtype=torch.float32, device=dev)
+            next_done = torch.tensor(next_done_np, dtype=torch.float32, device=dev)
+        snaps.append([t.clone() for t in (obs, actions, logprobs, rewards, dones, values, next_obs, next_done)])
+    return snaps
+
+
+@pytest.mark.parametrize("T,N,dims", [(16, 64, ((32, 64), (32,))), (8, 512, ((256, 512, 1024, 512), (512,)))])
+def test_collector_reproduces_the_reference_data_flow_bit_for_bit(dev, T, N, dims):
+    from oc_cleanrl_b200.architectures.ppo import PPObj
+    from oc_cleanrl_b200.rollout import RolloutCollector
+    F, D, A = 4, 6, 6
+    torch.manual_seed(7)
+    agent = PPObj(ref_ppo.stub_envs(F, D, A), dev, *dims).to(dev)
+    want = reference_style_rollout(agent, ToyVecEnv(N, F, D), dev, T, N, iterations=2, seed=11)
+
+    env = ToyVecEnv(N, F, D)
+    col = RolloutCollector(agent, T, N)
+    torch.cuda.manual_seed(11)
+    col.reset(env.reset())
+    for it in range(2):
+        if it:
+            col.start_next_iteration()
+        for step in range(T):
+            a = col.act(step)
+            assert a.dtype == np.int64 and a.shape == (N,)
+            col.observe(step, *env.step(a.copy())[:3])
+        torch.cuda.synchronize()
+        got = (col.obs, col.actions, col.logprobs, col.rewards, col.dones, col.values, col.next_obs, col.next_done)
+        for name, g, w in zip(("obs", "actions", "logprobs", "rewards", "dones", "values", "next_obs", "next_done"),
+                              got, want[it]):
+            assert g.shape == w.shape and g.dtype == w.dtype, name
+            assert torch.equal(g, w), f"iteration {it}: {name} differs"
+        assert col.obs.is_contiguous() and col.dones.is_contiguous()
+
+
+def test_collector_feeds_the_learner_and_rejects_bad_input(dev):
+    from oc_cleanrl_b200 import _abi
+    from oc_cleanrl_b200.architectures.ppo import PPObj
+    from oc_cleanrl_b200.learner import LearnerArgs, PPOLearner
+    from oc_cleanrl_b200.rollout import RolloutCollector
+    F, D, A, T, N = 4, 6, 6, 8, 32
+    torch.manual_seed(3)
+    agent = PPObj(ref_ppo.stub_envs(F, D, A), dev, (32, 64), (32,)).to(dev)
+    env = ToyVecEnv(N, F, D)
+    col = RolloutCollector(agent, T, N)
+    col.reset(env.reset())
+    for step in range(T):
+        col.observe(step, *env.step(col.act(step).copy())[:3])
+    learner = PPOLearner(agent, LearnerArgs(num_envs=N, num_steps=T), np_rng=np.random.RandomState(0))
+    adv, ret = learner.compute_gae(col.rewards, col.values, col.dones, col.next_obs, col.next_done)
+    stats = learner.update(col.obs, col.actions, col.logprobs, adv, ret, col.values)
+    assert np.isfinite(stats["loss"]) and stats["minibatches"] == 16
+    with pytest.raises(_abi.OcppoError):
+        col.act(T)
+    with pytest.raises(_abi.OcppoError):
+        col.observe(0, np.zeros((N + 1, F, D)), np.zeros(N), np.zeros(N))
