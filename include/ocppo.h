@@ -185,6 +185,13 @@ int ocppo_clip_adam(ocppo_handle *h, float inv_world, float max_grad_norm, doubl
                     double beta1, double beta2, double eps, int64_t step, float *grad_norm,
                     void *stream);
 
+/* ---- logged statistics -------------------------------------------------- */
+/* The two population variances of the script's explained-variance line (ppo_atari_oc.py:620-623) over the flat
+ * rollout: out2[0] = var(returns), out2[1] = var(returns - values), both device floats (the script moves both
+ * (T*N) buffers to the host and calls np.var twice).  Needs a training workspace (uses its partial-sum scratch). */
+int ocppo_explained_variance(ocppo_handle *h, const float *values, const float *returns, int64_t n, float *out2,
+                             void *stream);
+
 /* ---- autograd bridge (compat tier: script's own loss/optimizer) --------- */
 /* Trunk forward keeping activations: hidden (B, decoder_dims[-1]). */
 int ocppo_trunk_forward(ocppo_handle *h, const float *obs, int64_t B, float *hidden,

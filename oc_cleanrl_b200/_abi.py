@@ -78,6 +78,7 @@ _SIGNATURES = {
     "ocppo_minibatch_fwd_bwd": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _I64, C.POINTER(HParams), _P, _P]),
     "ocppo_clip_adam": (C.c_int, [_P, _F, _F, _D, _D, _D, _D, _I64, _P, _P]),
     "ocppo_trunk_forward": (C.c_int, [_P, _P, _I64, _P, _P]),
+    "ocppo_explained_variance": (C.c_int, [_P, _P, _P, _I64, _P, _P]),
     "ocppo_read_activation": (C.c_int, [_P, C.c_int32, _I64, _P, _P]),
     "ocppo_trunk_backward": (C.c_int, [_P, _P, _I64, _P, _P]),
 }

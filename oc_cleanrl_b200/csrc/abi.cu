@@ -554,6 +554,13 @@ int ocppo_clip_adam(ocppo_handle *h, float inv_world, float max_grad_norm, doubl
     return launch_clip_adam(h, inv_world, max_grad_norm, lr, beta1, beta2, eps, step, grad_norm, as_stream(stream));
 }
 
+int ocppo_explained_variance(ocppo_handle *h, const float *values, const float *returns, int64_t n, float *out2,
+                             void *stream) {
+    OCPPO_TRY(require_ready(h, true));
+    OCPPO_CHECK_ARG(values && returns && out2 && n >= 1, "explained_variance: bad argument");
+    return launch_explained_var(h, values, returns, n, out2, as_stream(stream));
+}
+
 int ocppo_trunk_forward(ocppo_handle *h, const float *obs, int64_t B, float *hidden, void *stream) {
     OCPPO_TRY(require_ready(h, false));
     OCPPO_CHECK_ARG(B >= 1 && B <= h->max_rows, "trunk_forward: B=%lld must be in [1,%lld]", (long long)B,

@@ -172,6 +172,8 @@ int launch_gather(const ocppo_handle *h, const float *b_obs, const int64_t *b_ac
                   cudaStream_t stream);
 int launch_adv_stats(const ocppo_handle *h, const float *b_adv, const int64_t *idx, int64_t mb, cudaStream_t stream);
 int launch_loss_head(const ocppo_handle *h, LossArgs a, int *blocks_used, int blocks_avail, cudaStream_t stream);
+int launch_explained_var(const ocppo_handle *h, const float *y_pred, const float *y_true, int64_t n, float *out2,
+                         cudaStream_t stream);
 int launch_loss_finalize(const double *part, int n_part, int64_t mb, float ent_coef, float vf_coef, float *stats,
                          cudaStream_t stream);
 int launch_splitk_reduce(const float *part, int splits, int64_t stride, int64_t count, float *out, int accumulate,

@@ -446,6 +446,47 @@ adv_stats_partial_kernel(const float *__restrict__ b_adv, const int64_t *__restr
     }
 }
 
+// Explained variance of the value function (ppo_atari_oc.py:620-623: np.var(y_true), np.var(y_true - y_pred), population
+// variances; y_true - y_pred is an fp32 subtraction there too).  Sums in fp64, ordered second stage.
+__global__ void __launch_bounds__(256)
+explained_var_partial_kernel(const float *__restrict__ y_pred, const float *__restrict__ y_true, int64_t n,
+                             double *__restrict__ part) {
+    double s[4] = {0, 0, 0, 0};          // sum y, sum y^2, sum d, sum d^2
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float yt = y_true[i];
+        const double y = (double)yt, d = (double)__fsub_rn(yt, y_pred[i]);
+        s[0] += y; s[1] += y * y; s[2] += d; s[3] += d * d;
+    }
+    __shared__ double red[8][4];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const double r = warp_sum_d(s[q]);
+        if (lane == 0) red[warp][q] = r;
+    }
+    __syncthreads();
+    if (threadIdx.x < 4) {
+        double a = 0;
+        for (int w = 0; w < 8; ++w) a += red[w][threadIdx.x];
+        part[(int64_t)blockIdx.x * 4 + threadIdx.x] = a;
+    }
+}
+
+__global__ void explained_var_finalize_kernel(const double *__restrict__ part, int n_part, int64_t n,
+                                              float *__restrict__ out) {
+    if (threadIdx.x == 0) {
+        double s[4] = {0, 0, 0, 0};
+        for (int b = 0; b < n_part; ++b)
+            for (int q = 0; q < 4; ++q) s[q] += part[4 * b + q];
+        const double my = s[0] / (double)n, md = s[2] / (double)n;
+        double vy = s[1] / (double)n - my * my, vd = s[3] / (double)n - md * md;
+        if (vy < 0) vy = 0;
+        if (vd < 0) vd = 0;
+        out[0] = (float)vy;               // np.var(y_true)
+        out[1] = (float)vd;               // np.var(y_true - y_pred)
+    }
+}
+
 __global__ void adv_stats_finalize_kernel(const double *__restrict__ part, int n_part, int64_t mb,
                                           float *__restrict__ stat) {
     if (threadIdx.x == 0) {
@@ -695,6 +736,17 @@ int launch_adv_stats(const ocppo_handle *h, const float *b_adv, const int64_t *i
     OCPPO_LAUNCH_CHECK("adv_stats_partial_kernel");
     adv_stats_finalize_kernel<<<1, 32, 0, stream>>>(h->adv_part, (int)grid, mb, h->adv_stat);
     OCPPO_LAUNCH_CHECK("adv_stats_finalize_kernel");
+    return OCPPO_OK;
+}
+
+int launch_explained_var(const ocppo_handle *h, const float *y_pred, const float *y_true, int64_t n, float *out2,
+                         cudaStream_t stream) {
+    const unsigned grid = grid_for(n, 256 * 8, h->sm_count * 2);       // <= kLossBlocksMax partial slots of 8 doubles
+    ProfScope ps(KC_AUX, 2, stream);
+    explained_var_partial_kernel<<<grid, 256, 0, stream>>>(y_pred, y_true, n, h->loss_part);
+    OCPPO_LAUNCH_CHECK("explained_var_partial_kernel");
+    explained_var_finalize_kernel<<<1, 32, 0, stream>>>(h->loss_part, (int)grid, n, out2);
+    OCPPO_LAUNCH_CHECK("explained_var_finalize_kernel");
     return OCPPO_OK;
 }
 

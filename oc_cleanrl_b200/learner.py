@@ -136,6 +136,20 @@ class PPOLearner:
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
+    # -- ppo_atari_oc.py:620-623 -------------------------------------------------
+    def explained_variance(self, values, returns):
+        """``1 - var(returns - values) / var(returns)`` over the flat rollout (nan when ``var(returns) == 0``), with
+        both variances reduced on the device: 8 bytes come back instead of the two (T, N) buffers."""
+        v, r = values.reshape(-1).contiguous(), returns.reshape(-1).contiguous()
+        if v.numel() != r.numel() or not v.is_cuda or v.dtype != torch.float32 or r.dtype != torch.float32:
+            raise _abi.OcppoError("explained_variance needs two fp32 CUDA tensors of equal size")
+        self.agent._ensure_workspace(1, training=True)
+        out = torch.empty(2, dtype=torch.float32, device=self.device)
+        _abi.check(_abi.lib().ocppo_explained_variance(self.agent._handle.raw, _abi.ptr(v), _abi.ptr(r), v.numel(),
+                                                       _abi.ptr(out), self._stream()))
+        var_y, var_d = (float(x) for x in out.cpu())
+        return float("nan") if var_y == 0 else 1.0 - var_d / var_y
+
     def minibatch_step(self, flat, idx_dev, slot):
         """One minibatch (ppo_atari_oc.py:563-610) on device index tensor `idx_dev`."""
         b_obs, b_actions, b_logprobs, b_advantages, b_returns, b_values = flat

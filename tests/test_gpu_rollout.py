@@ -117,3 +117,72 @@ def test_collector_feeds_the_learner_and_rejects_bad_input(dev):
         col.act(T)
     with pytest.raises(_abi.OcppoError):
         col.observe(0, np.zeros((N + 1, F, D)), np.zeros(N), np.zeros(N))
+
+
+@pytest.mark.parametrize("n,const", [(128 * 4096, False), (1000, False), (77, True)])
+def test_explained_variance_matches_the_numpy_line(dev, n, const):
+    """ppo_atari_oc.py:620-623 (np.var on host copies) against the device reduction."""
+    from oc_cleanrl_b200.architectures.ppo import PPObj
+    from oc_cleanrl_b200.learner import LearnerArgs, PPOLearner
+    torch.manual_seed(1)
+    agent = PPObj(ref_ppo.stub_envs(4, 6, 6), dev, (32, 64), (32,)).to(dev)
+    learner = PPOLearner(agent, LearnerArgs(num_envs=8, num_steps=8))
+    rs = np.random.RandomState(n)
+    y_true = np.full(n, 3.5, np.float32) if const else (2.0 + 1.5 * rs.randn(n)).astype(np.float32)
+    y_pred = (y_true + 0.3 * rs.randn(n)).astype(np.float32)
+    var_y = np.var(y_true)
+    want = np.nan if var_y == 0 else 1 - np.var(y_true - y_pred) / var_y
+    got = learner.explained_variance(torch.as_tensor(y_pred).to(dev), torch.as_tensor(y_true).to(dev))
+    if const:
+        assert np.isnan(want) and np.isnan(got)
+    else:
+        assert got == pytest.approx(float(want), rel=1e-4, abs=1e-6)
+
+
+def test_checkpoint_round_trips_with_the_reference_format(dev, tmp_path):
+    """ppo_atari_oc.py:484-491 / loading.py:111-122: a file written here loads into the reference-shaped
+    module, a file written the reference's way loads here, and training resumes bit-identically."""
+    from oc_cleanrl_b200.architectures.ppo import PPObj
+    from oc_cleanrl_b200.checkpoint import load_checkpoint, save_checkpoint
+    from oc_cleanrl_b200.learner import LearnerArgs, PPOLearner
+    from oc_cleanrl_b200.synthetic import make_rollout
+    F, D, A, T, N = 4, 6, 6, 8, 32
+    dims = ((32, 64), (32,))
+    torch.manual_seed(5)
+    agent = PPObj(ref_ppo.stub_envs(F, D, A), dev, *dims).to(dev)
+    learner = PPOLearner(agent, LearnerArgs(num_envs=N, num_steps=T), np_rng=np.random.RandomState(1))
+    data = make_rollout(T, N, F, D)
+    rs = np.random.RandomState(2)
+    roll = [data["obs"].to(dev), torch.as_tensor(rs.randint(0, A, (T, N))).to(dev),
+            torch.as_tensor(-1.79 + 0.05 * rs.randn(T, N), dtype=torch.float32).to(dev),
+            torch.as_tensor(rs.randn(T, N), dtype=torch.float32).to(dev),
+            torch.as_tensor(rs.randn(T, N), dtype=torch.float32).to(dev),
+            torch.as_tensor(rs.randn(T, N), dtype=torch.float32).to(dev)]
+    learner.update(*roll)
+    path = tmp_path / "run_1.cleanrl_model"
+    saved = save_checkpoint(path, agent, args={"env_id": "ALE/Pong-v5", "seed": 1}, timesteps=T * N, learner=learner)
+    assert list(saved["model_weights"].keys()) == list(agent.state_dict().keys()) and saved["Timesteps"] == T * N
+    # the reference-shaped module reads it the way loading.py does
+    ckpt = torch.load(path, map_location="cpu", weights_only=False)
+    oracle = ref_ppo.make_agent(F, D, A, *dims, seed=0)
+    oracle.load_state_dict(ckpt["model_weights"])
+    x = data["obs"].reshape(-1, F, D)[:64]
+    with torch.no_grad():
+        assert torch.allclose(agent.get_value(x.to(dev)).cpu(), oracle.get_value(x), rtol=1e-4, atol=1e-5)
+    # continue training, then restore into a fresh agent and continue again: identical weights
+    perm_rng = np.random.RandomState(9)
+    learner.np_rng = perm_rng
+    learner.update(*roll)
+    want = agent.arena.clone()
+    torch.manual_seed(99)
+    agent2 = PPObj(ref_ppo.stub_envs(F, D, A), dev, *dims).to(dev)
+    learner2 = PPOLearner(agent2, LearnerArgs(num_envs=N, num_steps=T), np_rng=np.random.RandomState(9))
+    load_checkpoint(path, agent2, learner2)
+    assert learner2.adam_step == 16
+    learner2.update(*roll)
+    assert torch.equal(agent2.arena, want)
+    # a file written the reference's way (weights only, :675-677)
+    path2 = tmp_path / "final.cleanrl_model"
+    torch.save({"model_weights": oracle.state_dict(), "args": {}}, path2)
+    load_checkpoint(path2, agent2)
+    assert all(torch.equal(a.cpu(), b) for a, b in zip(agent2.state_dict().values(), oracle.state_dict().values()))
