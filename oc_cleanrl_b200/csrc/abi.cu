@@ -120,6 +120,10 @@ static int64_t carve(ocppo_handle *h, void *base, int64_t R, int training, bool 
         if ((int64_t)L.out_dim * L.in_dim > max_w) max_w = (int64_t)L.out_dim * L.in_dim;
         if (L.out_dim > max_out) max_out = L.out_dim;
     }
+    t->amax = cv.take<float>(kAmaxSlots);
+    t->w_amax_valid = 0;
+    t->w16_hi = cv.take<uint16_t>(h->param_floats);
+    t->w16_lo = cv.take<uint16_t>(h->param_floats);
     const int AP = (int)round_up(c.n_actions + 1, 4);
     if ((int64_t)AP * h->hidden > max_w) max_w = (int64_t)AP * h->hidden;
     if (AP > max_out) max_out = AP;
@@ -164,10 +168,37 @@ static int require_ready(const ocppo_handle *h, bool need_training) {
 
 // ---- trunk forward / backward ---------------------------------------------
 // x: [B*frames, obs_dim] contiguous.  Writes h->act[l] for every trunk layer.
+// FP16x3 engine: max |act[l]| measured on demand when the kernel that wrote act[l] did not track it (FMA layers)
+static int ensure_act_amax(ocppo_handle *h, int l, int64_t B, cudaStream_t s) {
+    if (h->act_amax_valid[l]) return OCPPO_OK;
+    const Layer &L = h->layers[l];
+    OCPPO_TRY(launch_absmax(h->act[l], B * L.row_mult, L.out_dim, L.out_dim, h->amax + kAmaxAct + l, h->sm_count, s));
+    h->act_amax_valid[l] = 1;
+    return OCPPO_OK;
+}
+
 static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_t s) {
     const float *in = x;
+    const bool f16 = g_gemm_mode == 5;
+    if (f16) {
+        // operand scales of the FP16x3 engine: activations are tracked by the epilogue that writes them (slots zeroed
+        // here), the weights are measured now -- the arena is the caller's to modify between calls
+        OCPPO_CUDA(cudaMemsetAsync(h->amax, 0, kAmaxGrad * sizeof(float), s));
+        AbsmaxSegs segs{};
+        for (int l = 0; l < h->n_layers; ++l) {
+            const Layer &L = h->layers[l];
+            segs.x[l] = h->params + L.w_off; segs.n[l] = (int64_t)L.out_dim * L.in_dim; segs.out[l] = h->amax + kAmaxW + l;
+        }
+        segs.count = h->n_layers;
+        OCPPO_TRY(launch_absmax_multi(segs, s));
+        OCPPO_TRY(launch_split_f16_multi(segs, h->params, h->w16_hi, h->w16_lo, s));
+        h->w_amax_valid = 1;
+    } else {
+        h->w_amax_valid = 0;
+    }
     for (int l = 0; l < h->n_layers; ++l) {
         const Layer &L = h->layers[l];
+        h->act_amax_valid[l] = 0;
         SgemmArgs a{};
         a.A = in; a.lda = L.in_dim;
         a.B = h->params + L.w_off; a.ldb = L.in_dim;
@@ -176,8 +207,23 @@ static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_
         a.M = (int)(B * L.row_mult); a.N = L.out_dim; a.K = L.in_dim;
         a.k_per_split = round_up(L.in_dim, 8); a.splits = 1;
         a.relu_bits = h->training ? h->relu_bits[l] : nullptr;
-        h->relu_bits_valid[l] = a.relu_bits != nullptr && sgemm_uses_tc(SGEMM_FWD, a);
+        const bool tc = sgemm_uses_tc(SGEMM_FWD, a);
+        h->relu_bits_valid[l] = a.relu_bits != nullptr && tc;
+        if (f16) {
+            a.amax_scratch = h->amax;
+            if (tc && l > 0) {
+                OCPPO_TRY(ensure_act_amax(h, l - 1, B, s));
+                a.amax_a = h->amax + kAmaxAct + l - 1;
+            }
+            a.amax_b = h->amax + kAmaxW + l;
+            if (L.w_off % 8 == 0 && L.in_dim % 8 == 0) {
+                a.b16_hi = reinterpret_cast<const uint16_t *>(h->w16_hi) + L.w_off;
+                a.b16_lo = reinterpret_cast<const uint16_t *>(h->w16_lo) + L.w_off;
+            }
+            if (tc) a.amax_out = h->amax + kAmaxAct + l;
+        }
         OCPPO_TRY(sgemm_launch(SGEMM_FWD, a, s));
+        if (f16 && tc) h->act_amax_valid[l] = 1;
         in = h->act[l];
     }
     h->last_forward_rows = (int)B;
@@ -218,7 +264,8 @@ static void pick_split(const ocppo_handle *h, int M, int N, int64_t K, int *spli
 
 // dW[out,in] (+)= dY[rows,out]^T X[rows,in];  db[out] (+)= colsum(dY)
 static int wgrad(ocppo_handle *h, const float *dY, int out, const float *X, int in, int64_t rows, float *dW,
-                 int64_t w_count, float *db, int64_t b_count, int accumulate, cudaStream_t s) {
+                 int64_t w_count, float *db, int64_t b_count, int accumulate, cudaStream_t s,
+                 const float *amax_dy = nullptr, const float *amax_x = nullptr) {
     if (in <= 32) {          // skinny contraction (first trunk layer): HBM-bound dedicated kernel
         int G = 0, NS = 0;
         float *part = h->skinny, *wsum = h->skinny + (int64_t)h->sm_count * 4 * out * 32;
@@ -233,6 +280,7 @@ static int wgrad(ocppo_handle *h, const float *dY, int out, const float *X, int 
     a.C = h->splitk; a.ldc = in;
     a.bias_part = h->splitk_bias;
     a.M = out; a.N = in; a.K = rows;
+    a.amax_a = amax_dy; a.amax_b = amax_x; a.amax_scratch = h->amax;
     pick_split(h, out, in, rows, &a.splits, &a.k_per_split);
     OCPPO_TRY(sgemm_launch(SGEMM_WGRAD, a, s));
     OCPPO_TRY(launch_splitk_reduce(h->splitk, a.splits, (int64_t)out * in, w_count, dW, accumulate, h->sm_count, s));
@@ -242,13 +290,29 @@ static int wgrad(ocppo_handle *h, const float *dY, int out, const float *X, int 
 
 // g0 holds d loss / d pre-activation of the last trunk layer, [B, hidden].
 static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, int accumulate, cudaStream_t s) {
+    const bool f16 = g_gemm_mode == 5;
+    bool dy_amax_valid = false;
+    if (f16) {
+        // max |dY| of the top layer comes from one reduction pass; the dgrad epilogues track the layers below
+        OCPPO_CUDA(cudaMemsetAsync(h->amax + kAmaxGrad, 0, 2 * OCPPO_MAX_LAYERS * sizeof(float), s));
+        const Layer &LT = h->layers[h->n_layers - 1];
+        OCPPO_TRY(launch_absmax(h->gbuf[cur], B * LT.row_mult, LT.out_dim, LT.out_dim, h->amax + kAmaxGrad + h->n_layers - 1,
+                                h->sm_count, s));
+        dy_amax_valid = true;
+    }
     for (int l = h->n_layers - 1; l >= 0; --l) {
         const Layer &L = h->layers[l];
         const int64_t rows = B * L.row_mult;
         const float *X = (l == 0) ? x : h->act[l - 1];
         const float *dY = h->gbuf[cur];
+        const float *amax_dy = (f16 && dy_amax_valid) ? h->amax + kAmaxGrad + l : nullptr;
+        const float *amax_x = nullptr;
+        if (f16 && l > 0 && L.in_dim > 32) {
+            OCPPO_TRY(ensure_act_amax(h, l - 1, B, s));
+            amax_x = h->amax + kAmaxAct + l - 1;
+        }
         OCPPO_TRY(wgrad(h, dY, L.out_dim, X, L.in_dim, rows, h->grads + L.w_off, (int64_t)L.out_dim * L.in_dim,
-                        h->grads + L.b_off, L.out_dim, accumulate, s));
+                        h->grads + L.b_off, L.out_dim, accumulate, s, amax_dy, amax_x));
         if (l > 0) {
             SgemmArgs a{};
             a.A = dY; a.lda = L.out_dim;
@@ -260,6 +324,19 @@ static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, i
             // the layer below left its ReLU decisions as one bit per element (same row-major element order, so the
             // encoder -> decoder flatten does not matter): the tensor-core dgrad reads those instead of the activations
             if (h->relu_bits_valid[l - 1] && L.in_dim % 256 == 0) a.relu_bits = h->relu_bits[l - 1];
+            if (f16) {
+                a.amax_scratch = h->amax;
+                a.amax_a = amax_dy;
+                if (h->w_amax_valid) {
+                    a.amax_b = h->amax + kAmaxW + l;
+                    if (L.w_off % 8 == 0 && L.in_dim % 8 == 0) {
+                        a.b16_hi = reinterpret_cast<const uint16_t *>(h->w16_hi) + L.w_off;
+                        a.b16_lo = reinterpret_cast<const uint16_t *>(h->w16_lo) + L.w_off;
+                    }
+                }
+                dy_amax_valid = sgemm_uses_tc(SGEMM_DGRAD, a);
+                if (dy_amax_valid) a.amax_out = h->amax + kAmaxGrad + l - 1;
+            }
             OCPPO_TRY(sgemm_launch(SGEMM_DGRAD, a, s));
             cur ^= 1;
         }
@@ -283,7 +360,7 @@ int64_t ocppo_launch_count(void) {
 }
 
 int ocppo_set_gemm_mode(int32_t mode) {
-    OCPPO_CHECK_ARG(mode >= 0 && mode <= 4, "gemm mode must be 0 (fp32 FMA), 1 (tcgen05 3xTF32), 2 (3xTF32, single accumulator) or 3 (TF32 + BF16 corrections)");
+    OCPPO_CHECK_ARG(mode >= 0 && mode <= 5, "gemm mode must be 0 (fp32 FMA), 1 / 2 (tcgen05 3xTF32, split / single accumulator), 3 / 4 (TF32 + BF16 corrections, split / single) or 5 (FP16 x 3)");
     g_gemm_mode = mode;
     return OCPPO_OK;
 }
@@ -292,13 +369,25 @@ int ocppo_get_gemm_mode(void) { return g_gemm_mode; }
 int ocppo_gemm(int32_t op, int32_t engine, int32_t M, int32_t N, int64_t K, const float *A, int64_t lda,
                const float *B, int64_t ldb, float *C, int64_t ldc, const float *bias, const float *mask,
                float *bias_part, int32_t splits, int64_t k_per_split, void *stream) {
-    OCPPO_CHECK_ARG(op >= 0 && op <= 2 && engine >= 0 && engine <= 4, "bad op/engine");
+    OCPPO_CHECK_ARG(op >= 0 && op <= 2 && engine >= 0 && engine <= 5, "bad op/engine");
     OCPPO_CHECK_ARG(A && B && C, "null pointer");
     SgemmArgs a{};
     a.A = A; a.lda = lda; a.B = B; a.ldb = ldb; a.C = C; a.ldc = ldc; a.bias = bias; a.mask = mask;
     a.bias_part = bias_part; a.M = M; a.N = N; a.K = K; a.splits = splits < 1 ? 1 : splits;
     a.k_per_split = k_per_split > 0 ? k_per_split : round_up(K, 32);
-    if (engine >= 1) { a.single_acc = engine == 2 || engine == 4; a.corr_bf16 = engine >= 3; return tc_gemm_launch((SgemmMode)op, a, as_stream(stream)); }
+    if (engine >= 1) {
+        sgemm_engine_flags(engine, &a);
+        float *scratch = nullptr;
+        if (engine == 5) {              // test hook: the two operand maxima live in a transient allocation
+            OCPPO_CUDA(cudaMalloc(&scratch, 2 * sizeof(float)));
+            a.amax_scratch = scratch;
+            const int r0 = sgemm_fill_amax((SgemmMode)op, &a, as_stream(stream));
+            if (r0 != OCPPO_OK) { cudaFree(scratch); return r0; }
+        }
+        const int r = tc_gemm_launch((SgemmMode)op, a, as_stream(stream));
+        if (scratch != nullptr) { cudaStreamSynchronize(as_stream(stream)); cudaFree(scratch); }
+        return r;
+    }
     return fma_gemm_launch((SgemmMode)op, a, as_stream(stream));
 }
 
@@ -551,6 +640,7 @@ int ocppo_clip_adam(ocppo_handle *h, float inv_world, float max_grad_norm, doubl
     OCPPO_TRY(require_ready(h, true));
     OCPPO_CHECK_ARG(step >= 1, "Adam step is 1-based");
     OCPPO_CHECK_ARG(h->grads && h->exp_avg && h->exp_avg_sq, "grad/Adam arenas not bound");
+    h->w_amax_valid = 0;
     return launch_clip_adam(h, inv_world, max_grad_norm, lr, beta1, beta2, eps, step, grad_norm, as_stream(stream));
 }
 

@@ -1,6 +1,7 @@
 // Shared declarations for libocppo.so (sm_100a only).
 #pragma once
 #include <cuda_runtime.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdarg.h>
@@ -107,7 +108,15 @@ struct ocppo_handle {
     float *adv_stat;                    // mean, std
     double *norm_part;                  // [kNormBlocks]
     int last_forward_rows;
+    // FP16x3 tensor-core engine: max |.| per tensor as device scalars.  [0,1] scratch, then per trunk layer l:
+    // kAmaxAct + l = activations act[l], kAmaxW + l = weights, kAmaxGrad + l = gradient entering layer l's backward
+    float *amax;
+    int act_amax_valid[2 * OCPPO_MAX_LAYERS];
+    int w_amax_valid;
+    void *w16_hi, *w16_lo;              // the trunk weights split into scaled fp16 hi / lo (indexed like params)
 };
+constexpr int kAmaxAct = 2, kAmaxW = 2 + 2 * OCPPO_MAX_LAYERS, kAmaxGrad = 2 + 4 * OCPPO_MAX_LAYERS;
+constexpr int kAmaxSlots = 2 + 6 * OCPPO_MAX_LAYERS;
 
 namespace ocppo {
 
@@ -130,17 +139,58 @@ struct SgemmArgs {
     int dbg;                  // tc_gemm bring-up variant (0 in production)
     int single_acc;           // tc_gemm: 1 = one TMEM accumulator per tile (faster, ~3x the rounding error)
     int corr_bf16;            // tc_gemm: 1 = the two correction products run as BF16 MMAs (split accumulators only)
+    int f16x3;                // tc_gemm: 1 = three FP16 products on per-tensor power-of-two scaled operands (engine 5)
+    const float *amax_a;      // f16x3: device scalars, max |A| and max |B| (>= the true maxima); null = sgemm_launch
+    const float *amax_b;      //        measures them with a reduction pass into amax_scratch[0..1]
+    float *amax_out;          // optional (tensor-core FWD / DGRAD): atomicMax of |C| as float bits; caller zeroes it
+    float *amax_scratch;      // two floats of device scratch for the fallback reduction
+    const void *b16_hi;       // f16x3, FWD / DGRAD: B already split into fp16 hi / lo tensors (same shape and ldb, scaled by
+    const void *b16_lo;       //        the power of two that amax_b implies) -- the weights, split once per call
 };
 
 int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);       // dispatches FMA / tensor
 int fma_gemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);    // sgemm.cu, fp32 CUDA cores
 bool tc_gemm_supported(SgemmMode mode, const SgemmArgs &a);                      // tc_gemm.cu, tcgen05 3xTF32
 int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);
+void sgemm_engine_flags(int engine, SgemmArgs *b);                               // engine number -> tc_gemm variant flags
+int sgemm_fill_amax(SgemmMode mode, SgemmArgs *b, cudaStream_t stream);          // FP16x3: measure missing operand maxima
 bool sgemm_uses_tc(SgemmMode mode, const SgemmArgs &a);                          // what sgemm_launch will pick
 int tc_tile_n(bool single_acc);                                                   // N tile of the CTA pair: 128 (split accumulators) / 256
 // 0: fp32 FMA kernels only; 1: tcgen05 3xTF32 wherever the shape fits (fp32-grade accuracy; main and
 // correction products in separate TMEM accumulators); 2: same with a single, double-buffered accumulator
 extern int g_gemm_mode;
+
+// ---- FP16x3 operand split (tc_gemm.cu producers, absmax.cu weight pre-split) ----
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t pack_f16(float lo_elem, float hi_elem) {
+    uint32_t r;
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi_elem), "f"(lo_elem));
+    return r;
+}
+// scale 2^k with amax * 2^k in [2^14, 2^15), k clamped to [-100, 126]; inv = 2^-k
+__device__ __forceinline__ void f16_scale_of(float amax, float &scale, float &inv) {
+    const int e = (int)((__float_as_uint(amax) >> 23) & 0xFFu);        // biased exponent (0 for zero / subnormal)
+    int k = 14 - (e - 127);
+    k = k > 126 ? 126 : (k < -100 ? -100 : k);
+    if (e == 0 || e == 255) k = 0;                                     // all-zero tensor, or Inf / NaN: results follow the data
+    scale = __uint_as_float((uint32_t)(127 + k) << 23);
+    inv = __uint_as_float((uint32_t)(127 - k) << 23);
+}
+__device__ __forceinline__ void split_f16x2(float x, float y, float scale, uint32_t &hi, uint32_t &lo) {
+    x *= scale; y *= scale;
+    hi = pack_f16(x, y);
+    const float2 hf = __half22float2(*reinterpret_cast<const __half2 *>(&hi));
+    lo = pack_f16(x - hf.x, y - hf.y);
+}
+#endif
+
+struct AbsmaxSegs { const float *x[2 * OCPPO_MAX_LAYERS]; int64_t n[2 * OCPPO_MAX_LAYERS]; float *out[2 * OCPPO_MAX_LAYERS]; int count; };
+// hi[i] = fp16(x[i] s), lo[i] = fp16(x[i] s - hi[i]) per segment, s from the segment's max-abs (device scalar out[seg]);
+// hi / lo are indexed like x relative to segs.x[0]'s arena base `base`
+int launch_split_f16_multi(const AbsmaxSegs &segs, const float *base, void *hi, void *lo, cudaStream_t stream);
+int launch_absmax_multi(const AbsmaxSegs &segs, cudaStream_t stream);             // several small contiguous tensors, one launch; outs pre-zeroed
+// out[0] = max |x[r, c]| over an [rows, cols] view with row stride ld (zeroed first); absmax.cu
+int launch_absmax(const float *x, int64_t rows, int64_t cols, int64_t ld, float *out, int sm_count, cudaStream_t stream);
 
 int launch_gae(const float *rewards, const float *values, const float *dones,
                const float *next_value, const float *next_done, int64_t T, int64_t N, float g,

@@ -197,19 +197,41 @@ static int tc_ops_mask() {
     return ops_mask;
 }
 
+void sgemm_engine_flags(int engine, SgemmArgs *b) {
+    b->single_acc = engine == 2 || engine == 4;
+    b->corr_bf16 = engine >= 3;
+    b->f16x3 = engine == 5;
+}
+
 bool sgemm_uses_tc(SgemmMode mode, const SgemmArgs &a) {
     if (g_gemm_mode < 1 || !((tc_ops_mask() >> (int)mode) & 1)) return false;
     SgemmArgs b = a;
-    b.single_acc = g_gemm_mode == 2 || g_gemm_mode == 4;
-    b.corr_bf16 = g_gemm_mode >= 3;
+    sgemm_engine_flags(g_gemm_mode, &b);
     return tc_gemm_supported(mode, b);
+}
+
+// FP16x3 engine: operands whose max-abs the caller did not supply are measured here (one extra read of the operand)
+int sgemm_fill_amax(SgemmMode mode, SgemmArgs *b, cudaStream_t stream) {
+    if (!b->f16x3 || (b->amax_a != nullptr && b->amax_b != nullptr)) return OCPPO_OK;
+    OCPPO_CHECK_ARG(b->amax_scratch != nullptr, "sgemm: FP16x3 engine without operand maxima needs amax_scratch");
+    if (b->amax_a == nullptr) {
+        const bool kfirst = mode == SGEMM_WGRAD;                        // A is [K, M] for WGRAD, [M, K] otherwise
+        OCPPO_TRY(launch_absmax(b->A, kfirst ? b->K : b->M, kfirst ? b->M : b->K, b->lda, b->amax_scratch, 0, stream));
+        b->amax_a = b->amax_scratch;
+    }
+    if (b->amax_b == nullptr) {
+        const bool kfirst = mode != SGEMM_FWD;                          // B is [N, K] for FWD, [K, N] otherwise
+        OCPPO_TRY(launch_absmax(b->B, kfirst ? b->K : b->N, kfirst ? b->N : b->K, b->ldb, b->amax_scratch + 1, 0, stream));
+        b->amax_b = b->amax_scratch + 1;
+    }
+    return OCPPO_OK;
 }
 
 int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream) {
     if (sgemm_uses_tc(mode, a)) {
         SgemmArgs b = a;
-        b.single_acc = g_gemm_mode == 2 || g_gemm_mode == 4;
-        b.corr_bf16 = g_gemm_mode >= 3;
+        sgemm_engine_flags(g_gemm_mode, &b);
+        OCPPO_TRY(sgemm_fill_amax(mode, &b, stream));
         return tc_gemm_launch(mode, b, stream);
     }
     OCPPO_CHECK_ARG(mode != SGEMM_DGRAD || a.mask != nullptr, "sgemm: the FMA dgrad kernel needs the fp32 mask");

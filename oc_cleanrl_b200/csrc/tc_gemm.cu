@@ -22,6 +22,7 @@
 // remotely), empty (tcgen05.commit multicast to both CTAs), tmem_full / tmem_empty per accumulator.
 #include "common.cuh"
 #include <cuda.h>
+#include <cuda_fp16.h>
 #include <stdlib.h>
 
 namespace ocppo {
@@ -110,6 +111,25 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
             : "memory");
         if (done) break;
         if (clock64() - t0 > 4000000000LL) __trap();      // never hang the device on a protocol bug
+    }
+}
+
+// Long waits of warps that share an SM sub-partition with the producers (F16 engine: the conversion is on the
+// critical path and every poll takes an issue slot from it)
+__device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity, unsigned ns) {
+    const long long t0 = clock64();
+    uint32_t done = 0;
+    while (true) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (done) break;
+        __nanosleep(ns);
+        if (clock64() - t0 > 4000000000LL) __trap();
     }
 }
 
@@ -258,6 +278,36 @@ __device__ __forceinline__ void convert_operand_bf16(const uint8_t *raw, uint8_t
     }
 }
 
+// ---- FP16 x 3 (engine 5) ----------------------------------------------------------------------------------
+// fp16 carries the same 11 significant bits as TF32 at twice the MMA rate, so with x.s = h + l (h = fp16(x.s),
+// l = fp16(x.s - h), s a power of two that puts the tensor's largest magnitude in [2^14, 2^15)) the product is
+//   a.b = [ h_a.h_b + (h_a.l_b + l_a.h_b) ] / (s_a s_b)               -- three kind::f16 passes instead of TF32 + 2 BF16
+// (3 instead of 4 BF16-rate passes).  Dropped: l_a.l_b, 2^-22 relative.  The scale is exact (powers of two) and comes
+// from the tensor's max-abs, which the producing kernel's epilogue tracks (SgemmArgs::amax_*): elements below
+// 2^-29 of the tensor's maximum go subnormal in h (below 2^-18 in l), i.e. keep an ABSOLUTE accuracy of 2^-40 of the
+// maximum -- sixteen binary orders below the fp32 rounding of the large elements of the same tensor.
+__host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N, bool a_mn_major, bool b_mn_major) {
+    return (1u << 4) | ((a_mn_major ? 1u : 0u) << 15) | ((b_mn_major ? 1u : 0u) << 16) |
+           ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+template <bool MN, bool SUM>
+__device__ __forceinline__ void convert_operand_f16(const uint8_t *raw, uint8_t *hi16, uint8_t *lo16, int p, float scale,
+                                                    float4 &colsum) {
+    float4 v[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) v[q] = *reinterpret_cast<const float4 *>(raw + (MN ? off_mnmajor(p, q) : off_kmajor(p, q)));
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        if (SUM) { colsum.x += v[q].x; colsum.y += v[q].y; colsum.z += v[q].z; colsum.w += v[q].w; }
+        const int o = MN ? off16_mnmajor(p, q) : off16_kmajor(p, q);
+        uint32_t h0, l0, h1, l1;
+        split_f16x2(v[q].x, v[q].y, scale, h0, l0);
+        split_f16x2(v[q].z, v[q].w, scale, h1, l1);
+        *reinterpret_cast<uint2 *>(hi16 + o) = make_uint2(h0, h1);
+        *reinterpret_cast<uint2 *>(lo16 + o) = make_uint2(l0, l1);
+    }
+}
+
 // ---- TMA ----------------------------------------------------------------------
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
@@ -327,19 +377,21 @@ __device__ __forceinline__ TileCoord tile_coord(const SgemmArgs &p, int tile, in
         : "r"(taddr)                                                                                                \
         : "memory")
 
-template <int MODE, bool SPLIT, bool CORR16>
+template <int MODE, bool SPLIT, int CORR>      // CORR: 0 = TF32 corrections, 1 = BF16 corrections, 2 = FP16 x 3 (no TF32 pass)
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_gemm_kernel(SgemmArgs p, int nt_n, int nt_m, int ntiles, const __grid_constant__ CUtensorMap tmA,
                                                                                          const __grid_constant__ CUtensorMap tmB,
                                                                                          const __grid_constant__ CUtensorMap tmC,
-                                                                                         const __grid_constant__ CUtensorMap tmX) {
+                                                                                         const __grid_constant__ CUtensorMap tmX,
+                                                                                         const __grid_constant__ CUtensorMap tmB2) {
     constexpr bool A_MN = (MODE == SGEMM_WGRAD);
     constexpr bool B_MN = (MODE != SGEMM_FWD);
+    constexpr bool CORR16 = CORR >= 1, F16 = CORR == 2;
     constexpr int TN = Tile<SPLIT>::TN, TBW = Tile<SPLIT>::TBW, kStageBytesB = Tile<SPLIT>::kStageBytesB;
     constexpr int kStageBytes = Tile<SPLIT>::kStageBytes, kNumStages = Tile<SPLIT>::kNumStages;
     constexpr int kAccStride = Tile<SPLIT>::kAccStride, kAccBufs = Tile<SPLIT>::kAccBufs;
     // MMA instructions chained into the (main) accumulator per 32-deep stage: 4 main products, plus the corrections when
     // they share the accumulator (8 TF32 or 4 BF16; a K = 16 BF16 instruction loses about 1.5x what a K = 8 TF32 one does)
-    constexpr int kMmaPerStage = SPLIT ? 4 : (CORR16 ? 10 : 12);
+    constexpr int kMmaPerStage = SPLIT ? (F16 ? 3 : 4) : (CORR16 ? 10 : 12);   // F16: two K = 16 instructions
     // stage layout.  3xTF32: [A raw = hi 16K][A lo 16K][B raw = hi 16K][B lo 16K];
     // CORR16:  [A raw 16K][B raw 16K][A bf16 8K][A lo bf16 8K][B bf16 8K][B lo bf16 8K]
     constexpr int kOffA = 0, kOffB = CORR16 ? kStageBytesA : 2 * kStageBytesA;
@@ -370,6 +422,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
     const int ncl = gridDim.x >> 1, cl = blockIdx.x >> 1;    // clusters in the grid, this cluster
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    float scale_a = 1.f, scale_b = 1.f, inv_a = 1.f, inv_b = 1.f;      // FP16 x 3: per-tensor power-of-two scales
+    if (F16) {
+        f16_scale_of(__ldg(p.amax_a), scale_a, inv_a);
+        f16_scale_of(__ldg(p.amax_b), scale_b, inv_b);
+    }
     // The TMEM accumulator adds with round-toward-zero (tools/tc_probe.cu Q4): every MMA chained into it costs
     // about half an ulp of bias, and two of the three passes only add tiny correction products.  With SPLIT
     // those go to a second accumulator (the tile's columns [TN, 2 TN)) that the epilogue adds in fp32
@@ -381,7 +438,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
             mbar_init(bar_full + 8 * s, 2 * kProdWarps);     // both CTAs' producer warps
             mbar_init(bar_empty + 8 * s, 1);
             mbar_init(bar_tma + 8 * s, 1);
-            mbar_init(bar_rawfull + 8 * s, 2);               // one forwarder per CTA
+            mbar_init(bar_rawfull + 8 * s, F16 ? kProdWarps : 2);   // one forwarder per CTA | F16: raw tile consumed (own producers)
         }
         for (int w = 0; w < kEpiWarps; ++w) mbar_init(bar_aux + 8 * w, 1);
         for (int a = 0; a < 2; ++a) {
@@ -417,6 +474,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
         const int swz = lane & 7;
         uint32_t aux_phase = 0;
         int ai = 0;                           // accumulator passes handled so far (tile x k-segment)
+        float run_max = 0.f;                  // max |output| of this lane's rows (p.amax_out: the consumer's FP16 scale)
         for (int tile = cl; tile < ntiles; tile += ncl) {
           const TileCoord t = tile_coord(p, tile, nt_n, nt_m, TN);
           for (int kb0 = 0; kb0 < t.nk; kb0 += kSegStages, ++ai) {
@@ -449,7 +507,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
             uint4 rb = make_uint4(0u, 0u, 0u, 0u);
             const int64_t rb_off = (int64_t)(m_loc + lane) * (p.N >> 5) + (n_loc >> 5);
             if (bits && m_loc + lane < p.M) rb = __ldg(reinterpret_cast<const uint4 *>(p.relu_bits + rb_off));
-            mbar_wait(bar_tfull + 8 * acc, (uint32_t)((ai / nbuf) & 1));
+            if (F16) mbar_wait_sleep(bar_tfull + 8 * acc, (uint32_t)((ai / nbuf) & 1), 200);
+            else mbar_wait(bar_tfull + 8 * acc, (uint32_t)((ai / nbuf) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             if (!live) {
                 asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -486,7 +545,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                 for (int j = 0; j < 32; ++j) {
                     float x = __uint_as_float(v[j]);
                     x = fmaf(x, trunc_comp, x);
-                    if (split_acc) x += __uint_as_float(w[j]);
+                    if (F16) x = ((x + __uint_as_float(w[j])) * inv_a) * inv_b;
+                    else if (split_acc) x += __uint_as_float(w[j]);
                     v[j] = __float_as_uint(x);
                 }
                 __syncwarp();
@@ -518,6 +578,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                         o.x += ax[c].x; o.y += ax[c].y; o.z += ax[c].z; o.w += ax[c].w;
                     }
                     *reinterpret_cast<float4 *>(out_tile + lane * 128 + ((c ^ swz) << 4)) = o;
+                    if (MODE != SGEMM_WGRAD && m_loc + lane < p.M) run_max = fmaxf(fmaxf(run_max, fmaxf(fabsf(o.x), fabsf(o.y))), fmaxf(fabsf(o.z), fabsf(o.w)));
                 }
                 if (MODE == SGEMM_FWD && p.relu_bits != nullptr && m_loc + lane < p.M) p.relu_bits[rb_off + cc] = word;
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -537,6 +598,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
           }
         }
         if (lane == 0) bulk_wait_all0();       // all stores of this warp complete before the CTA may exit
+        if (MODE != SGEMM_WGRAD && p.amax_out != nullptr) {
+            const uint32_t m = __reduce_max_sync(0xffffffffu, __float_as_uint(run_max));   // non-negative floats order as uints
+            if (lane == 0) atomicMax(reinterpret_cast<unsigned int *>(p.amax_out), m);
+        }
     } else if (warp < kEpiWarps + 4) {
         // ===================== MMA issuer (warp 8; warps 10-11 idle) =====================
         if (warp == kEpiWarps && lane == 0 && cta_rank == 0) {
@@ -560,7 +625,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                     // The main product reads only the raw tiles: it starts as soon as both CTAs' TMA loads have landed
                     // and runs while the producers are still deriving the correction operands of the same stage.
                     const int s = stage, fphase = sphase;
-                    mbar_wait(bar_rawfull + 8 * s, (uint32_t)fphase);
+                    if (!F16) mbar_wait(bar_rawfull + 8 * s, (uint32_t)fphase);
                     if (++stage == kNumStages) { stage = 0; sphase ^= 1; }
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     uint8_t *st = smem + s * kStageBytes;
@@ -578,6 +643,24 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                         const uint64_t db16 = make_desc(smem_u32(st) + kOffB16, b16_lbo, b16_sbo, b16_ty);
                         const uint64_t da16lo = make_desc(a_lo, a16_lbo, a16_sbo, a16_ty);
                         const uint64_t db16lo = make_desc(b_lo, b16_lbo, b16_sbo, b16_ty);
+                        if (F16) {
+                            // all three products need the producers' tiles: h.h into the main accumulator, h.l + l.h
+                            // (2^-11 of it, applied by the epilogue) into the correction accumulator
+                            constexpr uint32_t idescf = make_idesc_f16(kPairM, TN, A_MN, B_MN);
+                            mbar_wait(bar_full + 8 * s, (uint32_t)fphase);
+                            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+                            for (int k2 = 0; k2 < TK / 16; ++k2)
+                                umma_bf16(d_tmem, da16 + k2 * a16_step, db16 + k2 * b16_step, idescf, (kb > kb0 || k2 > 0) ? 1u : 0u);
+                            if (!(p.dbg & 32))       // timing experiment: main product only
+#pragma unroll
+                            for (int k2 = 0; k2 < TK / 16; ++k2) {
+                                umma_bf16(d_tmem + TN, da16lo + k2 * a16_step, db16 + k2 * b16_step, idescf, (kb > kb0 || k2 > 0) ? 1u : 0u);
+                                umma_bf16(d_tmem + TN, da16 + k2 * a16_step, db16lo + k2 * b16_step, idescf, 1u);
+                            }
+                            umma_commit_pair(bar_empty + 8 * s);
+                            continue;
+                        }
 #pragma unroll
                         for (int ks = 0; ks < TK / 8; ++ks)
                             umma_tf32(d_tmem, da_hi + ks * a_step, db_hi + ks * b_step, idesc, (kb > kb0 || ks > 0) ? 1u : 0u);
@@ -619,20 +702,34 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                 const TileCoord t = tile_coord(p, tile, nt_n, nt_m, TN);
                 for (int kb = 0; kb < t.nk; ++kb) {
                     const int s = stage;
-                    mbar_wait(bar_empty + 8 * s, (uint32_t)(sphase ^ 1));
+                    // F16: nothing but the producers reads the raw tiles, so they are refilled as soon as the conversion
+                    // has consumed them -- one MMA stage earlier than the converted tiles come free
+                    mbar_wait((F16 ? bar_rawfull : bar_empty) + 8 * s, (uint32_t)(sphase ^ 1));
                     const uint32_t a_hi = smem_u32(smem + s * kStageBytes) + kOffA, b_hi = smem_u32(smem + s * kStageBytes) + kOffB;
                     const uint32_t bar = bar_tma + 8 * s;
                     const int k0 = (int)(t.kbeg + (int64_t)kb * TK);
                     mbar_expect_tx(bar, kStageBytesA + kStageBytesB);
                     if (A_MN) tma_load_3d(a_hi, &tmA, 0, k0, (t.m0 + rank_m) >> 5, bar);
                     else tma_load_2d(a_hi, &tmA, k0, t.m0 + rank_m, bar);
-                    if (B_MN) tma_load_3d(b_hi, &tmB, 0, k0, (t.n0 + rank_n) >> 5, bar);
+                    if (F16 && MODE != SGEMM_WGRAD && p.b16_hi != nullptr) {
+                        // B (the layer's weights) was split into fp16 hi / lo tensors once per call: its tiles arrive in
+                        // the MMA's layout (tmB = hi, tmB2 = lo) and wait for the MMAs of the stage's previous use
+                        const uint32_t b16h = smem_u32(smem + s * kStageBytes) + kOffB16, b16l = smem_u32(smem + s * kStageBytes) + kOffBLo;
+                        mbar_wait(bar_empty + 8 * s, (uint32_t)(sphase ^ 1));
+                        if (B_MN) {
+                            tma_load_3d(b16h, &tmB, 0, k0, (t.n0 + rank_n) >> 6, bar);
+                            tma_load_3d(b16l, &tmB2, 0, k0, (t.n0 + rank_n) >> 6, bar);
+                        } else {
+                            tma_load_2d(b16h, &tmB, k0, t.n0 + rank_n, bar);
+                            tma_load_2d(b16l, &tmB2, k0, t.n0 + rank_n, bar);
+                        }
+                    } else if (B_MN) tma_load_3d(b_hi, &tmB, 0, k0, (t.n0 + rank_n) >> 5, bar);
                     else tma_load_2d(b_hi, &tmB, k0, t.n0 + rank_n, bar);
                     if (++stage == kNumStages) { stage = 0; sphase ^= 1; }
                 }
             }
         }
-        else if (warp == kEpiWarps + 2 && lane == 0) {
+        else if (!F16 && warp == kEpiWarps + 2 && lane == 0) {
             // ===================== raw-tile forwarder (warp 10, both CTAs) =====================
             // tells the leader's MMA issuer that this CTA's raw tiles of a stage have landed
             int stage = 0, sphase = 0;
@@ -661,7 +758,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                 mbar_wait(bar_tma + 8 * s, (uint32_t)sphase);           // raw tile landed (TMA complete_tx)
                 uint8_t *st = smem + s * kStageBytes;
                 uint8_t *a_hi = st + kOffA, *a_lo = st + kOffALo, *b_hi = st + kOffB, *b_lo = st + kOffBLo;
-                if (CORR16) {
+                if (F16) {
+                    mbar_wait(bar_empty + 8 * s, (uint32_t)(sphase ^ 1));    // the MMAs of the previous use have read the fp16 tiles
+                    if (p.dbg & 16) { /* timing experiment: no conversion */ } else
+                    if (A_MN && do_bias) convert_operand_f16<A_MN, true>(a_hi, st + kOffA16, a_lo, pt, scale_a, bsum);
+                    else convert_operand_f16<A_MN, false>(a_hi, st + kOffA16, a_lo, pt, scale_a, bsum);
+                    if (MODE == SGEMM_WGRAD || p.b16_hi == nullptr) convert_operand_f16<B_MN, false>(b_hi, st + kOffB16, b_lo, pt, scale_b, bsum);
+                } else if (CORR16) {
                     if (A_MN && do_bias) convert_operand_bf16<A_MN, true>(a_hi, st + kOffA16, a_lo, pt, bsum);
                     else convert_operand_bf16<A_MN, false>(a_hi, st + kOffA16, a_lo, pt, bsum);
                     convert_operand_bf16<B_MN, false>(b_hi, st + kOffB16, b_lo, pt, bsum);
@@ -669,7 +772,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                 else convert_stage<A_MN, B_MN, false, TBW>(a_hi, a_lo, b_hi, b_lo, pt, bsum);
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
-                if (pwarp_lane0) mbar_arrive_on(bar_full + 8 * s, 0);      // the leader CTA's barrier
+                if (pwarp_lane0) {
+                    mbar_arrive_on(bar_full + 8 * s, 0);      // the leader CTA's barrier
+                    if (F16) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_rawfull + 8 * s) : "memory");
+                }
                 if (++stage == kNumStages) { stage = 0; sphase ^= 1; }
             }
             if (MODE == SGEMM_WGRAD) {
@@ -762,6 +868,31 @@ int make_map(CUtensorMap *tm, const float *base, bool mn_major, int64_t rows_or_
     return OCPPO_OK;
 }
 
+// fp16 operand that is already split and scaled in global memory (same shape / stride as the fp32 one): tiles arrive in
+// the layouts the producers write -- K-major [rows][32 k] = 64-byte rows, SWIZZLE_64B; MN-major [chunk][32 k][64], SWIZZLE_128B
+int make_map16(CUtensorMap *tm, const void *base, bool mn_major, int64_t rows_or_cols, int64_t K, int64_t ld, int box_mn) {
+    EncodeTiledFn fn = encode_fn();
+    if (fn == nullptr) { set_error("cuTensorMapEncodeTiled entry point not available"); return OCPPO_ECUDA; }
+    CUresult r;
+    if (!mn_major) {
+        const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows_or_cols};
+        const cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+        const cuuint32_t box[2] = {32, (cuuint32_t)box_mn}, estr[2] = {1, 1};
+        r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    } else {
+        const cuuint64_t dims[3] = {64, (cuuint64_t)K, (cuuint64_t)(rows_or_cols / 64)};
+        const cuuint64_t strides[2] = {(cuuint64_t)ld * 2, 128};
+        const cuuint32_t box[3] = {64, 32, (cuuint32_t)(box_mn / 64)}, estr[3] = {1, 1, 1};
+        r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void *>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    }
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (fp16 operand) failed (%d)", (int)r); return OCPPO_ECUDA; }
+    return OCPPO_OK;
+}
+
 // Output (and aux: DGRAD mask, WGRAD running partial) [rows, cols] row-major: 2-D map {cols, rows}, box 32 x 32,
 // SWIZZLE_128B -- one epilogue warp's chunk.  Rows past `rows` are clipped on store and zero-filled on load.
 int make_map_c(CUtensorMap *tm, const float *base, int64_t rows, int64_t cols, int64_t ld) {
@@ -791,31 +922,41 @@ int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
     const int64_t ntiles64 = (int64_t)nt_n * nt_m * splits;
     OCPPO_CHECK_ARG(ntiles64 < (1LL << 31), "tc_gemm: too many tiles");
     const int ntiles = (int)ntiles64;
-    typedef void (*Kern)(SgemmArgs, int, int, int, const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap);
-    static const Kern kerns[4][3] = {
-        {tc_gemm_kernel<SGEMM_FWD, false, false>, tc_gemm_kernel<SGEMM_DGRAD, false, false>, tc_gemm_kernel<SGEMM_WGRAD, false, false>},
-        {tc_gemm_kernel<SGEMM_FWD, true, false>, tc_gemm_kernel<SGEMM_DGRAD, true, false>, tc_gemm_kernel<SGEMM_WGRAD, true, false>},
-        {tc_gemm_kernel<SGEMM_FWD, true, true>, tc_gemm_kernel<SGEMM_DGRAD, true, true>, tc_gemm_kernel<SGEMM_WGRAD, true, true>},
-        {tc_gemm_kernel<SGEMM_FWD, false, true>, tc_gemm_kernel<SGEMM_DGRAD, false, true>, tc_gemm_kernel<SGEMM_WGRAD, false, true>}};
+    typedef void (*Kern)(SgemmArgs, int, int, int, const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap);
+    static const Kern kerns[5][3] = {
+        {tc_gemm_kernel<SGEMM_FWD, false, 0>, tc_gemm_kernel<SGEMM_DGRAD, false, 0>, tc_gemm_kernel<SGEMM_WGRAD, false, 0>},
+        {tc_gemm_kernel<SGEMM_FWD, true, 0>, tc_gemm_kernel<SGEMM_DGRAD, true, 0>, tc_gemm_kernel<SGEMM_WGRAD, true, 0>},
+        {tc_gemm_kernel<SGEMM_FWD, true, 1>, tc_gemm_kernel<SGEMM_DGRAD, true, 1>, tc_gemm_kernel<SGEMM_WGRAD, true, 1>},
+        {tc_gemm_kernel<SGEMM_FWD, false, 1>, tc_gemm_kernel<SGEMM_DGRAD, false, 1>, tc_gemm_kernel<SGEMM_WGRAD, false, 1>},
+        {tc_gemm_kernel<SGEMM_FWD, true, 2>, tc_gemm_kernel<SGEMM_DGRAD, true, 2>, tc_gemm_kernel<SGEMM_WGRAD, true, 2>}};
     static int sms = 0;
     if (sms == 0) {
         int dev = 0;
         OCPPO_CUDA(cudaGetDevice(&dev));
         OCPPO_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        for (int i = 0; i < 4; ++i)
+        for (int i = 0; i < 5; ++i)
             for (int j = 0; j < 3; ++j)
                 OCPPO_CUDA(cudaFuncSetAttribute(kerns[i][j], cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
     }
     const int grid = 2 * (ntiles < sms / 2 ? ntiles : sms / 2);     // CTA pairs
-    CUtensorMap tmA, tmB, tmC, tmX;
+    CUtensorMap tmA, tmB, tmC, tmX, tmB2;
     OCPPO_TRY(make_map(&tmA, a.A, mode == SGEMM_WGRAD, a.M, a.K, a.lda, TM));
-    OCPPO_TRY(make_map(&tmB, a.B, mode != SGEMM_FWD, a.N, a.K, a.ldb, tn / 2));
+    if (!(a.f16x3 && mode != SGEMM_WGRAD)) { a.b16_hi = nullptr; a.b16_lo = nullptr; }
+    if (a.b16_hi != nullptr) {
+        OCPPO_CHECK_ARG(a.b16_lo != nullptr && (a.ldb & 7) == 0 && al16(a.b16_hi) && al16(a.b16_lo), "tc_gemm: bad pre-split B operand");
+        OCPPO_TRY(make_map16(&tmB, a.b16_hi, mode != SGEMM_FWD, a.N, a.K, a.ldb, tn / 2));
+        OCPPO_TRY(make_map16(&tmB2, a.b16_lo, mode != SGEMM_FWD, a.N, a.K, a.ldb, tn / 2));
+    } else {
+        OCPPO_TRY(make_map(&tmB, a.B, mode != SGEMM_FWD, a.N, a.K, a.ldb, tn / 2));
+        tmB2 = tmB;
+    }
     OCPPO_TRY(make_map_c(&tmC, a.C, (int64_t)a.M * splits, a.N, a.ldc));
     if (mode == SGEMM_DGRAD) OCPPO_TRY(make_map_c(&tmX, a.mask, a.M, a.N, a.ldc));
     else tmX = tmC;
     const int mi = mode == SGEMM_FWD ? 0 : (mode == SGEMM_DGRAD ? 1 : 2);
     ProfScope ps(mode == SGEMM_FWD ? KC_SGEMM_FWD : (mode == SGEMM_DGRAD ? KC_SGEMM_DGRAD : KC_SGEMM_WGRAD), 1, stream);
-    kerns[split ? (a.corr_bf16 ? 2 : 1) : (a.corr_bf16 ? 3 : 0)][mi]<<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles, tmA, tmB, tmC, tmX);
+    OCPPO_CHECK_ARG(!a.f16x3 || (split && a.amax_a != nullptr && a.amax_b != nullptr), "tc_gemm: the FP16x3 engine needs both operands' max-abs");
+    kerns[a.f16x3 ? 4 : (split ? (a.corr_bf16 ? 2 : 1) : (a.corr_bf16 ? 3 : 0))][mi]<<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles, tmA, tmB, tmC, tmX, tmB2);
     OCPPO_LAUNCH_CHECK("tc_gemm_kernel");
     return OCPPO_OK;
 }

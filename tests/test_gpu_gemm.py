@@ -19,7 +19,7 @@ CASES = [
 ]
 
 
-@pytest.mark.parametrize("engine", [0, 1, 2, 3, 4])
+@pytest.mark.parametrize("engine", [0, 1, 2, 3, 4, 5])
 @pytest.mark.parametrize("op,M,N,K,S", CASES)
 def test_gemm_engine_vs_fp64(built_lib, engine, op, M, N, K, S):
     import gemm_diag
@@ -38,5 +38,6 @@ def test_gemm_mode_switch_roundtrip(built_lib):
     assert built_lib.ocppo_set_gemm_mode(2) == 0 and built_lib.ocppo_get_gemm_mode() == 2
     assert built_lib.ocppo_set_gemm_mode(3) == 0 and built_lib.ocppo_get_gemm_mode() == 3
     assert built_lib.ocppo_set_gemm_mode(4) == 0 and built_lib.ocppo_get_gemm_mode() == 4
+    assert built_lib.ocppo_set_gemm_mode(5) == 0 and built_lib.ocppo_get_gemm_mode() == 5
     assert built_lib.ocppo_set_gemm_mode(default) == 0
     assert built_lib.ocppo_set_gemm_mode(7) == -1

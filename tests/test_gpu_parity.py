@@ -27,12 +27,12 @@ def dev(built_lib):
     return torch.device("cuda:0")
 
 
-@pytest.fixture(params=["fma", "tc", "tc16"])
+@pytest.fixture(params=["fma", "tc", "tc16", "f16"])
 def gemm_engine(request, built_lib):
     """Runs the test once per trunk GEMM engine: fp32 CUDA-core FMA, tcgen05 3xTF32, tcgen05 TF32 + BF16 corrections."""
     default = built_lib.ocppo_get_gemm_mode()
-    assert built_lib.ocppo_set_gemm_mode({"fma": 0, "tc": 1, "tc16": 3}[request.param]) == 0
-    yield "tc" if request.param == "tc16" else request.param
+    assert built_lib.ocppo_set_gemm_mode({"fma": 0, "tc": 1, "tc16": 3, "f16": 5}[request.param]) == 0
+    yield "tc" if request.param in ("tc16", "f16") else request.param
     built_lib.ocppo_set_gemm_mode(default)
 
 
@@ -364,6 +364,41 @@ def test_update_vs_live_oracle_pong_default_dims(dev, gemm_engine):
                        np_rng=np.random.RandomState(5))
     assert rel_err(agent_flat(agent1), ref_ppo.flat_params(oracle1).numpy()) < REL_TOL
     assert np.allclose(got_stats, want_stats, rtol=0.02, atol=1e-3)        # later minibatches: chaotic amplification
+
+
+@pytest.mark.parametrize("game,D,A", [("spaceinvaders", 88, 6), ("breakout", 220, 4)])
+def test_single_update_step_vs_live_oracle_other_games(dev, game, D, A, gemm_engine):
+    """Configs 3a / 3b (SURVEY section 8 size table): SpaceInvaders- and Breakout-shaped observations and action
+    sets at the default widths.  One Adam step over a 2,048-sample batch from identical weights: loss statistics,
+    gradient norm and post-step weights vs the CPU oracle.  (First-layer K = 4*D = 352 / 880; 880 is not a
+    multiple of the tensor-core k-tile, so this also covers the engine selection for ragged K.)"""
+    from oc_cleanrl_b200.learner import LearnerArgs, PPOLearner, compute_gae
+    F, T, N = 4, 128, 16
+    enc, dec = (256, 512, 1024, 512), (512,)
+    agent, oracle = make_pair(dev, F, D, A, enc, dec)
+    data = make_rollout(T, N, F, D, seed=77)
+    obs = data["obs"].to(dev)
+    torch.cuda.manual_seed(3)
+    with torch.no_grad():
+        action, logp, _, value = agent.get_action_and_value(obs.reshape(T * N, F, D))
+        next_value = agent.get_value(data["next_obs"].to(dev)).reshape(-1)
+    assert int(action.max()) < A and int(action.min()) >= 0
+    values = value.reshape(T, N)
+    args = LearnerArgs(num_envs=N, num_steps=T, update_epochs=1, num_minibatches=1)
+    adv, ret = compute_gae(data["rewards"].to(dev), values, data["dones"].to(dev), next_value,
+                           data["next_done"].to(dev), args.gamma, args.gae_lambda)
+    learner = PPOLearner(agent, args, np_rng=np.random.RandomState(5))
+    out = learner.update(obs, action.reshape(T, N), logp.reshape(T, N), adv, ret, values)
+    oargs = ref_ppo.PPOArgs(num_envs=N, num_steps=T, update_epochs=1, num_minibatches=1)
+    trace = []
+    ref_ppo.ref_update(oracle, ref_ppo.make_optimizer(oracle, oargs), data["obs"], action.cpu().reshape(T, N),
+                       logp.cpu().reshape(T, N), adv.cpu(), ret.cpu(), values.cpu(), oargs,
+                       np_rng=np.random.RandomState(5), trace=trace)
+    want = np.array([float(trace[0]["stats"][k]) for k in STAT_KEYS])
+    got = learner._stats[0, :7].cpu().numpy()
+    assert np.allclose(got, want, rtol=REL_TOL, atol=1e-6), (got, want)
+    assert np.allclose(out["grad_norms"][0], float(trace[0]["gn"]), rtol=REL_TOL)
+    assert rel_err(agent_flat(agent), ref_ppo.flat_params(oracle).numpy()) < REL_TOL
 
 
 def test_chunked_minibatch_is_equivalent_and_deterministic(dev):
