@@ -190,7 +190,7 @@ int dispatch(const SgemmArgs &a, bool av, bool bv, dim3 grid, cudaStream_t s) {
 
 }  // namespace
 
-int g_gemm_mode = 3;   // tcgen05: TF32 main product + two BF16 correction products; see ocppo_set_gemm_mode
+int g_gemm_mode = 5;   // tcgen05: three FP16 passes on power-of-two scaled operands; see ocppo_set_gemm_mode
 
 static int tc_ops_mask() {
     static const int ops_mask = getenv("OCPPO_TC_OPS") ? atoi(getenv("OCPPO_TC_OPS")) : 7;   // bring-up: bit per op

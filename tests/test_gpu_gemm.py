@@ -31,6 +31,19 @@ def test_gemm_engine_vs_fp64(built_lib, engine, op, M, N, K, S):
         assert float(msg.split("bias_rel=")[1].split()[0]) < 2e-5, msg
 
 
+@pytest.mark.parametrize("kind", ["wide", "big", "small", "zero", "relu", "tiny+relu"])
+@pytest.mark.parametrize("op,M,N,K,S", [(0, 1000, 512, 256, 1), (1, 640, 1024, 512, 1), (2, 256, 512, 8192, 4)])
+def test_gemm_fp16_engine_operand_ranges(built_lib, op, M, N, K, S, kind):
+    """Engine 5 scales every operand tensor by a power of two derived from its max-abs: magnitudes far from 1, nine
+    decades of spread inside one tensor, and all-zero operands must neither overflow nor lose the result."""
+    import gemm_diag
+    if "+" in kind and op != 2:
+        pytest.skip("mixed operand kinds are a WGRAD case")
+    msg = gemm_diag.run(op, 5, M, N, K, S, kind, seed=11 + op)
+    assert "BAD" not in msg and "rc=" not in msg, msg
+    assert float(msg.split("rel_err=")[1].split()[0]) < 2e-5, msg
+
+
 def test_gemm_mode_switch_roundtrip(built_lib):
     default = built_lib.ocppo_get_gemm_mode()
     assert built_lib.ocppo_set_gemm_mode(1) == 0 and built_lib.ocppo_get_gemm_mode() == 1

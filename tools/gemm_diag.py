@@ -24,6 +24,15 @@ def run(op, engine, M, N, K, splits=1, kind="randn", seed=0):
             return torch.randint(-4, 5, shape, device=dev, generator=g).float()
         if kind == "tiny":
             return torch.randn(*shape, device=dev, generator=g) * 1e-7
+        if kind == "wide":          # nine decades of dynamic range inside one tensor
+            e = torch.rand(*shape, device=dev, generator=g) * 9.0 - 6.0
+            return torch.randn(*shape, device=dev, generator=g) * torch.pow(10.0, e)
+        if kind == "big":
+            return torch.randn(*shape, device=dev, generator=g) * 1e15
+        if kind == "small":
+            return torch.randn(*shape, device=dev, generator=g) * 1e-15
+        if kind == "zero":
+            return torch.zeros(*shape, device=dev)
         if kind == "relu":          # post-ReLU-like: half exact zeros, large positive values
             return torch.relu(torch.randn(*shape, device=dev, generator=g)) * 50.0
         return torch.randn(*shape, device=dev, generator=g)
