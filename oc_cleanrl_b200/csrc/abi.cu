@@ -220,10 +220,10 @@ static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_
                 a.b16_hi = reinterpret_cast<const uint16_t *>(h->w16_hi) + L.w_off;
                 a.b16_lo = reinterpret_cast<const uint16_t *>(h->w16_lo) + L.w_off;
             }
-            if (tc) a.amax_out = h->amax + kAmaxAct + l;
+            a.amax_out = h->amax + kAmaxAct + l;          // both kernels track it
         }
         OCPPO_TRY(sgemm_launch(SGEMM_FWD, a, s));
-        if (f16 && tc) h->act_amax_valid[l] = 1;
+        if (f16) h->act_amax_valid[l] = 1;
         in = h->act[l];
     }
     h->last_forward_rows = (int)B;
@@ -289,10 +289,11 @@ static int wgrad(ocppo_handle *h, const float *dY, int out, const float *X, int 
 }
 
 // g0 holds d loss / d pre-activation of the last trunk layer, [B, hidden].
-static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, int accumulate, cudaStream_t s) {
+static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, int accumulate, cudaStream_t s,
+                          bool top_amax_tracked = false) {
     const bool f16 = g_gemm_mode == 5;
-    bool dy_amax_valid = false;
-    if (f16) {
+    bool dy_amax_valid = f16 && top_amax_tracked;   // the caller zeroed the gradient slots and the loss head filled the top one
+    if (f16 && !top_amax_tracked) {
         // max |dY| of the top layer comes from one reduction pass; the dgrad epilogues track the layers below
         OCPPO_CUDA(cudaMemsetAsync(h->amax + kAmaxGrad, 0, 2 * OCPPO_MAX_LAYERS * sizeof(float), s));
         const Layer &LT = h->layers[h->n_layers - 1];
@@ -598,6 +599,11 @@ int ocppo_minibatch_fwd_bwd(ocppo_handle *h, const float *b_obs, const int64_t *
         a.clip_f = (float)hp->clip_coef; a.ent_coef = (float)hp->ent_coef; a.vf_coef = (float)hp->vf_coef;
         a.norm_adv = hp->norm_adv; a.clip_vloss = hp->clip_vloss;
         a.dh = h->gbuf[0]; a.gz = h->gz;
+        const bool f16 = g_gemm_mode == 5;
+        if (f16) {
+            OCPPO_CUDA(cudaMemsetAsync(h->amax + kAmaxGrad, 0, 2 * OCPPO_MAX_LAYERS * sizeof(float), s));
+            a.dh_amax = h->amax + kAmaxGrad + h->n_layers - 1;
+        }
         a.part = h->loss_part + (int64_t)used * 8;
         int blocks = 0;
         const int avail = (int)((kLossBlocksMax - used) / (n_chunks - ci));
@@ -629,7 +635,7 @@ int ocppo_minibatch_fwd_bwd(ocppo_handle *h, const float *b_obs, const int64_t *
             OCPPO_TRY(launch_splitk_reduce(h->splitk_bias, g.splits, AP, A, h->grads + h->actor.b_off, acc, h->sm_count, s));
             OCPPO_TRY(launch_splitk_reduce(h->splitk_bias + A, g.splits, AP, 1, h->grads + h->critic.b_off, acc, h->sm_count, s));
         }
-        OCPPO_TRY(trunk_backward(h, h->x0, rows, 0, acc, s));
+        OCPPO_TRY(trunk_backward(h, h->x0, rows, 0, acc, s, g_gemm_mode == 5));
     }
     OCPPO_TRY(launch_loss_finalize(h->loss_part, used, mb, (float)hp->ent_coef, (float)hp->vf_coef, stats, s));
     return OCPPO_OK;

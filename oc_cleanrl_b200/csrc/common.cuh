@@ -208,6 +208,7 @@ struct LossArgs {
     int norm_adv, clip_vloss;
     float *dh;                  // [rows, H]  d loss / d (pre-activation of last trunk layer)
     float *gz;                  // [rows, AP] d loss / d (logits, value), zero padded
+    float *dh_amax;             // optional: atomicMax of |dh| as float bits (FP16x3 engine's operand scale); caller zeroes it
     double *part;               // [gridDim.x, 8] partial sums of the logged statistics
 };
 

@@ -290,6 +290,7 @@ __global__ void __launch_bounds__(kHeadThreads) loss_head_kernel(LossArgs p) {
     if (p.norm_adv) { mean = p.adv_stat[0]; stdv = p.adv_stat[1]; }
 
     double acc[6] = {0, 0, 0, 0, 0, 0};   // pg, vmax, entropy, -logratio, (ratio-1)-logratio, clipped
+    float dmax = 0.f;                     // max |dh| written by this lane
     const int64_t i0 = (int64_t)blockIdx.x * kWarpsPerBlock + warp, istep = (int64_t)gridDim.x * kWarpsPerBlock;
     if (HV > 0) {
         constexpr int NV = HV > 0 ? HV : 1;
@@ -342,6 +343,7 @@ __global__ void __launch_bounds__(kHeadThreads) loss_head_kernel(LossArgs p) {
                 const float4 o = make_float4(hv[g].x > 0.f ? s[g].x : 0.f, hv[g].y > 0.f ? s[g].y : 0.f,
                                              hv[g].z > 0.f ? s[g].z : 0.f, hv[g].w > 0.f ? s[g].w : 0.f);
                 *(reinterpret_cast<float4 *>(p.dh + i * H + g * 128) + lane) = o;
+                dmax = fmaxf(fmaxf(dmax, fmaxf(fabsf(o.x), fabsf(o.y))), fmaxf(fabsf(o.z), fabsf(o.w)));
             }
         }
     } else {
@@ -361,9 +363,17 @@ __global__ void __launch_bounds__(kHeadThreads) loss_head_kernel(LossArgs p) {
                     const float dzk = __shfl_sync(kFull, dz, k);
                     if (on) s = fmaf(dzk, sW[k * H + j], s);
                 }
-                if (on) p.dh[i * H + j] = h[j] > 0.f ? s : 0.f;
+                if (on) {
+                    const float o = h[j] > 0.f ? s : 0.f;
+                    p.dh[i * H + j] = o;
+                    dmax = fmaxf(dmax, fabsf(o));
+                }
             }
         }
+    }
+    if (p.dh_amax != nullptr) {
+        const unsigned m = __reduce_max_sync(kFull, __float_as_uint(dmax));
+        if (lane == 0 && m != 0u) atomicMax(reinterpret_cast<unsigned int *>(p.dh_amax), m);
     }
     __shared__ double red[kWarpsPerBlock][6];
     if (lane == 0)

@@ -139,6 +139,7 @@ __global__ void __launch_bounds__(kThreads, 2) sgemm_kernel(SgemmArgs p) {
     float *C = p.C;
     if (MODE == SGEMM_WGRAD) C += (int64_t)split * p.M * p.N;
     const bool c_vec = ((p.N & 3) == 0) && ((p.ldc & 3) == 0);
+    float run_max = 0.f;                  // max |C| of this thread's stores (p.amax_out: the consumer's FP16 scale)
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         const int m = m0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
@@ -161,6 +162,7 @@ __global__ void __launch_bounds__(kThreads, 2) sgemm_kernel(SgemmArgs p) {
                     v[2] = mk.z > 0.f ? v[2] : 0.f; v[3] = mk.w > 0.f ? v[3] : 0.f;
                 }
                 *reinterpret_cast<float4 *>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+                if (MODE != SGEMM_WGRAD) run_max = fmaxf(fmaxf(run_max, fmaxf(fabsf(v[0]), fabsf(v[1]))), fmaxf(fabsf(v[2]), fabsf(v[3])));
             } else {
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
@@ -169,9 +171,14 @@ __global__ void __launch_bounds__(kThreads, 2) sgemm_kernel(SgemmArgs p) {
                     if (MODE == SGEMM_FWD) o = fmaxf(o + p.bias[n + j], 0.f);
                     else if (MODE == SGEMM_DGRAD) o = p.mask[(int64_t)m * p.ldc + n + j] > 0.f ? o : 0.f;
                     dst[j] = o;
+                    if (MODE != SGEMM_WGRAD) run_max = fmaxf(run_max, fabsf(o));
                 }
             }
         }
+    }
+    if (MODE != SGEMM_WGRAD && p.amax_out != nullptr) {          // uniform across the grid
+        const unsigned m = __reduce_max_sync(0xffffffffu, __float_as_uint(run_max));   // non-negative floats order as uints
+        if ((tid & 31) == 0 && m != 0u) atomicMax(reinterpret_cast<unsigned int *>(p.amax_out), m);
     }
 }
 
