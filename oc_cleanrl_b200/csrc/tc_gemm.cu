@@ -49,10 +49,11 @@ constexpr int TK = 32;
 constexpr int kPairM = 2 * TM;                              // 256-row tile per CTA pair
 // 16 warps: 0-7 epilogue (two per TMEM lane quarter, each half of the tile's columns), 8 MMA issuer, 9 TMA issuer,
 // 10-11 idle, 12-15 lo-tile producers
-constexpr int kEpiWarps = 8, kProdWarps = 4;
-constexpr int kProdThreads = kProdWarps * 32;               // 128
-constexpr int kProdTid0 = 384;
-constexpr int kTcThreads = kProdTid0 + kProdThreads;        // 512
+constexpr int kEpiWarps = 8, kProdWarps = 8;
+constexpr int kProdThreads = kProdWarps * 32;               // 256
+constexpr int kProdTid0 = (kEpiWarps + 2) * 32;             // 320
+constexpr int kTcThreads = kProdTid0 + kProdThreads;        // 576: at most 112 registers per thread
+constexpr int kProdQ = 1024 / kProdThreads;                 // 16-byte chunks of a 16 KB raw tile per producer thread (4)
 constexpr int kStageBytesA = TM * TK * 4;                   // 16 KB
 constexpr int kRingBytes = 192 * 1024;                      // 3 x 64 KB or 4 x 48 KB
 constexpr int kMaxStages = 4;
@@ -67,7 +68,7 @@ constexpr int kTmemCols = 512;                              // two tiles' accumu
 constexpr float kTruncPerMma = 2.1e-8f;
 constexpr int kEpiChunkBytes = 32 * 32 * 4;                 // one warp's 32 rows x 32 columns, SWIZZLE_128B
 constexpr int kEpiPadBytes = kEpiWarps * kEpiChunkBytes;    // per warp: one chunk, incoming aux then outgoing result (32 KB)
-constexpr int kBiasRedBytes = kProdWarps * TM * 4;          // WGRAD bias partials [4 k-lanes][128] (2 KB)
+constexpr int kBiasRedBytes = 4 * TM * 4;                   // WGRAD bias partials [4][128] (2 KB): the 8 k-lanes fold in two steps
 constexpr int kTcSmemBytes = kRingBytes + kEpiPadBytes + kBiasRedBytes + 256 /*barriers*/;   // base is 1024-aligned
 static_assert(kTcSmemBytes <= 232448, "shared memory budget (227 KB per CTA)");
 
@@ -203,13 +204,13 @@ __device__ __forceinline__ float4 lo4(const float4 &v) {
 // offsets of the 4 chunks thread p owns in a 16 KB operand tile
 // K-major tile of 128 rows x 32 floats (SWIZZLE_128B): 8 threads per row, 16 rows per pass.
 __device__ __forceinline__ int off_kmajor(int p, int q) {
-    const int row = q * 16 + (p >> 3), c = p & 7;
+    const int row = q * (kProdThreads / 8) + (p >> 3), c = p & 7;
     return row * 128 + ((c ^ (row & 7)) << 4);
 }
 // MN-major tile of 32 k-rows x 128 floats (4 chunks of [32 k][32 floats], SWIZZLE_128B_BASE32B).  Thread p
 // owns the 4 columns (p % 32) * 4.. in k-rows p / 32 + 4 q (so its values sum into one float4 of column sums).
 __device__ __forceinline__ int off_mnmajor(int p, int q) {
-    const int g = p & 31, k = q * 4 + (p >> 5);
+    const int g = p & 31, k = q * kProdWarps + (p >> 5);
     const int mb = g >> 3, c = g & 7;
     return mb * 4096 + k * 128 + ((((c >> 1) ^ (k & 3)) << 5) | ((c & 1) << 4));
 }
@@ -218,25 +219,25 @@ template <bool A_MN, bool B_MN, bool SUM, int BW>
 __device__ __forceinline__ void convert_stage(const uint8_t *a_hi, uint8_t *a_lo, const uint8_t *b_hi, uint8_t *b_lo,
                                               int p, float4 &colsum) {
     static_assert(BW == 128, "B tile width");
-    int o[8];
-    float4 v[8];
+    int o[kProdQ];
+    float4 v[kProdQ];
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
+    for (int q = 0; q < kProdQ; ++q) {
         o[q] = A_MN ? off_mnmajor(p, q) : off_kmajor(p, q);
         v[q] = *reinterpret_cast<const float4 *>(a_hi + o[q]);
     }
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
+    for (int q = 0; q < kProdQ; ++q) {
         if (SUM) { colsum.x += v[q].x; colsum.y += v[q].y; colsum.z += v[q].z; colsum.w += v[q].w; }
         *reinterpret_cast<float4 *>(a_lo + o[q]) = lo4(v[q]);
     }
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
+    for (int q = 0; q < kProdQ; ++q) {
         o[q] = B_MN ? off_mnmajor(p, q) : off_kmajor(p, q);
         v[q] = *reinterpret_cast<const float4 *>(b_hi + o[q]);
     }
 #pragma unroll
-    for (int q = 0; q < 8; ++q) *reinterpret_cast<float4 *>(b_lo + o[q]) = lo4(v[q]);
+    for (int q = 0; q < kProdQ; ++q) *reinterpret_cast<float4 *>(b_lo + o[q]) = lo4(v[q]);
 }
 
 // ---- BF16 correction operands -----------------------------------------------------------------------------
@@ -255,21 +256,21 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo_elem, float hi_elem) {
 __device__ __forceinline__ float resid_tf32(float x) { return x - __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
 // byte offset of this thread's 4 consecutive elements (8 bytes) in the bf16 tile, for the raw chunk (p, q)
 __device__ __forceinline__ int off16_kmajor(int p, int q) {
-    const int row = q * 16 + (p >> 3), c = p & 7;
+    const int row = q * (kProdThreads / 8) + (p >> 3), c = p & 7;
     return row * 64 + ((((c >> 1) ^ (row >> 1)) & 3) << 4) + ((c & 1) << 3);
 }
 __device__ __forceinline__ int off16_mnmajor(int p, int q) {
-    const int g = p & 31, k = q * 4 + (p >> 5);
+    const int g = p & 31, k = q * kProdWarps + (p >> 5);
     const int e = g * 4;                                   // first MN element of the chunk, 0..124
     return (e >> 6) * 4096 + k * 128 + (((((e & 63) >> 3) ^ (k & 7))) << 4) + (((e >> 2) & 1) << 3);
 }
 template <bool MN, bool SUM>
 __device__ __forceinline__ void convert_operand_bf16(const uint8_t *raw, uint8_t *full16, uint8_t *lo16, int p, float4 &colsum) {
-    float4 v[8];
+    float4 v[kProdQ];
 #pragma unroll
-    for (int q = 0; q < 8; ++q) v[q] = *reinterpret_cast<const float4 *>(raw + (MN ? off_mnmajor(p, q) : off_kmajor(p, q)));
+    for (int q = 0; q < kProdQ; ++q) v[q] = *reinterpret_cast<const float4 *>(raw + (MN ? off_mnmajor(p, q) : off_kmajor(p, q)));
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
+    for (int q = 0; q < kProdQ; ++q) {
         if (SUM) { colsum.x += v[q].x; colsum.y += v[q].y; colsum.z += v[q].z; colsum.w += v[q].w; }
         const int o = MN ? off16_mnmajor(p, q) : off16_kmajor(p, q);
         *reinterpret_cast<uint2 *>(full16 + o) = make_uint2(pack_bf16(v[q].x, v[q].y), pack_bf16(v[q].z, v[q].w));
@@ -293,11 +294,11 @@ __host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N, bool a_mn_ma
 template <bool MN, bool SUM>
 __device__ __forceinline__ void convert_operand_f16(const uint8_t *raw, uint8_t *hi16, uint8_t *lo16, int p, float scale,
                                                     float4 &colsum) {
-    float4 v[8];
+    float4 v[kProdQ];
 #pragma unroll
-    for (int q = 0; q < 8; ++q) v[q] = *reinterpret_cast<const float4 *>(raw + (MN ? off_mnmajor(p, q) : off_kmajor(p, q)));
+    for (int q = 0; q < kProdQ; ++q) v[q] = *reinterpret_cast<const float4 *>(raw + (MN ? off_mnmajor(p, q) : off_kmajor(p, q)));
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
+    for (int q = 0; q < kProdQ; ++q) {
         if (SUM) { colsum.x += v[q].x; colsum.y += v[q].y; colsum.z += v[q].z; colsum.w += v[q].w; }
         const int o = MN ? off16_mnmajor(p, q) : off16_kmajor(p, q);
         uint32_t h0, l0, h1, l1;
@@ -395,9 +396,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
     // stage layout.  3xTF32: [A raw = hi 16K][A lo 16K][B raw = hi 16K][B lo 16K];
     // CORR16:  [A raw 16K][B raw 16K][A bf16 8K][A lo bf16 8K][B bf16 8K][B lo bf16 8K]
     constexpr int kOffA = 0, kOffB = CORR16 ? kStageBytesA : 2 * kStageBytesA;
-    constexpr int kOffALo = CORR16 ? 2 * kStageBytesA + kStageBytesA / 2 : kStageBytesA;
-    constexpr int kOffBLo = CORR16 ? 3 * kStageBytesA + kStageBytesB / 2 : 2 * kStageBytesA + kStageBytesB;
-    constexpr int kOffA16 = 2 * kStageBytesA, kOffB16 = 3 * kStageBytesA;     // CORR16 only
+    constexpr int kOffALo_ = CORR16 ? 2 * kStageBytesA + kStageBytesA / 2 : kStageBytesA;
+    constexpr int kOffBLo_ = CORR16 ? 3 * kStageBytesA + kStageBytesB / 2 : 2 * kStageBytesA + kStageBytesB;
+    constexpr int kOffA16_ = 2 * kStageBytesA, kOffB16_ = 3 * kStageBytesA;     // CORR16 only
+    // FP16 x 3 with the weights pre-split in global memory (FWD / DGRAD of the learner): nothing ever lands in the raw-B
+    // slot, so the stage shrinks to [A raw 16K][A hi 8K][A lo 8K][B hi 8K][B lo 8K] = 48 KB and the ring holds FOUR stages
+    const bool compact = F16 && MODE != SGEMM_WGRAD && p.b16_hi != nullptr && !(p.dbg & 64);
+    const int stage_bytes = compact ? 48 * 1024 : kStageBytes, nstages = compact ? 4 : kNumStages;
+    const int kOffA16 = compact ? kStageBytesA : kOffA16_, kOffALo = compact ? kStageBytesA + kStageBytesA / 2 : kOffALo_;
+    const int kOffB16 = compact ? 2 * kStageBytesA : kOffB16_, kOffBLo = compact ? 2 * kStageBytesA + kStageBytesB / 2 : kOffBLo_;
 
     static_assert(kNumStages * kStageBytes <= kRingBytes && kNumStages <= kMaxStages, "stage ring");
     // The TMEM accumulator adds with truncation (measured: error grows linearly with the number of MMAs
@@ -434,11 +441,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
     constexpr bool split_acc = SPLIT;
 
     if (tid == 0) {
-        for (int s = 0; s < kNumStages; ++s) {
+        for (int s = 0; s < kMaxStages; ++s) {
             mbar_init(bar_full + 8 * s, 2 * kProdWarps);     // both CTAs' producer warps
             mbar_init(bar_empty + 8 * s, 1);
             mbar_init(bar_tma + 8 * s, 1);
-            mbar_init(bar_rawfull + 8 * s, F16 ? kProdWarps : 2);   // one forwarder per CTA | F16: raw tile consumed (own producers)
+            mbar_init(bar_rawfull + 8 * s, F16 ? kProdWarps : 1);   // the peer's forwarder | F16: raw tile consumed (own producers)
         }
         for (int w = 0; w < kEpiWarps; ++w) mbar_init(bar_aux + 8 * w, 1);
         for (int a = 0; a < 2; ++a) {
@@ -524,16 +531,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                 OCPPO_TMEM_LD32(v, taddr);
                 uint32_t w[32];
                 if (split_acc) OCPPO_TMEM_LD32(w, taddr + TN);      // main in columns [0,TN), corrections in [TN,2TN)
-                float4 ax[8];
-                if (aux) {
-                    mbar_wait(my_aux_bar, aux_phase);
-                    aux_phase ^= 1;
-#pragma unroll
-                    for (int c = 0; c < 8; ++c)
-                        ax[c] = *reinterpret_cast<const float4 *>(out_tile + lane * 128 + ((c ^ swz) << 4));
-                } else if (lane == 0) {
-                    bulk_wait_read0();         // the previous chunk's store has read the tile
-                }
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                 if (cc == kChunks - 1) {       // accumulator drained: hand it back to the MMA warp
                     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -548,6 +545,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                     if (F16) x = ((x + __uint_as_float(w[j])) * inv_a) * inv_b;
                     else if (split_acc) x += __uint_as_float(w[j]);
                     v[j] = __float_as_uint(x);
+                }
+                // (the aux tile is read only now, when the correction registers are dead: 96 registers per thread)
+                float4 ax[8];
+                if (aux) {
+                    mbar_wait(my_aux_bar, aux_phase);
+                    aux_phase ^= 1;
+#pragma unroll
+                    for (int c = 0; c < 8; ++c)
+                        ax[c] = *reinterpret_cast<const float4 *>(out_tile + lane * 128 + ((c ^ swz) << 4));
+                } else if (lane == 0) {
+                    bulk_wait_read0();         // the previous chunk's store has read the tile
                 }
                 __syncwarp();
                 const int n = n_loc + cc * 32;
@@ -602,8 +610,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
             const uint32_t m = __reduce_max_sync(0xffffffffu, __float_as_uint(run_max));   // non-negative floats order as uints
             if (lane == 0) atomicMax(reinterpret_cast<unsigned int *>(p.amax_out), m);
         }
-    } else if (warp < kEpiWarps + 4) {
-        // ===================== MMA issuer (warp 8; warps 10-11 idle) =====================
+    } else if (warp < kEpiWarps + 2) {
+        // ===================== MMA issuer (warp 8 of the leader; the peer's warp 8 forwards) =====================
         if (warp == kEpiWarps && lane == 0 && cta_rank == 0) {
             constexpr uint32_t idesc = make_idesc(kPairM, TN, A_MN, B_MN);   // M = 256 across the pair
             // K-major: SBO = 8-row group stride (1024 B), LBO unused.  MN-major: LBO = stride between
@@ -625,10 +633,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                     // The main product reads only the raw tiles: it starts as soon as both CTAs' TMA loads have landed
                     // and runs while the producers are still deriving the correction operands of the same stage.
                     const int s = stage, fphase = sphase;
-                    if (!F16) mbar_wait(bar_rawfull + 8 * s, (uint32_t)fphase);
-                    if (++stage == kNumStages) { stage = 0; sphase ^= 1; }
+                    if (!F16) {
+                        mbar_wait(bar_tma + 8 * s, (uint32_t)fphase);        // own raw tiles
+                        mbar_wait(bar_rawfull + 8 * s, (uint32_t)fphase);    // the peer's
+                    }
+                    if (++stage == nstages) { stage = 0; sphase ^= 1; }
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    uint8_t *st = smem + s * kStageBytes;
+                    uint8_t *st = smem + s * stage_bytes;
                     const uint32_t a_hi = smem_u32(st) + kOffA, a_lo = smem_u32(st) + kOffALo;
                     const uint32_t b_hi = smem_u32(st) + kOffB, b_lo = smem_u32(st) + kOffBLo;
                     const uint64_t da_hi = make_desc(a_hi, a_lbo, a_sbo, a_ty), db_hi = make_desc(b_hi, b_lbo, b_sbo, b_ty);
@@ -705,7 +716,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                     // F16: nothing but the producers reads the raw tiles, so they are refilled as soon as the conversion
                     // has consumed them -- one MMA stage earlier than the converted tiles come free
                     mbar_wait((F16 ? bar_rawfull : bar_empty) + 8 * s, (uint32_t)(sphase ^ 1));
-                    const uint32_t a_hi = smem_u32(smem + s * kStageBytes) + kOffA, b_hi = smem_u32(smem + s * kStageBytes) + kOffB;
+                    const uint32_t a_hi = smem_u32(smem + s * stage_bytes) + kOffA, b_hi = smem_u32(smem + s * stage_bytes) + kOffB;
                     const uint32_t bar = bar_tma + 8 * s;
                     const int k0 = (int)(t.kbeg + (int64_t)kb * TK);
                     mbar_expect_tx(bar, kStageBytesA + kStageBytesB);
@@ -714,7 +725,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                     if (F16 && MODE != SGEMM_WGRAD && p.b16_hi != nullptr) {
                         // B (the layer's weights) was split into fp16 hi / lo tensors once per call: its tiles arrive in
                         // the MMA's layout (tmB = hi, tmB2 = lo) and wait for the MMAs of the stage's previous use
-                        const uint32_t b16h = smem_u32(smem + s * kStageBytes) + kOffB16, b16l = smem_u32(smem + s * kStageBytes) + kOffBLo;
+                        const uint32_t b16h = smem_u32(smem + s * stage_bytes) + kOffB16, b16l = smem_u32(smem + s * stage_bytes) + kOffBLo;
                         mbar_wait(bar_empty + 8 * s, (uint32_t)(sphase ^ 1));
                         if (B_MN) {
                             tma_load_3d(b16h, &tmB, 0, k0, (t.n0 + rank_n) >> 6, bar);
@@ -725,20 +736,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                         }
                     } else if (B_MN) tma_load_3d(b_hi, &tmB, 0, k0, (t.n0 + rank_n) >> 5, bar);
                     else tma_load_2d(b_hi, &tmB, k0, t.n0 + rank_n, bar);
-                    if (++stage == kNumStages) { stage = 0; sphase ^= 1; }
+                    if (++stage == nstages) { stage = 0; sphase ^= 1; }
                 }
             }
         }
-        else if (!F16 && warp == kEpiWarps + 2 && lane == 0) {
-            // ===================== raw-tile forwarder (warp 10, both CTAs) =====================
-            // tells the leader's MMA issuer that this CTA's raw tiles of a stage have landed
+        else if (!F16 && warp == kEpiWarps && lane == 0 && cta_rank == 1) {
+            // ===================== raw-tile forwarder (warp 8 of the peer CTA) =====================
+            // tells the leader's MMA issuer that this CTA's raw tiles of a stage have landed (the leader polls its own)
             int stage = 0, sphase = 0;
             for (int tile = cl; tile < ntiles; tile += ncl) {
                 const TileCoord t = tile_coord(p, tile, nt_n, nt_m, TN);
                 for (int kb = 0; kb < t.nk; ++kb) {
                     mbar_wait(bar_tma + 8 * stage, (uint32_t)sphase);
                     mbar_arrive_on(bar_rawfull + 8 * stage, 0);
-                    if (++stage == kNumStages) { stage = 0; sphase ^= 1; }
+                    if (++stage == nstages) { stage = 0; sphase ^= 1; }
                 }
             }
         }
@@ -756,7 +767,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
             for (int kb = 0; kb < t.nk; ++kb) {
                 const int s = stage;
                 mbar_wait(bar_tma + 8 * s, (uint32_t)sphase);           // raw tile landed (TMA complete_tx)
-                uint8_t *st = smem + s * kStageBytes;
+                uint8_t *st = smem + s * stage_bytes;
                 uint8_t *a_hi = st + kOffA, *a_lo = st + kOffALo, *b_hi = st + kOffB, *b_lo = st + kOffBLo;
                 if (F16) {
                     mbar_wait(bar_empty + 8 * s, (uint32_t)(sphase ^ 1));    // the MMAs of the previous use have read the fp16 tiles
@@ -776,17 +787,24 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                     mbar_arrive_on(bar_full + 8 * s, 0);      // the leader CTA's barrier
                     if (F16) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_rawfull + 8 * s) : "memory");
                 }
-                if (++stage == kNumStages) { stage = 0; sphase ^= 1; }
+                if (++stage == nstages) { stage = 0; sphase ^= 1; }
             }
             if (MODE == SGEMM_WGRAD) {
                 if (do_bias) {           // tile-uniform across the producer warps
-                    // [4 k-lanes][128 columns]; thread pt holds columns (pt % 32) * 4.. of k-lane pt / 32
-                    *reinterpret_cast<float4 *>(bias_red + (pt >> 5) * TM + (pt & 31) * 4) = bsum;
+                    // thread pt holds columns (pt % 32) * 4.. of k-lane pt / 32: lanes 4-7 park theirs in [4][128 columns],
+                    // lanes 0-3 add their own on top, then 128 threads sum the four rows
+                    float4 *slot = reinterpret_cast<float4 *>(bias_red + ((pt >> 5) & 3) * TM + (pt & 31) * 4);
+                    if (pt >= 128) *slot = bsum;
+                    asm volatile("bar.sync 1, %0;" ::"n"(kProdThreads) : "memory");
+                    if (pt < 128) {
+                        const float4 o = *slot;
+                        *slot = make_float4(bsum.x + o.x, bsum.y + o.y, bsum.z + o.z, bsum.w + o.w);
+                    }
                     asm volatile("bar.sync 1, %0;" ::"n"(kProdThreads) : "memory");
                     if (pt < TM) {
                         float sum = 0.f;
 #pragma unroll
-                        for (int kr = 0; kr < kProdWarps; ++kr) sum += bias_red[kr * TM + pt];
+                        for (int kr = 0; kr < 4; ++kr) sum += bias_red[kr * TM + pt];
                         if (t.m0 + rank_m + pt < p.M) p.bias_part[(int64_t)t.split * p.M + t.m0 + rank_m + pt] = sum;
                     }
                     asm volatile("bar.sync 1, %0;" ::"n"(kProdThreads) : "memory");
