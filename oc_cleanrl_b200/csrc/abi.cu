@@ -109,16 +109,22 @@ static int64_t carve(ocppo_handle *h, void *base, int64_t R, int training, bool 
     ocppo_handle tmp = *h;
     ocppo_handle *t = assign ? h : &tmp;
     const ocppo_config &c = h->cfg;
-    int64_t max_act = 0, max_w = 0, max_out = 0;
+    int64_t max_act = 0, max_w = 0, max_out = 0, max_dim = 0;
     for (int l = 0; l < h->n_layers; ++l) {
         const Layer &L = h->layers[l];
         const int64_t n = R * L.row_mult * L.out_dim;
         t->act[l] = cv.take<float>(n);
+        const bool pair = l + 1 < h->n_layers && n % 8 == 0;      // every activation a trunk GEMM may consume
+        t->act16_hi[l] = pair ? cv.take<uint16_t>(n) : nullptr;
+        t->act16_lo[l] = pair ? cv.take<uint16_t>(n) : nullptr;
+        t->act16_valid[l] = 0; t->act32_valid[l] = 0; t->act_scale[l] = nullptr;
         t->relu_bits[l] = (training && L.out_dim % 32 == 0) ? cv.take<uint32_t>(n / 32) : nullptr;
         t->relu_bits_valid[l] = 0;
         if (n > max_act) max_act = n;
         if ((int64_t)L.out_dim * L.in_dim > max_w) max_w = (int64_t)L.out_dim * L.in_dim;
         if (L.out_dim > max_out) max_out = L.out_dim;
+        if (L.in_dim > max_dim) max_dim = L.in_dim;
+        if (L.out_dim > max_dim) max_dim = L.out_dim;
     }
     t->amax = cv.take<float>(kAmaxSlots);
     t->w_amax_valid = 0;
@@ -131,6 +137,11 @@ static int64_t carve(ocppo_handle *h, void *base, int64_t R, int training, bool 
         t->x0 = cv.take<float>(R * c.frames * c.obs_dim);
         t->gbuf[0] = cv.take<float>(max_act);
         t->gbuf[1] = cv.take<float>(max_act);
+        for (int i = 0; i < 2; ++i) {
+            t->g16_hi[i] = cv.take<uint16_t>(max_act);
+            t->g16_lo[i] = cv.take<uint16_t>(max_act);
+        }
+        t->colsum_part = cv.take<float>((int64_t)kColsumBlocksMax * max_dim);
         t->gz = cv.take<float>(R * AP);
         t->mb_action = cv.take<int32_t>(R);
         t->mb_logp = cv.take<float>(R);
@@ -177,9 +188,43 @@ static int ensure_act_amax(ocppo_handle *h, int l, int64_t B, cudaStream_t s) {
     return OCPPO_OK;
 }
 
+// fp16-pair storage (engine 6): whichever representation of act[l] the last forward did not leave is made on demand
+static int ensure_act_fp32(ocppo_handle *h, int l, int64_t B, cudaStream_t s) {
+    if (h->act32_valid[l]) return OCPPO_OK;
+    const Layer &L = h->layers[l];
+    OCPPO_CHECK_ARG(h->act16_valid[l], "activation %d exists in neither representation", l);
+    OCPPO_TRY(launch_merge16(h->act16_hi[l], h->act16_lo[l], B * L.row_mult * L.out_dim, h->act_scale[l], h->act[l], h->sm_count, s));
+    h->act32_valid[l] = 1;
+    return OCPPO_OK;
+}
+static int ensure_act16(ocppo_handle *h, int l, int64_t B, cudaStream_t s) {
+    if (h->act16_valid[l]) return OCPPO_OK;
+    const Layer &L = h->layers[l];
+    OCPPO_CHECK_ARG(h->act32_valid[l] && h->act16_hi[l] != nullptr, "activation %d cannot be split", l);
+    OCPPO_TRY(ensure_act_amax(h, l, B, s));
+    h->act_scale[l] = h->amax + kAmaxAct + l;                      // the true maximum
+    OCPPO_TRY(launch_split16(h->act[l], B * L.row_mult * L.out_dim, h->act_scale[l], h->act16_hi[l], h->act16_lo[l], h->sm_count, s));
+    h->act16_valid[l] = 1;
+    return OCPPO_OK;
+}
+static bool pair_ok(const ocppo_handle *h, int l, int64_t B) {      // act[l] can live as a pair
+    const Layer &L = h->layers[l];
+    return h->act16_hi[l] != nullptr && (B * L.row_mult * L.out_dim) % 4 == 0 && L.out_dim % 8 == 0;
+}
+
+static void fwd_args(const ocppo_handle *h, int l, int64_t B, const float *in, SgemmArgs *a) {
+    const Layer &L = h->layers[l];
+    a->A = in; a->lda = L.in_dim;
+    a->B = h->params + L.w_off; a->ldb = L.in_dim;
+    a->C = h->act[l]; a->ldc = L.out_dim;
+    a->bias = h->params + L.b_off;
+    a->M = (int)(B * L.row_mult); a->N = L.out_dim; a->K = L.in_dim;
+    a->k_per_split = round_up(L.in_dim, 8); a->splits = 1;
+}
+
 static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_t s) {
     const float *in = x;
-    const bool f16 = g_gemm_mode == 5;
+    const bool f16 = g_gemm_mode >= 5, pre16 = g_gemm_mode >= 6;
     if (f16) {
         // operand scales of the FP16x3 engine: activations are tracked by the epilogue that writes them (slots zeroed
         // here), the weights are measured now -- the arena is the caller's to modify between calls
@@ -193,37 +238,70 @@ static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_
         OCPPO_TRY(launch_absmax_multi(segs, s));
         OCPPO_TRY(launch_split_f16_multi(segs, h->params, h->w16_hi, h->w16_lo, s));
         h->w_amax_valid = 1;
+        if (pre16) {        // the weight norms the epilogues bound their fp16-pair outputs with
+            OCPPO_CUDA(cudaMemsetAsync(h->amax + kWRowL1, 0, (kAmaxSlots - kWRowL1) * sizeof(float), s));
+            WnormSegs w{};
+            for (int l = 0; l < h->n_layers; ++l) {
+                const Layer &L = h->layers[l];
+                w.w[l] = h->params + L.w_off; w.b[l] = h->params + L.b_off; w.out_dim[l] = L.out_dim; w.in_dim[l] = L.in_dim;
+                w.row_l1[l] = h->amax + kWRowL1 + l; w.col_l1[l] = h->amax + kWColL1 + l; w.b_max[l] = h->amax + kBMax + l;
+            }
+            w.count = h->n_layers;
+            OCPPO_TRY(launch_wnorm(w, s));
+        }
     } else {
         h->w_amax_valid = 0;
     }
     for (int l = 0; l < h->n_layers; ++l) {
         const Layer &L = h->layers[l];
         h->act_amax_valid[l] = 0;
+        h->act16_valid[l] = 0; h->act32_valid[l] = 0;
         SgemmArgs a{};
-        a.A = in; a.lda = L.in_dim;
-        a.B = h->params + L.w_off; a.ldb = L.in_dim;
-        a.C = h->act[l]; a.ldc = L.out_dim;
-        a.bias = h->params + L.b_off;
-        a.M = (int)(B * L.row_mult); a.N = L.out_dim; a.K = L.in_dim;
-        a.k_per_split = round_up(L.in_dim, 8); a.splits = 1;
+        fwd_args(h, l, B, in, &a);
         a.relu_bits = h->training ? h->relu_bits[l] : nullptr;
         const bool tc = sgemm_uses_tc(SGEMM_FWD, a);
         h->relu_bits_valid[l] = a.relu_bits != nullptr && tc;
+        const bool w16 = L.w_off % 8 == 0 && L.in_dim % 8 == 0;
+        bool pair_out = false;
         if (f16) {
             a.amax_scratch = h->amax;
-            if (tc && l > 0) {
-                OCPPO_TRY(ensure_act_amax(h, l - 1, B, s));
-                a.amax_a = h->amax + kAmaxAct + l - 1;
-            }
             a.amax_b = h->amax + kAmaxW + l;
-            if (L.w_off % 8 == 0 && L.in_dim % 8 == 0) {
+            if (w16) {
                 a.b16_hi = reinterpret_cast<const uint16_t *>(h->w16_hi) + L.w_off;
                 a.b16_lo = reinterpret_cast<const uint16_t *>(h->w16_lo) + L.w_off;
             }
             a.amax_out = h->amax + kAmaxAct + l;          // both kernels track it
+            if (pre16 && tc && l > 0 && w16 && pair_ok(h, l - 1, B)) {
+                // the input arrives as an fp16 pair (written by the layer below, or split here once when an FMA layer made it)
+                OCPPO_TRY(ensure_act16(h, l - 1, B, s));
+                a.a16_hi = h->act16_hi[l - 1]; a.a16_lo = h->act16_lo[l - 1];
+                a.amax_a = h->act_scale[l - 1];
+                bool next_tc = false;
+                if (l + 1 < h->n_layers && pair_ok(h, l, B)) {
+                    SgemmArgs n{};
+                    fwd_args(h, l + 1, B, h->act[l], &n);
+                    next_tc = sgemm_uses_tc(SGEMM_FWD, n);
+                }
+                if (next_tc) {                            // ... and so does the output: no fp32 copy of it is ever written
+                    OCPPO_TRY(ensure_act_amax(h, l - 1, B, s));
+                    a.c16_hi = h->act16_hi[l]; a.c16_lo = h->act16_lo[l];
+                    a.bnd_amax = h->amax + kAmaxAct + l - 1;
+                    a.bnd_wl1 = h->amax + kWRowL1 + l; a.bnd_bmax = h->amax + kBMax + l;
+                    a.c_scale_src = h->amax + kBndAct + l;
+                    pair_out = true;
+                }
+            } else {
+                if (l > 0) OCPPO_TRY(ensure_act_fp32(h, l - 1, B, s));
+                if (tc && l > 0) {
+                    OCPPO_TRY(ensure_act_amax(h, l - 1, B, s));
+                    a.amax_a = h->amax + kAmaxAct + l - 1;
+                }
+            }
         }
         OCPPO_TRY(sgemm_launch(SGEMM_FWD, a, s));
         if (f16) h->act_amax_valid[l] = 1;
+        if (pair_out) { h->act16_valid[l] = 1; h->act_scale[l] = h->amax + kBndAct + l; }
+        else h->act32_valid[l] = 1;
         in = h->act[l];
     }
     h->last_forward_rows = (int)B;
@@ -231,7 +309,7 @@ static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_
 }
 
 static void pick_split(const ocppo_handle *h, int M, int N, int64_t K, int *splits, int64_t *k_per) {
-    const int tn = tc_tile_n(g_gemm_mode == 2 || g_gemm_mode == 4);
+    const int tn = tc_tile_n(g_gemm_mode == 2 || g_gemm_mode == 4 || g_gemm_mode == 8);
     const bool tc = g_gemm_mode >= 1 && M % 128 == 0 && N % tn == 0;
     int64_t S;
     const int64_t s_cap0 = K / 256 > 1 ? K / 256 : 1;
@@ -288,10 +366,19 @@ static int wgrad(ocppo_handle *h, const float *dY, int out, const float *X, int 
     return OCPPO_OK;
 }
 
+// fp16-pair WGRAD (engine 6): dY and X both as pairs -> the conversion-free kernel; the bias gradient is a column-sum pass
+static void wgrad_args(const ocppo_handle *h, const float *dY, int out, const float *X, int in, int64_t rows, SgemmArgs *a) {
+    a->A = dY; a->lda = out;
+    a->B = X; a->ldb = in;
+    a->C = h->splitk; a->ldc = in;
+    a->M = out; a->N = in; a->K = rows;
+    pick_split(h, out, in, rows, &a->splits, &a->k_per_split);
+}
+
 // g0 holds d loss / d pre-activation of the last trunk layer, [B, hidden].
 static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, int accumulate, cudaStream_t s,
                           bool top_amax_tracked = false) {
-    const bool f16 = g_gemm_mode == 5;
+    const bool f16 = g_gemm_mode >= 5, pre16 = g_gemm_mode >= 6;
     bool dy_amax_valid = f16 && top_amax_tracked;   // the caller zeroed the gradient slots and the loss head filled the top one
     if (f16 && !top_amax_tracked) {
         // max |dY| of the top layer comes from one reduction pass; the dgrad epilogues track the layers below
@@ -301,44 +388,126 @@ static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, i
                                 h->sm_count, s));
         dy_amax_valid = true;
     }
+    // which representations of the gradient entering layer l exist: fp32 in gbuf[cur], fp16 pair in g16[cur]
+    bool dy32 = true, dy16 = false;
+    bool db_done = false;                 // the dgrad above already reduced this layer's bias gradient (fused column sums)
+    const float *dy_scale = nullptr;
     for (int l = h->n_layers - 1; l >= 0; --l) {
         const Layer &L = h->layers[l];
         const int64_t rows = B * L.row_mult;
         const float *X = (l == 0) ? x : h->act[l - 1];
         const float *dY = h->gbuf[cur];
         const float *amax_dy = (f16 && dy_amax_valid) ? h->amax + kAmaxGrad + l : nullptr;
-        const float *amax_x = nullptr;
-        if (f16 && l > 0 && L.in_dim > 32) {
-            OCPPO_TRY(ensure_act_amax(h, l - 1, B, s));
-            amax_x = h->amax + kAmaxAct + l - 1;
+        const bool w16 = L.w_off % 8 == 0 && L.in_dim % 8 == 0;
+        const bool dy_pair_ok = pre16 && dy_amax_valid && (rows * L.out_dim) % 4 == 0 && L.out_dim % 8 == 0;
+
+        // ---- plan: which of this layer's two GEMMs take fp16 pairs
+        bool pre_w = false, pre_d = false;
+        SgemmArgs wa{}, da{};
+        if (l > 0 && L.in_dim > 32) {
+            wgrad_args(h, dY, L.out_dim, X, L.in_dim, rows, &wa);
+            pre_w = dy_pair_ok && sgemm_uses_tc(SGEMM_WGRAD, wa) && L.out_dim % 64 == 0 && pair_ok(h, l - 1, B);
         }
-        OCPPO_TRY(wgrad(h, dY, L.out_dim, X, L.in_dim, rows, h->grads + L.w_off, (int64_t)L.out_dim * L.in_dim,
-                        h->grads + L.b_off, L.out_dim, accumulate, s, amax_dy, amax_x));
         if (l > 0) {
-            SgemmArgs a{};
-            a.A = dY; a.lda = L.out_dim;
-            a.B = h->params + L.w_off; a.ldb = L.in_dim;
-            a.C = h->gbuf[cur ^ 1]; a.ldc = L.in_dim;
-            a.mask = h->act[l - 1];
-            a.M = (int)rows; a.N = L.in_dim; a.K = L.out_dim;
-            a.k_per_split = round_up(L.out_dim, 8); a.splits = 1;
+            da.A = dY; da.lda = L.out_dim;
+            da.B = h->params + L.w_off; da.ldb = L.in_dim;
+            da.C = h->gbuf[cur ^ 1]; da.ldc = L.in_dim;
+            da.mask = h->act[l - 1];
+            da.M = (int)rows; da.N = L.in_dim; da.K = L.out_dim;
+            da.k_per_split = round_up(L.out_dim, 8); da.splits = 1;
             // the layer below left its ReLU decisions as one bit per element (same row-major element order, so the
             // encoder -> decoder flatten does not matter): the tensor-core dgrad reads those instead of the activations
-            if (h->relu_bits_valid[l - 1] && L.in_dim % 256 == 0) a.relu_bits = h->relu_bits[l - 1];
+            if (h->relu_bits_valid[l - 1] && L.in_dim % 256 == 0) da.relu_bits = h->relu_bits[l - 1];
+            pre_d = dy_pair_ok && w16 && h->w_amax_valid && sgemm_uses_tc(SGEMM_DGRAD, da);
+        }
+        OCPPO_CHECK_ARG(!db_done || pre_w, "layer %d: bias gradient formed twice", l);
+        if ((pre_w || pre_d) && !dy16) {        // the loss head's (or an FMA layer's) fp32 gradient, split once for both GEMMs
+            dy_scale = amax_dy;
+            OCPPO_TRY(launch_split16(dY, rows * L.out_dim, dy_scale, h->g16_hi[cur], h->g16_lo[cur], h->sm_count, s));
+            dy16 = true;
+        }
+        if ((!pre_w || (l > 0 && !pre_d)) && !dy32) {
+            OCPPO_TRY(launch_merge16(h->g16_hi[cur], h->g16_lo[cur], rows * L.out_dim, dy_scale, h->gbuf[cur], h->sm_count, s));
+            dy32 = true;
+        }
+
+        // ---- weight and bias gradients
+        if (pre_w) {
+            OCPPO_TRY(ensure_act16(h, l - 1, B, s));
+            wa.a16_hi = h->g16_hi[cur]; wa.a16_lo = h->g16_lo[cur]; wa.amax_a = dy_scale;
+            wa.b16_hi = h->act16_hi[l - 1]; wa.b16_lo = h->act16_lo[l - 1]; wa.amax_b = h->act_scale[l - 1];
+            wa.amax_scratch = h->amax;
+            OCPPO_TRY(sgemm_launch(SGEMM_WGRAD, wa, s));
+            OCPPO_TRY(launch_splitk_reduce(h->splitk, wa.splits, (int64_t)L.out_dim * L.in_dim, (int64_t)L.out_dim * L.in_dim,
+                                           h->grads + L.w_off, accumulate, h->sm_count, s));
+            if (!db_done) {
+                int blocks = 0;
+                OCPPO_TRY(launch_colsum16(h->g16_hi[cur], h->g16_lo[cur], rows, L.out_dim, dy_scale, h->colsum_part, &blocks, h->sm_count, s));
+                OCPPO_TRY(launch_colsum_reduce(h->colsum_part, blocks, L.out_dim, h->grads + L.b_off, accumulate, s));
+            }
+            db_done = false;
+        } else {
+            const float *amax_x = nullptr;
+            if (l > 0) OCPPO_TRY(ensure_act_fp32(h, l - 1, B, s));
+            if (f16 && l > 0 && L.in_dim > 32) {
+                OCPPO_TRY(ensure_act_amax(h, l - 1, B, s));
+                amax_x = h->amax + kAmaxAct + l - 1;
+            }
+            OCPPO_TRY(wgrad(h, dY, L.out_dim, X, L.in_dim, rows, h->grads + L.w_off, (int64_t)L.out_dim * L.in_dim,
+                            h->grads + L.b_off, L.out_dim, accumulate, s, amax_dy, amax_x));
+        }
+
+        // ---- gradient of the layer's input
+        if (l > 0) {
+            SgemmArgs &a = da;
+            bool pair_out = false;
+            if (da.relu_bits == nullptr) OCPPO_TRY(ensure_act_fp32(h, l - 1, B, s));      // fp32 mask
             if (f16) {
                 a.amax_scratch = h->amax;
                 a.amax_a = amax_dy;
                 if (h->w_amax_valid) {
                     a.amax_b = h->amax + kAmaxW + l;
-                    if (L.w_off % 8 == 0 && L.in_dim % 8 == 0) {
+                    if (w16) {
                         a.b16_hi = reinterpret_cast<const uint16_t *>(h->w16_hi) + L.w_off;
                         a.b16_lo = reinterpret_cast<const uint16_t *>(h->w16_lo) + L.w_off;
                     }
                 }
                 dy_amax_valid = sgemm_uses_tc(SGEMM_DGRAD, a);
                 if (dy_amax_valid) a.amax_out = h->amax + kAmaxGrad + l - 1;
+                if (pre_d) {
+                    a.a16_hi = h->g16_hi[cur]; a.a16_lo = h->g16_lo[cur]; a.amax_a = dy_scale;
+                    // the gradient leaves as a pair when both GEMMs of the layer below will take it that way
+                    const Layer &Ln = h->layers[l - 1];
+                    bool next_pair = l - 1 >= 1 && Ln.in_dim > 32 && Ln.out_dim % 64 == 0 && (rows * L.in_dim) % 4 == 0 && pair_ok(h, l - 2, B);
+                    if (next_pair) {
+                        SgemmArgs nw{};
+                        wgrad_args(h, h->gbuf[cur ^ 1], Ln.out_dim, h->act[l - 2], Ln.in_dim, B * Ln.row_mult, &nw);
+                        next_pair = sgemm_uses_tc(SGEMM_WGRAD, nw);
+                    }
+                    if (next_pair) {
+                        a.c16_hi = h->g16_hi[cur ^ 1]; a.c16_lo = h->g16_lo[cur ^ 1];
+                        a.bnd_amax = h->amax + kAmaxGrad + l; a.bnd_wl1 = h->amax + kWColL1 + l; a.bnd_bmax = nullptr;
+                        a.c_scale_src = h->amax + kBndGrad + l - 1;
+                        pair_out = true;
+                        // ... and its column sums (the bias gradient of the layer below) come out of the same epilogue
+                        const int parts = tc_gemm_ctas(SGEMM_DGRAD, a, h->sm_count) * 4;
+                        if (parts <= kColsumBlocksMax && L.in_dim % Ln.out_dim == 0) {
+                            a.colsum_part = h->colsum_part;
+                            OCPPO_CUDA(cudaMemsetAsync(h->colsum_part, 0, (size_t)parts * L.in_dim * sizeof(float), s));
+                        }
+                    }
+                }
             }
             OCPPO_TRY(sgemm_launch(SGEMM_DGRAD, a, s));
+            if (a.colsum_part != nullptr) {
+                // [parts, in] partial rows read as [parts * in / out', out']: the flatten's frame groups fold with the rest
+                const Layer &Ln = h->layers[l - 1];
+                const int parts = tc_gemm_ctas(SGEMM_DGRAD, a, h->sm_count) * 4 * (L.in_dim / Ln.out_dim);
+                OCPPO_TRY(launch_colsum_reduce(h->colsum_part, parts, Ln.out_dim, h->grads + Ln.b_off, accumulate, s));
+                db_done = true;
+            }
+            if (pair_out) { dy16 = true; dy32 = false; dy_scale = h->amax + kBndGrad + l - 1; }
+            else { dy16 = false; dy32 = true; }
             cur ^= 1;
         }
     }
@@ -361,7 +530,7 @@ int64_t ocppo_launch_count(void) {
 }
 
 int ocppo_set_gemm_mode(int32_t mode) {
-    OCPPO_CHECK_ARG(mode >= 0 && mode <= 5, "gemm mode must be 0 (fp32 FMA), 1 / 2 (tcgen05 3xTF32, split / single accumulator), 3 / 4 (TF32 + BF16 corrections, split / single) or 5 (FP16 x 3)");
+    OCPPO_CHECK_ARG((mode >= 0 && mode <= 6) || mode == 8, "gemm mode must be 0 (fp32 FMA), 1 / 2 (tcgen05 3xTF32, split / single accumulator), 3 / 4 (TF32 + BF16 corrections, split / single), 5 (FP16 x 3, fp32 storage) or 6 (FP16 x 3, fp16-pair storage)");
     g_gemm_mode = mode;
     return OCPPO_OK;
 }
@@ -370,23 +539,64 @@ int ocppo_get_gemm_mode(void) { return g_gemm_mode; }
 int ocppo_gemm(int32_t op, int32_t engine, int32_t M, int32_t N, int64_t K, const float *A, int64_t lda,
                const float *B, int64_t ldb, float *C, int64_t ldc, const float *bias, const float *mask,
                float *bias_part, int32_t splits, int64_t k_per_split, void *stream) {
-    OCPPO_CHECK_ARG(op >= 0 && op <= 2 && engine >= 0 && engine <= 5, "bad op/engine");
+    OCPPO_CHECK_ARG(op >= 0 && op <= 2 && engine >= 0 && engine <= 8, "bad op/engine");
     OCPPO_CHECK_ARG(A && B && C, "null pointer");
     SgemmArgs a{};
     a.A = A; a.lda = lda; a.B = B; a.ldb = ldb; a.C = C; a.ldc = ldc; a.bias = bias; a.mask = mask;
     a.bias_part = bias_part; a.M = M; a.N = N; a.K = K; a.splits = splits < 1 ? 1 : splits;
     a.k_per_split = k_per_split > 0 ? k_per_split : round_up(K, 32);
     if (engine >= 1) {
+        cudaStream_t s = as_stream(stream);
         sgemm_engine_flags(engine, &a);
         float *scratch = nullptr;
-        if (engine == 5) {              // test hook: the two operand maxima live in a transient allocation
-            OCPPO_CUDA(cudaMalloc(&scratch, 2 * sizeof(float)));
+        uint16_t *pairs = nullptr;
+        int r = OCPPO_OK;
+        if (engine >= 5) {              // test hook: operand maxima (and, engines 6 / 7, the fp16 pairs) live in transient allocations
+            OCPPO_CUDA(cudaMalloc(&scratch, 8 * sizeof(float)));
+            OCPPO_CUDA(cudaMemsetAsync(scratch, 0, 8 * sizeof(float), s));
             a.amax_scratch = scratch;
-            const int r0 = sgemm_fill_amax((SgemmMode)op, &a, as_stream(stream));
-            if (r0 != OCPPO_OK) { cudaFree(scratch); return r0; }
+            r = sgemm_fill_amax((SgemmMode)op, &a, s);
         }
-        const int r = tc_gemm_launch((SgemmMode)op, a, as_stream(stream));
-        if (scratch != nullptr) { cudaStreamSynchronize(as_stream(stream)); cudaFree(scratch); }
+        if (r == OCPPO_OK && engine >= 6) {
+            // engine 6: A and B split into pairs, fp32 C.  engine 7 (FWD / DGRAD): C leaves as a pair too and is merged back.
+            const int64_t a_rows = op == 2 ? K : M, a_cols = op == 2 ? M : K;
+            const int64_t b_rows = op == 0 ? N : K, b_cols = op == 0 ? K : N;
+            const int64_t na = a_rows * a_cols, nb = b_rows * b_cols, nc = (int64_t)M * N;
+            const bool ok = lda == a_cols && ldb == b_cols && ldc == N && na % 8 == 0 && nb % 8 == 0 && nc % 8 == 0;
+            if (!ok) { set_error("ocppo_gemm: engines 6 / 7 take contiguous operands"); r = OCPPO_EINVAL; }
+            a.bias_part = nullptr;      // WGRAD bias sums: a column-sum pass over the pair (below), not the GEMM kernel
+            const int64_t n_part = (op == 2 && bias_part != nullptr) ? (int64_t)kColsumBlocksMax * M * 2 : 0;   // floats, as uint16 pairs
+            if (r == OCPPO_OK && cudaMalloc(&pairs, (size_t)(2 * (na + nb + nc) + 2 * n_part) * sizeof(uint16_t)) != cudaSuccess) {
+                set_error("ocppo_gemm: transient allocation failed"); r = OCPPO_ECUDA;
+            }
+            if (r == OCPPO_OK) {
+                uint16_t *a_hi = pairs, *a_lo = pairs + na, *b_hi = a_lo + na, *b_lo = b_hi + nb, *c_hi = b_lo + nb, *c_lo = c_hi + nc;
+                r = launch_split16(A, na, a.amax_a, a_hi, a_lo, 0, s);
+                if (r == OCPPO_OK) r = launch_split16(B, nb, a.amax_b, b_hi, b_lo, 0, s);
+                a.a16_hi = a_hi; a.a16_lo = a_lo; a.b16_hi = b_hi; a.b16_lo = b_lo;
+                if (r == OCPPO_OK && engine == 7 && op != 2) {
+                    WnormSegs w{};
+                    w.w[0] = B; w.b[0] = op == 0 ? bias : nullptr; w.out_dim[0] = (int)b_rows; w.in_dim[0] = (int)b_cols;
+                    w.row_l1[0] = scratch + 2; w.col_l1[0] = scratch + 3; w.b_max[0] = scratch + 4; w.count = 1;
+                    r = launch_wnorm(w, s);
+                    a.c16_hi = c_hi; a.c16_lo = c_lo;
+                    a.bnd_amax = a.amax_a; a.bnd_wl1 = op == 0 ? scratch + 2 : scratch + 3; a.bnd_bmax = op == 0 && bias ? scratch + 4 : nullptr;
+                    a.c_scale_src = scratch + 5;
+                }
+                if (r == OCPPO_OK) r = tc_gemm_launch((SgemmMode)op, a, s);
+                if (r == OCPPO_OK && a.c16_hi != nullptr) r = launch_merge16(c_hi, c_lo, nc, scratch + 5, C, 0, s);
+                if (r == OCPPO_OK && n_part > 0) {          // bias_part[0] = column sums of A, the other splits' rows zero
+                    float *part = reinterpret_cast<float *>(c_lo + nc);
+                    int blocks = 0;
+                    cudaMemsetAsync(bias_part, 0, (size_t)a.splits * M * sizeof(float), s);
+                    r = launch_colsum16(a_hi, a_lo, K, M, a.amax_a, part, &blocks, 0, s);
+                    if (r == OCPPO_OK) r = launch_colsum_reduce(part, blocks, M, bias_part, 0, s);
+                }
+            }
+        } else if (r == OCPPO_OK) {
+            r = tc_gemm_launch((SgemmMode)op, a, s);
+        }
+        if (scratch != nullptr || pairs != nullptr) { cudaStreamSynchronize(s); cudaFree(scratch); cudaFree(pairs); }
         return r;
     }
     return fma_gemm_launch((SgemmMode)op, a, as_stream(stream));
@@ -599,7 +809,7 @@ int ocppo_minibatch_fwd_bwd(ocppo_handle *h, const float *b_obs, const int64_t *
         a.clip_f = (float)hp->clip_coef; a.ent_coef = (float)hp->ent_coef; a.vf_coef = (float)hp->vf_coef;
         a.norm_adv = hp->norm_adv; a.clip_vloss = hp->clip_vloss;
         a.dh = h->gbuf[0]; a.gz = h->gz;
-        const bool f16 = g_gemm_mode == 5;
+        const bool f16 = g_gemm_mode >= 5;
         if (f16) {
             OCPPO_CUDA(cudaMemsetAsync(h->amax + kAmaxGrad, 0, 2 * OCPPO_MAX_LAYERS * sizeof(float), s));
             a.dh_amax = h->amax + kAmaxGrad + h->n_layers - 1;
@@ -635,7 +845,7 @@ int ocppo_minibatch_fwd_bwd(ocppo_handle *h, const float *b_obs, const int64_t *
             OCPPO_TRY(launch_splitk_reduce(h->splitk_bias, g.splits, AP, A, h->grads + h->actor.b_off, acc, h->sm_count, s));
             OCPPO_TRY(launch_splitk_reduce(h->splitk_bias + A, g.splits, AP, 1, h->grads + h->critic.b_off, acc, h->sm_count, s));
         }
-        OCPPO_TRY(trunk_backward(h, h->x0, rows, 0, acc, s, g_gemm_mode == 5));
+        OCPPO_TRY(trunk_backward(h, h->x0, rows, 0, acc, s, g_gemm_mode >= 5));
     }
     OCPPO_TRY(launch_loss_finalize(h->loss_part, used, mb, (float)hp->ent_coef, (float)hp->vf_coef, stats, s));
     return OCPPO_OK;
@@ -686,6 +896,9 @@ int ocppo_read_activation(const ocppo_handle *h, int32_t layer, int64_t B, float
     OCPPO_CHECK_ARG(B >= 1 && B == h->last_forward_rows, "read_activation: B=%lld does not match last forward (%d)",
                     (long long)B, h->last_forward_rows);
     const Layer &L = h->layers[layer];
+    if (!h->act32_valid[layer] && h->act16_valid[layer])     // fp16-pair storage: the tensor only exists as (hi, lo)
+        return launch_merge16(h->act16_hi[layer], h->act16_lo[layer], B * L.row_mult * L.out_dim, h->act_scale[layer], out,
+                              h->sm_count, as_stream(stream));
     OCPPO_CUDA(cudaMemcpyAsync(out, h->act[layer], (size_t)B * L.row_mult * L.out_dim * sizeof(float),
                                cudaMemcpyDeviceToDevice, as_stream(stream)));
     return OCPPO_OK;

@@ -114,9 +114,21 @@ struct ocppo_handle {
     int act_amax_valid[2 * OCPPO_MAX_LAYERS];
     int w_amax_valid;
     void *w16_hi, *w16_lo;              // the trunk weights split into scaled fp16 hi / lo (indexed like params)
+    // fp16-pair storage (GEMM engine 6): activations of every trunk layer but the last and the gradients flowing down the
+    // trunk exist as (hi, lo) fp16 tensors; the fp32 buffers above are filled on demand only (merge16)
+    void *act16_hi[2 * OCPPO_MAX_LAYERS], *act16_lo[2 * OCPPO_MAX_LAYERS];
+    int act16_valid[2 * OCPPO_MAX_LAYERS], act32_valid[2 * OCPPO_MAX_LAYERS];
+    const float *act_scale[2 * OCPPO_MAX_LAYERS];   // device scalar the pair's power-of-two scale derives from
+    void *g16_hi[2], *g16_lo[2];        // pair twins of gbuf[]
+    float *colsum_part;                 // [kColsumBlocksMax, max(out)] bias-gradient partials
 };
+// device scalars in ocppo_handle::amax: true maxima (Act / W / Grad), the bounds the epilogues scale their fp16-pair outputs
+// by (BndAct + l: act[l]; BndGrad + l: gradient entering layer l's backward), and per layer the weights' largest row / column
+// L1 norm and largest |bias|
 constexpr int kAmaxAct = 2, kAmaxW = 2 + 2 * OCPPO_MAX_LAYERS, kAmaxGrad = 2 + 4 * OCPPO_MAX_LAYERS;
-constexpr int kAmaxSlots = 2 + 6 * OCPPO_MAX_LAYERS;
+constexpr int kBndAct = 2 + 6 * OCPPO_MAX_LAYERS, kBndGrad = 2 + 8 * OCPPO_MAX_LAYERS;
+constexpr int kWRowL1 = 2 + 10 * OCPPO_MAX_LAYERS, kWColL1 = 2 + 12 * OCPPO_MAX_LAYERS, kBMax = 2 + 14 * OCPPO_MAX_LAYERS;
+constexpr int kAmaxSlots = 2 + 16 * OCPPO_MAX_LAYERS;
 
 namespace ocppo {
 
@@ -137,6 +149,7 @@ struct SgemmArgs {
     int64_t k_per_split;
     int splits;
     int dbg;                  // tc_gemm bring-up variant (0 in production)
+    float trunc_scale;        // tc_gemm: multiplies the accumulator-truncation compensation (1 in production; set by the launcher)
     int single_acc;           // tc_gemm: 1 = one TMEM accumulator per tile (faster, ~3x the rounding error)
     int corr_bf16;            // tc_gemm: 1 = the two correction products run as BF16 MMAs (split accumulators only)
     int f16x3;                // tc_gemm: 1 = three FP16 products on per-tensor power-of-two scaled operands (engine 5)
@@ -146,12 +159,22 @@ struct SgemmArgs {
     float *amax_scratch;      // two floats of device scratch for the fallback reduction
     const void *b16_hi;       // f16x3, FWD / DGRAD: B already split into fp16 hi / lo tensors (same shape and ldb, scaled by
     const void *b16_lo;       //        the power of two that amax_b implies) -- the weights, split once per call
+    // fp16-pair storage (engine 6): activations / gradients live in global memory as (hi, lo) fp16 tensors of the fp32
+    // tensor's shape and stride.  With A and B both pre-split the conversion-free kernel runs (B also for WGRAD).
+    const void *a16_hi, *a16_lo;   // A pre-split, scaled by the power of two that *amax_a implies
+    void *c16_hi, *c16_lo;         // FWD / DGRAD: write C as an fp16 pair INSTEAD of fp32 C, scaled by the power of two of
+    const float *bnd_amax;         //   bound = *bnd_amax (true max |A|) * *bnd_wl1 (largest row / column L1 norm of the
+    const float *bnd_wl1;          //   weights) + *bnd_bmax (largest |bias|, may be null);
+    const float *bnd_bmax;
+    float *c_scale_src;            //   the kernel stores the bound here: the consumers' amax_a / amax_b
+    float *colsum_part;            // DGRAD, conversion-free kernel: [tc_gemm_ctas() * 4, N] column sums of C, pre-zeroed
 };
 
 int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);       // dispatches FMA / tensor
 int fma_gemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);    // sgemm.cu, fp32 CUDA cores
 bool tc_gemm_supported(SgemmMode mode, const SgemmArgs &a);                      // tc_gemm.cu, tcgen05 3xTF32
 int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream);
+int tc_gemm_ctas(SgemmMode mode, const SgemmArgs &a, int sm_count);                 // grid of that launch
 void sgemm_engine_flags(int engine, SgemmArgs *b);                               // engine number -> tc_gemm variant flags
 int sgemm_fill_amax(SgemmMode mode, SgemmArgs *b, cudaStream_t stream);          // FP16x3: measure missing operand maxima
 bool sgemm_uses_tc(SgemmMode mode, const SgemmArgs &a);                          // what sgemm_launch will pick
@@ -188,6 +211,18 @@ struct AbsmaxSegs { const float *x[2 * OCPPO_MAX_LAYERS]; int64_t n[2 * OCPPO_MA
 // hi[i] = fp16(x[i] s), lo[i] = fp16(x[i] s - hi[i]) per segment, s from the segment's max-abs (device scalar out[seg]);
 // hi / lo are indexed like x relative to segs.x[0]'s arena base `base`
 int launch_split_f16_multi(const AbsmaxSegs &segs, const float *base, void *hi, void *lo, cudaStream_t stream);
+// ---- fp16-pair storage (pair16.cu; GEMM engine 6) ----
+struct WnormSegs {
+    const float *w[2 * OCPPO_MAX_LAYERS]; const float *b[2 * OCPPO_MAX_LAYERS]; int out_dim[2 * OCPPO_MAX_LAYERS], in_dim[2 * OCPPO_MAX_LAYERS];
+    float *row_l1[2 * OCPPO_MAX_LAYERS], *col_l1[2 * OCPPO_MAX_LAYERS], *b_max[2 * OCPPO_MAX_LAYERS]; int count;
+};
+constexpr int kColsumBlocksMax = 1024;
+int launch_split16(const float *x, int64_t n, const float *scale_src, void *hi, void *lo, int sm_count, cudaStream_t stream);
+int launch_merge16(const void *hi, const void *lo, int64_t n, const float *scale_src, float *out, int sm_count, cudaStream_t stream);
+int launch_colsum16(const void *hi, const void *lo, int64_t rows, int cols, const float *scale_src, float *part, int *blocks,
+                    int sm_count, cudaStream_t stream);     // part: [kColsumBlocksMax][cols] at most; *blocks partial rows written
+int launch_colsum_reduce(const float *part, int parts, int cols, float *out, int accumulate, cudaStream_t stream);
+int launch_wnorm(const WnormSegs &segs, cudaStream_t stream);                     // outputs pre-zeroed
 int launch_absmax_multi(const AbsmaxSegs &segs, cudaStream_t stream);             // several small contiguous tensors, one launch; outs pre-zeroed
 // out[0] = max |x[r, c]| over an [rows, cols] view with row stride ld (zeroed first); absmax.cu
 int launch_absmax(const float *x, int64_t rows, int64_t cols, int64_t ld, float *out, int sm_count, cudaStream_t stream);

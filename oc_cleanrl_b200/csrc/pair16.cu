@@ -1,0 +1,209 @@
+// fp16-pair storage (GEMM engine 6): a tensor x lives in global memory as hi = fp16(x s), lo = fp16(x s - hi) with s the
+// power of two that a device scalar (the tensor's max-abs, or a rigorous bound on it) implies -- the layout the tensor-core
+// kernel (tc_gemm.cu, PRE variant) loads with TMA straight into its MMA tiles.  The GEMM epilogues write pairs themselves;
+// these HBM-bound passes cover the tensors that other kernels produce in fp32 (first-layer activations, the loss head's
+// gradient), the bias gradients (column sums of a pair) and the weight norms the epilogues' scale bounds come from.
+#include "common.cuh"
+#include <cuda_fp16.h>
+
+namespace ocppo {
+
+namespace {
+
+// x[n] fp32 -> pair; n % 4 == 0, 16-byte aligned
+__global__ void __launch_bounds__(256) split16_kernel(const float *__restrict__ x, int64_t n4, const float *__restrict__ scale_src,
+                                                      uint2 *__restrict__ hi, uint2 *__restrict__ lo) {
+    float scale, inv;
+    f16_scale_of(__ldg(scale_src), scale, inv);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        const float4 v = __ldcs(reinterpret_cast<const float4 *>(x) + i);
+        uint32_t h0, l0, h1, l1;
+        split_f16x2(v.x, v.y, scale, h0, l0);
+        split_f16x2(v.z, v.w, scale, h1, l1);
+        hi[i] = make_uint2(h0, h1);
+        lo[i] = make_uint2(l0, l1);
+    }
+}
+
+__device__ __forceinline__ float4 merge4(const uint2 h, const uint2 l, float inv) {
+    const float2 h0 = __half22float2(*reinterpret_cast<const __half2 *>(&h.x)), h1 = __half22float2(*reinterpret_cast<const __half2 *>(&h.y));
+    const float2 l0 = __half22float2(*reinterpret_cast<const __half2 *>(&l.x)), l1 = __half22float2(*reinterpret_cast<const __half2 *>(&l.y));
+    return make_float4((h0.x + l0.x) * inv, (h0.y + l0.y) * inv, (h1.x + l1.x) * inv, (h1.y + l1.y) * inv);
+}
+
+// pair -> fp32 (test hooks, fp32 consumers of a tensor that only exists as a pair)
+__global__ void __launch_bounds__(256) merge16_kernel(const uint2 *__restrict__ hi, const uint2 *__restrict__ lo, int64_t n4,
+                                                      const float *__restrict__ scale_src, float4 *__restrict__ out) {
+    float scale, inv;
+    f16_scale_of(__ldg(scale_src), scale, inv);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x)
+        out[i] = merge4(__ldg(hi + i), __ldg(lo + i), inv);
+}
+
+// column sums of a pair [rows, cols] (cols % 4 == 0): block g sums its fixed slab of rows into part[g][cols] -- a fixed
+// order, so the bias gradients stay bitwise repeatable.  Thread t owns the 4 columns 4 (t % (cols / 4)) and every
+// (256 / (cols / 4))-th row of the slab when cols < 1024.
+__global__ void __launch_bounds__(256) colsum16_kernel(const uint2 *__restrict__ hi, const uint2 *__restrict__ lo, int64_t rows, int cols,
+                                                       int64_t rows_per_block, const float *__restrict__ scale_src,
+                                                       float *__restrict__ part) {
+    float scale, inv;
+    f16_scale_of(__ldg(scale_src), scale, inv);
+    const int cq = cols >> 2;                                   // float4 groups per row
+    const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+    const int64_t r1 = r0 + rows_per_block < rows ? r0 + rows_per_block : rows;
+    __shared__ float4 red[256];
+    for (int c0 = 0; c0 < cq; c0 += 256) {
+        const int lanes = cq - c0 < 256 ? cq - c0 : 256;        // column groups handled in this pass
+        const int rstep = 256 / lanes > 0 ? 256 / lanes : 1;    // rows processed side by side
+        const int cg = threadIdx.x % lanes, rl = threadIdx.x / lanes;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (rl < rstep)
+            for (int64_t r = r0 + rl; r < r1; r += rstep) {
+                const int64_t i = r * cq + c0 + cg;
+                const float4 v = merge4(__ldcs(hi + i), __ldcs(lo + i), 1.f);
+                acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+            }
+        red[threadIdx.x] = acc;
+        __syncthreads();
+        if (threadIdx.x < lanes) {
+            float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int k = 0; k < rstep; ++k) {
+                const float4 v = red[k * lanes + threadIdx.x];
+                s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+            }
+            reinterpret_cast<float4 *>(part + (int64_t)blockIdx.x * cols)[c0 + threadIdx.x] =
+                make_float4(s.x * inv, s.y * inv, s.z * inv, s.w * inv);
+        }
+        __syncthreads();
+    }
+}
+
+// per weight matrix W[out, in] (+ bias[out]): largest row L1 norm, largest column L1 norm, largest |bias| as float bits
+// (atomicMax on pre-zeroed slots).  grid (slices, matrices)
+__global__ void __launch_bounds__(256) wnorm_kernel(WnormSegs segs) {
+    const int m = blockIdx.y;
+    const float *W = segs.w[m];
+    const int out = segs.out_dim[m], in = segs.in_dim[m];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float rmax = 0.f;
+    for (int j = blockIdx.x * 8 + warp; j < out; j += gridDim.x * 8) {
+        float s = 0.f;
+        for (int k = lane; k < in; k += 32) s += fabsf(__ldg(W + (int64_t)j * in + k));
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        rmax = fmaxf(rmax, s);
+    }
+    float cmax = 0.f;
+    for (int k = blockIdx.x * 256 + threadIdx.x; k < in; k += gridDim.x * 256) {
+        float s = 0.f;
+        for (int j = 0; j < out; ++j) s += fabsf(__ldg(W + (int64_t)j * in + k));
+        cmax = fmaxf(cmax, s);
+    }
+    float bmax = 0.f;
+    if (blockIdx.x == 0 && segs.b[m] != nullptr)
+        for (int j = threadIdx.x; j < out; j += 256) bmax = fmaxf(bmax, fabsf(__ldg(segs.b[m] + j)));
+    // sums of non-negative terms in fp32 can come out a few ulp low: pad the norms so the bound stays a bound
+    rmax *= 1.0001f; cmax *= 1.0001f;
+    const unsigned r = __reduce_max_sync(0xffffffffu, __float_as_uint(rmax));
+    const unsigned c = __reduce_max_sync(0xffffffffu, __float_as_uint(cmax));
+    const unsigned b = __reduce_max_sync(0xffffffffu, __float_as_uint(bmax));
+    if (lane == 0) {
+        if (r) atomicMax(reinterpret_cast<unsigned *>(segs.row_l1[m]), r);
+        if (c) atomicMax(reinterpret_cast<unsigned *>(segs.col_l1[m]), c);
+        if (b) atomicMax(reinterpret_cast<unsigned *>(segs.b_max[m]), b);
+    }
+}
+
+// out[c] (+)= sum over p of part[p][c]: block = 32 columns, warp w adds rows w, w + 8, ... in order, then the 8 warps fold in
+// order -- a fixed summation tree whatever the launch looks like
+__global__ void __launch_bounds__(256) colsum_reduce_kernel(const float *__restrict__ part, int parts, int cols, float *__restrict__ out,
+                                                            int accumulate) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, c = blockIdx.x * 32 + lane;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    if (c < cols) {
+        int r = warp;
+        for (; r + 24 < parts; r += 32) {
+            s0 += __ldg(part + (int64_t)r * cols + c);
+            s1 += __ldg(part + (int64_t)(r + 8) * cols + c);
+            s2 += __ldg(part + (int64_t)(r + 16) * cols + c);
+            s3 += __ldg(part + (int64_t)(r + 24) * cols + c);
+        }
+        for (; r < parts; r += 8) s0 += __ldg(part + (int64_t)r * cols + c);
+    }
+    __shared__ float red[8][33];
+    red[warp][lane] = (s0 + s1) + (s2 + s3);
+    __syncthreads();
+    if (warp == 0 && c < cols) {
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) s += red[w][lane];
+        out[c] = accumulate ? out[c] + s : s;
+    }
+}
+
+inline int grid_of(int64_t items, int sm_count) {
+    int64_t g = ceil_div(items, 256 * 4);
+    const int64_t cap = (int64_t)(sm_count > 0 ? sm_count : 148) * 8;
+    if (g > cap) g = cap;
+    return g < 1 ? 1 : (int)g;
+}
+
+}  // namespace
+
+int launch_split16(const float *x, int64_t n, const float *scale_src, void *hi, void *lo, int sm_count, cudaStream_t stream) {
+    if (n == 0) return OCPPO_OK;
+    OCPPO_CHECK_ARG(x && scale_src && hi && lo && n % 4 == 0 && ((((uintptr_t)x) | ((uintptr_t)hi) | ((uintptr_t)lo)) & 15) == 0,
+                    "split16: bad arguments");
+    ProfScope ps(KC_AUX, 1, stream);
+    split16_kernel<<<grid_of(n / 4, sm_count), 256, 0, stream>>>(x, n / 4, scale_src, reinterpret_cast<uint2 *>(hi), reinterpret_cast<uint2 *>(lo));
+    OCPPO_LAUNCH_CHECK("split16_kernel");
+    return OCPPO_OK;
+}
+
+int launch_merge16(const void *hi, const void *lo, int64_t n, const float *scale_src, float *out, int sm_count, cudaStream_t stream) {
+    if (n == 0) return OCPPO_OK;
+    OCPPO_CHECK_ARG(hi && lo && scale_src && out && n % 4 == 0, "merge16: bad arguments");
+    ProfScope ps(KC_AUX, 1, stream);
+    merge16_kernel<<<grid_of(n / 4, sm_count), 256, 0, stream>>>(reinterpret_cast<const uint2 *>(hi), reinterpret_cast<const uint2 *>(lo), n / 4,
+                                                                 scale_src, reinterpret_cast<float4 *>(out));
+    OCPPO_LAUNCH_CHECK("merge16_kernel");
+    return OCPPO_OK;
+}
+
+int colsum16_blocks(int64_t rows, int sm_count) {
+    int64_t g = (int64_t)(sm_count > 0 ? sm_count : 148) * 4;
+    if (g > kColsumBlocksMax) g = kColsumBlocksMax;
+    if (g > rows) g = rows;
+    return g < 1 ? 1 : (int)g;
+}
+
+int launch_colsum16(const void *hi, const void *lo, int64_t rows, int cols, const float *scale_src, float *part, int *blocks,
+                    int sm_count, cudaStream_t stream) {
+    OCPPO_CHECK_ARG(hi && lo && scale_src && part && blocks && rows >= 1 && cols >= 4 && cols % 4 == 0, "colsum16: bad arguments");
+    const int g = colsum16_blocks(rows, sm_count);
+    const int64_t rpb = ceil_div(rows, g);
+    *blocks = (int)ceil_div(rows, rpb);
+    ProfScope ps(KC_AUX, 1, stream);
+    colsum16_kernel<<<*blocks, 256, 0, stream>>>(reinterpret_cast<const uint2 *>(hi), reinterpret_cast<const uint2 *>(lo), rows, cols, rpb,
+                                                 scale_src, part);
+    OCPPO_LAUNCH_CHECK("colsum16_kernel");
+    return OCPPO_OK;
+}
+
+int launch_colsum_reduce(const float *part, int parts, int cols, float *out, int accumulate, cudaStream_t stream) {
+    OCPPO_CHECK_ARG(part && out && parts >= 1 && cols >= 1, "colsum_reduce: bad arguments");
+    ProfScope ps(KC_AUX, 1, stream);
+    colsum_reduce_kernel<<<(unsigned)ceil_div(cols, 32), 256, 0, stream>>>(part, parts, cols, out, accumulate);
+    OCPPO_LAUNCH_CHECK("colsum_reduce_kernel");
+    return OCPPO_OK;
+}
+
+int launch_wnorm(const WnormSegs &segs, cudaStream_t stream) {
+    if (segs.count <= 0) return OCPPO_OK;
+    ProfScope ps(KC_AUX, 1, stream);
+    wnorm_kernel<<<dim3(16, (unsigned)segs.count), 256, 0, stream>>>(segs);
+    OCPPO_LAUNCH_CHECK("wnorm_kernel");
+    return OCPPO_OK;
+}
+
+}  // namespace ocppo

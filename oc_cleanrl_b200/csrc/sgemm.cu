@@ -205,9 +205,9 @@ static int tc_ops_mask() {
 }
 
 void sgemm_engine_flags(int engine, SgemmArgs *b) {
-    b->single_acc = engine == 2 || engine == 4;
+    b->single_acc = engine == 2 || engine == 4 || engine == 8;    // 8: fp16-pair storage, one double-buffered accumulator
     b->corr_bf16 = engine >= 3;
-    b->f16x3 = engine == 5;
+    b->f16x3 = engine >= 5;       // 6, 7: same kernels, operands / outputs stored as fp16 pairs
 }
 
 bool sgemm_uses_tc(SgemmMode mode, const SgemmArgs &a) {

@@ -56,7 +56,7 @@ constexpr int kTcThreads = kProdTid0 + kProdThreads;        // 576: at most 112 
 constexpr int kProdQ = 1024 / kProdThreads;                 // 16-byte chunks of a 16 KB raw tile per producer thread (4)
 constexpr int kStageBytesA = TM * TK * 4;                   // 16 KB
 constexpr int kRingBytes = 192 * 1024;                      // 3 x 64 KB or 4 x 48 KB
-constexpr int kMaxStages = 4;
+constexpr int kMaxStages = 6;
 constexpr int kTmemCols = 512;                              // two tiles' accumulators
 // The TMEM accumulator rounds TOWARD ZERO on every accumulate (tools/tc_probe.cu Q4): each chained MMA shrinks the running
 // sum by half an ulp on average, a systematic loss that does not average out -- through five layers forward and
@@ -69,7 +69,8 @@ constexpr float kTruncPerMma = 2.1e-8f;
 constexpr int kEpiChunkBytes = 32 * 32 * 4;                 // one warp's 32 rows x 32 columns, SWIZZLE_128B
 constexpr int kEpiPadBytes = kEpiWarps * kEpiChunkBytes;    // per warp: one chunk, incoming aux then outgoing result (32 KB)
 constexpr int kBiasRedBytes = 4 * TM * 4;                   // WGRAD bias partials [4][128] (2 KB): the 8 k-lanes fold in two steps
-constexpr int kTcSmemBytes = kRingBytes + kEpiPadBytes + kBiasRedBytes + 256 /*barriers*/;   // base is 1024-aligned
+constexpr int kBarBytes = 512;                               // 36 mbarriers + the TMEM slot
+constexpr int kTcSmemBytes = kRingBytes + kEpiPadBytes + kBiasRedBytes + kBarBytes;   // base is 1024-aligned
 static_assert(kTcSmemBytes <= 232448, "shared memory budget (227 KB per CTA)");
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -379,20 +380,25 @@ __device__ __forceinline__ TileCoord tile_coord(const SgemmArgs &p, int tile, in
         : "memory")
 
 template <int MODE, bool SPLIT, int CORR>      // CORR: 0 = TF32 corrections, 1 = BF16 corrections, 2 = FP16 x 3 (no TF32 pass)
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_gemm_kernel(SgemmArgs p, int nt_n, int nt_m, int ntiles, const __grid_constant__ CUtensorMap tmA,
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid0 : kTcThreads, 1) tc_gemm_kernel(SgemmArgs p, int nt_n, int nt_m, int ntiles, const __grid_constant__ CUtensorMap tmA,
                                                                                          const __grid_constant__ CUtensorMap tmB,
                                                                                          const __grid_constant__ CUtensorMap tmC,
                                                                                          const __grid_constant__ CUtensorMap tmX,
-                                                                                         const __grid_constant__ CUtensorMap tmB2) {
+                                                                                         const __grid_constant__ CUtensorMap tmB2,
+                                                                                         const __grid_constant__ CUtensorMap tmA2,
+                                                                                         const __grid_constant__ CUtensorMap tmC2) {
     constexpr bool A_MN = (MODE == SGEMM_WGRAD);
     constexpr bool B_MN = (MODE != SGEMM_FWD);
-    constexpr bool CORR16 = CORR >= 1, F16 = CORR == 2;
+    constexpr bool CORR16 = CORR >= 1, F16 = CORR >= 2, PRE = CORR == 3;   // PRE: both operands arrive as fp16 hi / lo pairs
     constexpr int TN = Tile<SPLIT>::TN, TBW = Tile<SPLIT>::TBW, kStageBytesB = Tile<SPLIT>::kStageBytesB;
     constexpr int kStageBytes = Tile<SPLIT>::kStageBytes, kNumStages = Tile<SPLIT>::kNumStages;
     constexpr int kAccStride = Tile<SPLIT>::kAccStride, kAccBufs = Tile<SPLIT>::kAccBufs;
     // MMA instructions chained into the (main) accumulator per 32-deep stage: 4 main products, plus the corrections when
     // they share the accumulator (8 TF32 or 4 BF16; a K = 16 BF16 instruction loses about 1.5x what a K = 8 TF32 one does)
-    constexpr int kMmaPerStage = SPLIT ? (F16 ? 3 : 4) : (CORR16 ? 10 : 12);   // F16: two K = 16 instructions
+    // FP16 x 3: calibrated on zero-mean products (tools/acc_sweep.sh) -- every GEMM of the trunk multiplies a signed operand,
+    // so the running sum is a random walk and loses ~0.6 of what a linearly growing sum would: 2 K = 16 instructions per
+    // stage in the main accumulator (split), 6 when the corrections share it
+    constexpr float kMmaPerStage = F16 ? (SPLIT ? 1.9f : 5.6f) : (SPLIT ? 4.f : (CORR16 ? 10.f : 12.f));
     // stage layout.  3xTF32: [A raw = hi 16K][A lo 16K][B raw = hi 16K][B lo 16K];
     // CORR16:  [A raw 16K][B raw 16K][A bf16 8K][A lo bf16 8K][B bf16 8K][B lo bf16 8K]
     constexpr int kOffA = 0, kOffB = CORR16 ? kStageBytesA : 2 * kStageBytesA;
@@ -401,10 +407,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
     constexpr int kOffA16_ = 2 * kStageBytesA, kOffB16_ = 3 * kStageBytesA;     // CORR16 only
     // FP16 x 3 with the weights pre-split in global memory (FWD / DGRAD of the learner): nothing ever lands in the raw-B
     // slot, so the stage shrinks to [A raw 16K][A hi 8K][A lo 8K][B hi 8K][B lo 8K] = 48 KB and the ring holds FOUR stages
-    const bool compact = F16 && MODE != SGEMM_WGRAD && p.b16_hi != nullptr && !(p.dbg & 64);
-    const int stage_bytes = compact ? 48 * 1024 : kStageBytes, nstages = compact ? 4 : kNumStages;
-    const int kOffA16 = compact ? kStageBytesA : kOffA16_, kOffALo = compact ? kStageBytesA + kStageBytesA / 2 : kOffALo_;
-    const int kOffB16 = compact ? 2 * kStageBytesA : kOffB16_, kOffBLo = compact ? 2 * kStageBytesA + kStageBytesB / 2 : kOffBLo_;
+    // PRE: both operands live in global memory as fp16 pairs: [A hi 8K][A lo 8K][B hi 8K][B lo 8K] = 32 KB, SIX stages,
+    // no conversion warps at all (the kernel is launched with the first ten warps only)
+    const bool compact = !PRE && F16 && MODE != SGEMM_WGRAD && p.b16_hi != nullptr && !(p.dbg & 64);
+    const int stage_bytes = PRE ? 32 * 1024 : (compact ? 48 * 1024 : kStageBytes);
+    const int nstages = PRE ? ((p.dbg & 128) ? 3 : 6) : (compact ? 4 : kNumStages);
+    const int kOffA16 = PRE ? 0 : (compact ? kStageBytesA : kOffA16_);
+    const int kOffALo = PRE ? kStageBytesA / 2 : (compact ? kStageBytesA + kStageBytesA / 2 : kOffALo_);
+    const int kOffB16 = PRE ? kStageBytesA : (compact ? 2 * kStageBytesA : kOffB16_);
+    const int kOffBLo = PRE ? kStageBytesA + kStageBytesB / 2 : (compact ? 2 * kStageBytesA + kStageBytesB / 2 : kOffBLo_);
 
     static_assert(kNumStages * kStageBytes <= kRingBytes && kNumStages <= kMaxStages, "stage ring");
     // The TMEM accumulator adds with truncation (measured: error grows linearly with the number of MMAs
@@ -416,15 +427,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
     float *epi_pad = reinterpret_cast<float *>(smem + kRingBytes);
     float *bias_red = reinterpret_cast<float *>(smem + kRingBytes + kEpiPadBytes);
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kRingBytes + kEpiPadBytes + kBiasRedBytes);
-    // bars[0..3] full (used in the leader CTA), [4..7] empty, [8..9] tmem_full, [10..11] tmem_empty (leader),
-    // [12..15] tma (raw tile landed, per CTA), [16..23] aux chunk landed (one per epilogue warp),
-    // [24..27] raw_full (leader: raw tiles of BOTH CTAs landed -- the main product needs nothing else)
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 28);
-    const uint32_t bar_rawfull = smem_u32(&bars[24]);
-    const uint32_t bar_aux = smem_u32(&bars[16]);
-    const uint32_t bar_tma = smem_u32(&bars[12]);
-    const uint32_t bar_full = smem_u32(&bars[0]), bar_empty = smem_u32(&bars[4]);
-    const uint32_t bar_tfull = smem_u32(&bars[8]), bar_tempty = smem_u32(&bars[10]);
+    // bars[0..5] full (used in the leader CTA), [6..11] empty, [12..13] tmem_full, [14..15] tmem_empty (leader),
+    // [16..21] tma (tiles landed, per CTA), [22..29] aux chunk landed (one per epilogue warp),
+    // [30..35] raw_full (leader: the PEER's tiles landed; the leader polls its own tma barrier)
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 36);
+    const uint32_t bar_rawfull = smem_u32(&bars[30]);
+    const uint32_t bar_aux = smem_u32(&bars[22]);
+    const uint32_t bar_tma = smem_u32(&bars[16]);
+    const uint32_t bar_full = smem_u32(&bars[0]), bar_empty = smem_u32(&bars[6]);
+    const uint32_t bar_tfull = smem_u32(&bars[12]), bar_tempty = smem_u32(&bars[14]);
     const uint32_t cta_rank = cluster_ctarank();             // 0 = leader of the pair
     const int ncl = gridDim.x >> 1, cl = blockIdx.x >> 1;    // clusters in the grid, this cluster
 
@@ -433,6 +444,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
     if (F16) {
         f16_scale_of(__ldg(p.amax_a), scale_a, inv_a);
         f16_scale_of(__ldg(p.amax_b), scale_b, inv_b);
+    }
+    // fp16-pair output (FWD / DGRAD): the scale must be fixed before the first element exists, so it comes from a rigorous
+    // bound, max|A| * (largest row / column L1 norm of the weights) + max|bias| -- typically 2^3 .. 2^6 above the true
+    // maximum, which costs nothing that matters: elements keep an absolute accuracy of 2^-40 of the BOUND
+    const bool out16 = F16 && MODE != SGEMM_WGRAD && p.c16_hi != nullptr;
+    float scale_c = 1.f;
+    if (out16) {
+        const float bound = __ldg(p.bnd_amax) * __ldg(p.bnd_wl1) + (p.bnd_bmax != nullptr ? __ldg(p.bnd_bmax) : 0.f);
+        float inv_c;
+        f16_scale_of(bound, scale_c, inv_c);
+        if (blockIdx.x == 0 && tid == 0) *p.c_scale_src = bound;       // what the consumers derive the same scale from
     }
     // The TMEM accumulator adds with round-toward-zero (tools/tc_probe.cu Q4): every MMA chained into it costs
     // about half an ulp of bias, and two of the three passes only add tiny correction products.  With SPLIT
@@ -445,7 +467,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
             mbar_init(bar_full + 8 * s, 2 * kProdWarps);     // both CTAs' producer warps
             mbar_init(bar_empty + 8 * s, 1);
             mbar_init(bar_tma + 8 * s, 1);
-            mbar_init(bar_rawfull + 8 * s, F16 ? kProdWarps : 1);   // the peer's forwarder | F16: raw tile consumed (own producers)
+            mbar_init(bar_rawfull + 8 * s, (F16 && !PRE) ? kProdWarps : 1);   // the peer's forwarder | F16: raw tile consumed (own producers)
         }
         for (int w = 0; w < kEpiWarps; ++w) mbar_init(bar_aux + 8 * w, 1);
         for (int a = 0; a < 2; ++a) {
@@ -488,7 +510,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
             const int nbuf = (p.dbg & 4) ? 1 : kAccBufs, acc = ai % nbuf;
             const bool rmw = (MODE == SGEMM_WGRAD) && kb0 > 0;     // later k-segments add onto the first
             const int seg_stages = t.nk - kb0 < kSegStages ? t.nk - kb0 : kSegStages;
-            const float trunc_comp = (p.dbg & 8) ? 0.f : kTruncPerMma * (float)(seg_stages * kMmaPerStage);
+            const float trunc_comp = (p.dbg & 8) ? 0.f : kTruncPerMma * p.trunc_scale * ((float)seg_stages * kMmaPerStage);
             const bool bits = (MODE == SGEMM_DGRAD) && p.relu_bits != nullptr;   // ReLU decisions as packed words
             const bool aux = ((MODE == SGEMM_DGRAD) && !bits) || rmw;
             const int m_loc = t.m0 + (int)cta_rank * TM + quarter * 32;     // first of this warp's 32 rows
@@ -542,7 +564,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                 for (int j = 0; j < 32; ++j) {
                     float x = __uint_as_float(v[j]);
                     x = fmaf(x, trunc_comp, x);
-                    if (F16) x = ((x + __uint_as_float(w[j])) * inv_a) * inv_b;
+                    if (F16) x = ((split_acc ? x + __uint_as_float(w[j]) : x) * inv_a) * inv_b;
                     else if (split_acc) x += __uint_as_float(w[j]);
                     v[j] = __float_as_uint(x);
                 }
@@ -563,6 +585,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                 if (bits) word = (cc & 2) ? ((cc & 1) ? rb.w : rb.z) : ((cc & 1) ? rb.y : rb.x);
                 // each lane reads (aux) and writes only its own row of the tile, and every value written depends on
                 // the aux value read from the same place, so no lane can overwrite data that is still to be read
+                // (fp16-pair output: rows move, but every lane's aux row is in registers before the __syncwarp above)
+                uint32_t ph0 = 0, ph1 = 0, pl0 = 0, pl1 = 0;
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
                     float4 o = make_float4(__uint_as_float(v[4 * c]), __uint_as_float(v[4 * c + 1]),
@@ -585,15 +609,50 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                     } else if (rmw) {
                         o.x += ax[c].x; o.y += ax[c].y; o.z += ax[c].z; o.w += ax[c].w;
                     }
+                    if (PRE && MODE == SGEMM_DGRAD) {          // kept for the column sums below
+                        v[4 * c] = __float_as_uint(o.x); v[4 * c + 1] = __float_as_uint(o.y);
+                        v[4 * c + 2] = __float_as_uint(o.z); v[4 * c + 3] = __float_as_uint(o.w);
+                    }
+                    if (out16) {
+                        // fp16 pair: two [32 rows][32 fp16] tiles (hi at 0, lo at 2 KB), 64-byte rows, SWIZZLE_64B; one
+                        // 16-byte unit = 8 columns = two of these float4 groups (conflict-free per quarter-warp)
+                        uint32_t h0, l0, h1, l1;
+                        split_f16x2(o.x, o.y, scale_c, h0, l0);
+                        split_f16x2(o.z, o.w, scale_c, h1, l1);
+                        if ((c & 1) == 0) { ph0 = h0; ph1 = h1; pl0 = l0; pl1 = l1; }
+                        else {
+                            const int off16 = lane * 64 + ((((c >> 1) ^ (lane >> 1)) & 3) << 4);
+                            *reinterpret_cast<uint4 *>(out_tile + off16) = make_uint4(ph0, ph1, h0, h1);
+                            *reinterpret_cast<uint4 *>(out_tile + 2048 + off16) = make_uint4(pl0, pl1, l0, l1);
+                        }
+                    } else
                     *reinterpret_cast<float4 *>(out_tile + lane * 128 + ((c ^ swz) << 4)) = o;
                     if (MODE != SGEMM_WGRAD && m_loc + lane < p.M) run_max = fmaxf(fmaxf(run_max, fmaxf(fabsf(o.x), fabsf(o.y))), fmaxf(fabsf(o.z), fabsf(o.w)));
                 }
                 if (MODE == SGEMM_FWD && p.relu_bits != nullptr && m_loc + lane < p.M) p.relu_bits[rb_off + cc] = word;
+                if (PRE && MODE == SGEMM_DGRAD && p.colsum_part != nullptr) {
+                    // bias gradient of the layer below = column sums of this output: the warp's 32 rows fold in a butterfly
+                    // (31 shuffles; lane j ends with column j), then onto the warp's PRIVATE partial row in global memory
+                    // (rows past M are exact zeros).  Fixed order everywhere: bitwise repeatable.
+#pragma unroll
+                    for (int off = 16; off >= 1; off >>= 1) {
+                        const bool up = (lane & off) != 0;
+#pragma unroll
+                        for (int j = 0; j < off; ++j) {
+                            const float lo_v = __uint_as_float(v[j]), hi_v = __uint_as_float(v[j + off]);
+                            const float got = __shfl_xor_sync(0xffffffffu, up ? lo_v : hi_v, off);
+                            v[j] = __float_as_uint((up ? hi_v : lo_v) + got);
+                        }
+                    }
+                    float *cp = p.colsum_part + ((int64_t)blockIdx.x * 4 + quarter) * p.N + n + lane;
+                    *cp += __uint_as_float(v[0]);
+                }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
                 if (lane == 0) {
                     if (!(p.dbg & 2)) {
                         tma_store_2d(&tmC, out_s, n, row0);
+                        if (out16) tma_store_2d(&tmC2, out_s + 2048, n, row0);
                         bulk_commit();
                     }
                     if (aux && cc + 1 < kChunks) {           // next aux chunk, once the store has read the tile
@@ -658,7 +717,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                             // all three products need the producers' tiles: h.h into the main accumulator, h.l + l.h
                             // (2^-11 of it, applied by the epilogue) into the correction accumulator
                             constexpr uint32_t idescf = make_idesc_f16(kPairM, TN, A_MN, B_MN);
-                            mbar_wait(bar_full + 8 * s, (uint32_t)fphase);
+                            if (PRE) {
+                                mbar_wait(bar_tma + 8 * s, (uint32_t)fphase);        // own fp16 tiles (TMA)
+                                mbar_wait(bar_rawfull + 8 * s, (uint32_t)fphase);    // the peer's
+                            } else {
+                                mbar_wait(bar_full + 8 * s, (uint32_t)fphase);
+                            }
                             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
                             for (int k2 = 0; k2 < TK / 16; ++k2)
@@ -666,8 +730,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                             if (!(p.dbg & 32))       // timing experiment: main product only
 #pragma unroll
                             for (int k2 = 0; k2 < TK / 16; ++k2) {
-                                umma_bf16(d_tmem + TN, da16lo + k2 * a16_step, db16 + k2 * b16_step, idescf, (kb > kb0 || k2 > 0) ? 1u : 0u);
-                                umma_bf16(d_tmem + TN, da16 + k2 * a16_step, db16lo + k2 * b16_step, idescf, 1u);
+                                const uint32_t d_corrf = split_acc ? d_tmem + TN : d_tmem;
+                                umma_bf16(d_corrf, da16lo + k2 * a16_step, db16 + k2 * b16_step, idescf, (!split_acc || kb > kb0 || k2 > 0) ? 1u : 0u);
+                                umma_bf16(d_corrf, da16 + k2 * a16_step, db16lo + k2 * b16_step, idescf, 1u);
                             }
                             umma_commit_pair(bar_empty + 8 * s);
                             continue;
@@ -713,6 +778,29 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                 const TileCoord t = tile_coord(p, tile, nt_n, nt_m, TN);
                 for (int kb = 0; kb < t.nk; ++kb) {
                     const int s = stage;
+                    if (PRE) {
+                        // both operands as fp16 hi / lo pairs, straight into the MMA's tiles: four loads per stage
+                        const uint32_t st = smem_u32(smem + s * stage_bytes), bar = bar_tma + 8 * s;
+                        const int k0 = (int)(t.kbeg + (int64_t)kb * TK);
+                        mbar_wait(bar_empty + 8 * s, (uint32_t)(sphase ^ 1));
+                        mbar_expect_tx(bar, kStageBytesA + kStageBytesB);
+                        if (A_MN) {
+                            tma_load_3d(st + kOffA16, &tmA, 0, k0, (t.m0 + rank_m) >> 6, bar);
+                            tma_load_3d(st + kOffALo, &tmA2, 0, k0, (t.m0 + rank_m) >> 6, bar);
+                        } else {
+                            tma_load_2d(st + kOffA16, &tmA, k0, t.m0 + rank_m, bar);
+                            tma_load_2d(st + kOffALo, &tmA2, k0, t.m0 + rank_m, bar);
+                        }
+                        if (B_MN) {
+                            tma_load_3d(st + kOffB16, &tmB, 0, k0, (t.n0 + rank_n) >> 6, bar);
+                            tma_load_3d(st + kOffBLo, &tmB2, 0, k0, (t.n0 + rank_n) >> 6, bar);
+                        } else {
+                            tma_load_2d(st + kOffB16, &tmB, k0, t.n0 + rank_n, bar);
+                            tma_load_2d(st + kOffBLo, &tmB2, k0, t.n0 + rank_n, bar);
+                        }
+                        if (++stage == nstages) { stage = 0; sphase ^= 1; }
+                        continue;
+                    }
                     // F16: nothing but the producers reads the raw tiles, so they are refilled as soon as the conversion
                     // has consumed them -- one MMA stage earlier than the converted tiles come free
                     mbar_wait((F16 ? bar_rawfull : bar_empty) + 8 * s, (uint32_t)(sphase ^ 1));
@@ -740,7 +828,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
                 }
             }
         }
-        else if (!F16 && warp == kEpiWarps && lane == 0 && cta_rank == 1) {
+        else if ((!F16 || PRE) && warp == kEpiWarps && lane == 0 && cta_rank == 1) {
             // ===================== raw-tile forwarder (warp 8 of the peer CTA) =====================
             // tells the leader's MMA issuer that this CTA's raw tiles of a stage have landed (the leader polls its own)
             int stage = 0, sphase = 0;
@@ -754,7 +842,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1) tc_ge
             }
         }
         __syncwarp();
-    } else {
+    } else if (!PRE) {
         // ===================== producers =====================
         const int pt = tid - kProdTid0;
         const int pwarp_lane0 = (lane == 0);
@@ -926,12 +1014,34 @@ int make_map_c(CUtensorMap *tm, const float *base, int64_t rows, int64_t cols, i
     return OCPPO_OK;
 }
 
+// fp16 half of an fp16-pair output [rows, cols]: box 32 x 32 = 64-byte rows, SWIZZLE_64B (what the epilogue writes)
+int make_map_c16(CUtensorMap *tm, const void *base, int64_t rows, int64_t cols, int64_t ld) {
+    EncodeTiledFn fn = encode_fn();
+    if (fn == nullptr) { set_error("cuTensorMapEncodeTiled entry point not available"); return OCPPO_ECUDA; }
+    const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    const cuuint32_t box[2] = {32, 32}, estr[2] = {1, 1};
+    const CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (fp16 output map) failed (%d)", (int)r); return OCPPO_ECUDA; }
+    return OCPPO_OK;
+}
+
 }  // namespace
+
+int tc_gemm_ctas(SgemmMode mode, const SgemmArgs &a, int sm_count) {
+    const int tn = tc_tile_n(a.single_acc != 0);
+    const int64_t ntiles = (int64_t)(a.N / tn) * ceil_div(a.M, kPairM) * (mode == SGEMM_WGRAD ? a.splits : 1);
+    return (int)(2 * (ntiles < sm_count / 2 ? ntiles : sm_count / 2));
+}
 
 int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
     static const int dbg = getenv("OCPPO_TC_DBG") ? atoi(getenv("OCPPO_TC_DBG")) : 0;   // bring-up knob only
+    static const float trunc_scale = getenv("OCPPO_TC_TRUNC") ? (float)atof(getenv("OCPPO_TC_TRUNC")) : 1.f;   // calibration knob
     SgemmArgs a = a_in;
     a.dbg = dbg;
+    a.trunc_scale = trunc_scale;
     OCPPO_CHECK_ARG(tc_gemm_supported(mode, a), "tc_gemm: unsupported shape M=%d N=%d K=%lld", a.M, a.N, (long long)a.K);
     const int splits = mode == SGEMM_WGRAD ? a.splits : 1;
     const bool split = a.single_acc == 0;
@@ -940,26 +1050,48 @@ int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
     const int64_t ntiles64 = (int64_t)nt_n * nt_m * splits;
     OCPPO_CHECK_ARG(ntiles64 < (1LL << 31), "tc_gemm: too many tiles");
     const int ntiles = (int)ntiles64;
-    typedef void (*Kern)(SgemmArgs, int, int, int, const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap);
-    static const Kern kerns[5][3] = {
+    typedef void (*Kern)(SgemmArgs, int, int, int, const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap,
+                         const CUtensorMap, const CUtensorMap);
+    constexpr int kVariants = 7;
+    static const Kern kerns[kVariants][3] = {
         {tc_gemm_kernel<SGEMM_FWD, false, 0>, tc_gemm_kernel<SGEMM_DGRAD, false, 0>, tc_gemm_kernel<SGEMM_WGRAD, false, 0>},
         {tc_gemm_kernel<SGEMM_FWD, true, 0>, tc_gemm_kernel<SGEMM_DGRAD, true, 0>, tc_gemm_kernel<SGEMM_WGRAD, true, 0>},
         {tc_gemm_kernel<SGEMM_FWD, true, 1>, tc_gemm_kernel<SGEMM_DGRAD, true, 1>, tc_gemm_kernel<SGEMM_WGRAD, true, 1>},
         {tc_gemm_kernel<SGEMM_FWD, false, 1>, tc_gemm_kernel<SGEMM_DGRAD, false, 1>, tc_gemm_kernel<SGEMM_WGRAD, false, 1>},
-        {tc_gemm_kernel<SGEMM_FWD, true, 2>, tc_gemm_kernel<SGEMM_DGRAD, true, 2>, tc_gemm_kernel<SGEMM_WGRAD, true, 2>}};
+        {tc_gemm_kernel<SGEMM_FWD, true, 2>, tc_gemm_kernel<SGEMM_DGRAD, true, 2>, tc_gemm_kernel<SGEMM_WGRAD, true, 2>},
+        {tc_gemm_kernel<SGEMM_FWD, true, 3>, tc_gemm_kernel<SGEMM_DGRAD, true, 3>, tc_gemm_kernel<SGEMM_WGRAD, true, 3>},
+        {tc_gemm_kernel<SGEMM_FWD, false, 3>, tc_gemm_kernel<SGEMM_DGRAD, false, 3>, tc_gemm_kernel<SGEMM_WGRAD, false, 3>}};
     static int sms = 0;
     if (sms == 0) {
         int dev = 0;
         OCPPO_CUDA(cudaGetDevice(&dev));
         OCPPO_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        for (int i = 0; i < 5; ++i)
+        for (int i = 0; i < kVariants; ++i)
             for (int j = 0; j < 3; ++j)
                 OCPPO_CUDA(cudaFuncSetAttribute(kerns[i][j], cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
     }
     const int grid = 2 * (ntiles < sms / 2 ? ntiles : sms / 2);     // CTA pairs
-    CUtensorMap tmA, tmB, tmC, tmX, tmB2;
-    OCPPO_TRY(make_map(&tmA, a.A, mode == SGEMM_WGRAD, a.M, a.K, a.lda, TM));
-    if (!(a.f16x3 && mode != SGEMM_WGRAD)) { a.b16_hi = nullptr; a.b16_lo = nullptr; }
+    CUtensorMap tmA, tmB, tmC, tmX, tmB2, tmA2, tmC2;
+    // operands that already live in global memory as fp16 hi / lo pairs: both (PRE kernel: no conversion warps), or only
+    // the weights of FWD / DGRAD (the conversion kernel loads them straight into the MMA tiles)
+    if (!a.f16x3) { a.a16_hi = a.a16_lo = a.b16_hi = a.b16_lo = nullptr; a.c16_hi = a.c16_lo = nullptr; }
+    const bool pre = a.a16_hi != nullptr && a.b16_hi != nullptr;
+    if (!pre) {
+        a.a16_hi = a.a16_lo = nullptr;
+        if (mode == SGEMM_WGRAD) { a.b16_hi = nullptr; a.b16_lo = nullptr; }
+        OCPPO_CHECK_ARG(a.A != nullptr && (a.B != nullptr || a.b16_hi != nullptr), "tc_gemm: operand neither fp32 nor pre-split");
+    } else {
+        OCPPO_CHECK_ARG(a.a16_lo != nullptr && (a.lda & 7) == 0 && al16(a.a16_hi) && al16(a.a16_lo), "tc_gemm: bad pre-split A operand");
+        OCPPO_CHECK_ARG(mode != SGEMM_WGRAD || a.bias_part == nullptr, "tc_gemm: the pre-split WGRAD kernel does not form bias sums");
+        OCPPO_CHECK_ARG(mode != SGEMM_WGRAD || a.M % 64 == 0, "tc_gemm: pre-split WGRAD needs M %% 64 == 0");
+    }
+    if (pre) {
+        OCPPO_TRY(make_map16(&tmA, a.a16_hi, mode == SGEMM_WGRAD, a.M, a.K, a.lda, TM));
+        OCPPO_TRY(make_map16(&tmA2, a.a16_lo, mode == SGEMM_WGRAD, a.M, a.K, a.lda, TM));
+    } else {
+        OCPPO_TRY(make_map(&tmA, a.A, mode == SGEMM_WGRAD, a.M, a.K, a.lda, TM));
+        tmA2 = tmA;
+    }
     if (a.b16_hi != nullptr) {
         OCPPO_CHECK_ARG(a.b16_lo != nullptr && (a.ldb & 7) == 0 && al16(a.b16_hi) && al16(a.b16_lo), "tc_gemm: bad pre-split B operand");
         OCPPO_TRY(make_map16(&tmB, a.b16_hi, mode != SGEMM_FWD, a.N, a.K, a.ldb, tn / 2));
@@ -968,13 +1100,28 @@ int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
         OCPPO_TRY(make_map(&tmB, a.B, mode != SGEMM_FWD, a.N, a.K, a.ldb, tn / 2));
         tmB2 = tmB;
     }
-    OCPPO_TRY(make_map_c(&tmC, a.C, (int64_t)a.M * splits, a.N, a.ldc));
-    if (mode == SGEMM_DGRAD) OCPPO_TRY(make_map_c(&tmX, a.mask, a.M, a.N, a.ldc));
+    if (mode == SGEMM_WGRAD) { a.c16_hi = nullptr; a.c16_lo = nullptr; }
+    if (!(pre && mode == SGEMM_DGRAD)) a.colsum_part = nullptr;
+    if (a.c16_hi != nullptr) {
+        OCPPO_CHECK_ARG(a.c16_lo != nullptr && (a.ldc & 7) == 0 && al16(a.c16_hi) && al16(a.c16_lo) && a.bnd_amax != nullptr &&
+                        a.bnd_wl1 != nullptr && a.c_scale_src != nullptr, "tc_gemm: bad fp16-pair output arguments");
+        OCPPO_TRY(make_map_c16(&tmC, a.c16_hi, a.M, a.N, a.ldc));
+        OCPPO_TRY(make_map_c16(&tmC2, a.c16_lo, a.M, a.N, a.ldc));
+    } else {
+        OCPPO_CHECK_ARG(a.C != nullptr, "tc_gemm: no output");
+        OCPPO_TRY(make_map_c(&tmC, a.C, (int64_t)a.M * splits, a.N, a.ldc));
+        tmC2 = tmC;
+    }
+    if (mode == SGEMM_DGRAD && a.mask != nullptr) OCPPO_TRY(make_map_c(&tmX, a.mask, a.M, a.N, a.ldc));
     else tmX = tmC;
+    OCPPO_CHECK_ARG(mode != SGEMM_DGRAD || a.mask != nullptr || a.relu_bits != nullptr, "tc_gemm: DGRAD needs a mask or ReLU decision bits");
     const int mi = mode == SGEMM_FWD ? 0 : (mode == SGEMM_DGRAD ? 1 : 2);
     ProfScope ps(mode == SGEMM_FWD ? KC_SGEMM_FWD : (mode == SGEMM_DGRAD ? KC_SGEMM_DGRAD : KC_SGEMM_WGRAD), 1, stream);
-    OCPPO_CHECK_ARG(!a.f16x3 || (split && a.amax_a != nullptr && a.amax_b != nullptr), "tc_gemm: the FP16x3 engine needs both operands' max-abs");
-    kerns[a.f16x3 ? 4 : (split ? (a.corr_bf16 ? 2 : 1) : (a.corr_bf16 ? 3 : 0))][mi]<<<grid, kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles, tmA, tmB, tmC, tmX, tmB2);
+    OCPPO_CHECK_ARG(!a.f16x3 || ((split || pre) && a.amax_a != nullptr && a.amax_b != nullptr), "tc_gemm: the FP16x3 engine needs both operands' max-abs");
+    // fp16-pair storage with one accumulator (engine 8): FWD / DGRAD overlap their epilogue with the next tile's mainloop;
+    // WGRAD drains only every 128 stages and keeps the split accumulators' 3x smaller rounding error
+    const int variant = a.f16x3 ? (pre ? ((split || mode == SGEMM_WGRAD) ? 5 : 6) : 4) : (split ? (a.corr_bf16 ? 2 : 1) : (a.corr_bf16 ? 3 : 0));
+    kerns[variant][mi]<<<grid, pre ? kProdTid0 : kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles, tmA, tmB, tmC, tmX, tmB2, tmA2, tmC2);
     OCPPO_LAUNCH_CHECK("tc_gemm_kernel");
     return OCPPO_OK;
 }

@@ -27,12 +27,12 @@ def dev(built_lib):
     return torch.device("cuda:0")
 
 
-@pytest.fixture(params=["fma", "tc", "tc16", "f16"])
+@pytest.fixture(params=["fma", "tc", "tc16", "f16", "f16p", "f16p1"])
 def gemm_engine(request, built_lib):
     """Runs the test once per trunk GEMM engine: fp32 CUDA-core FMA, tcgen05 3xTF32, tcgen05 TF32 + BF16 corrections."""
     default = built_lib.ocppo_get_gemm_mode()
-    assert built_lib.ocppo_set_gemm_mode({"fma": 0, "tc": 1, "tc16": 3, "f16": 5}[request.param]) == 0
-    yield "tc" if request.param in ("tc16", "f16") else request.param
+    assert built_lib.ocppo_set_gemm_mode({"fma": 0, "tc": 1, "tc16": 3, "f16": 5, "f16p": 6, "f16p1": 8}[request.param]) == 0
+    yield "tc" if request.param in ("tc16", "f16", "f16p", "f16p1") else request.param
     built_lib.ocppo_set_gemm_mode(default)
 
 
