@@ -55,10 +55,11 @@ def parse():
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--gae-sweep", default="4096,16384,65536")
-    p.add_argument("--gemm", default="tc", choices=["fma", "tc", "tc-pair", "tc-pair1", "tc-bf16", "tc-3xtf32", "tc-fast"],
-                   help="trunk GEMM engine: fp32 CUDA-core FMA | tcgen05, three FP16 passes on power-of-two scaled operands "
-                        "(library default) | tcgen05 TF32 main product + two BF16 correction products | tcgen05 3xTF32 | "
-                        "as tc-bf16 with one double-buffered accumulator (2x the rounding)")
+    p.add_argument("--gemm", default="tc", choices=["fma", "tc", "tc-pair2", "tc-f32", "tc-bf16", "tc-3xtf32", "tc-fast"],
+                   help="trunk GEMM engine: fp32 CUDA-core FMA | tcgen05, three FP16 passes on operands stored as fp16 (hi, lo) "
+                        "pairs, one double-buffered accumulator for FWD / DGRAD (library default) | the same with split "
+                        "accumulators everywhere | three FP16 passes on fp32-stored operands (in-kernel conversion) | TF32 main "
+                        "product + two BF16 correction products | 3xTF32 | as tc-bf16 with one accumulator")
     return p.parse_args()
 
 
@@ -305,7 +306,7 @@ def run_b200(a):
     torch.cuda.set_device(dev)
     ocd.init_process_group(world, "nccl")
     lib = _abi.lib()
-    assert lib.ocppo_set_gemm_mode({"fma": 0, "tc": 5, "tc-pair": 6, "tc-pair1": 8, "tc-bf16": 3, "tc-3xtf32": 1, "tc-fast": 4}[a.gemm]) == 0
+    assert lib.ocppo_set_gemm_mode({"fma": 0, "tc": 8, "tc-pair2": 6, "tc-f32": 5, "tc-bf16": 3, "tc-3xtf32": 1, "tc-fast": 4}[a.gemm]) == 0
     D, A = GAME_SHAPES[a.game]
     T, N = a.num_steps, a.num_envs
     pk = peaks()
@@ -408,7 +409,9 @@ def run_b200(a):
     roofline = {"bound": "tensor", "achieved": gemm_tflops, "peak": pk["bf16_sustained"], "unit": "TFLOP/s",
                 "frac": gemm_tflops / pk["bf16_sustained"], "traffic": TRAFFIC_BYTES_PER_LAUNCH if tc else None,
                 "kernel": ("tc_gemm_kernel<FWD|DGRAD|WGRAD> (tcgen05.mma cta_group::2: " +
-                           {"tc": "three FP16 products (hi.hi + hi.lo + lo.hi) on power-of-two scaled operands",
+                           {"tc": "three FP16 products (hi.hi + hi.lo + lo.hi) on operands stored in HBM as power-of-two scaled fp16 (hi, lo) pairs, conversion-free six-stage pipeline",
+                            "tc-pair2": "three FP16 products on fp16-pair stored operands, split accumulators",
+                            "tc-f32": "three FP16 products on fp32-stored operands converted in the kernel",
                             "tc-bf16": "TF32 main product + two BF16 correction products",
                             "tc-fast": "TF32 main product + two BF16 correction products, one accumulator",
                             "tc-3xtf32": "TF32 main product + two TF32 correction products"}.get(a.gemm, "") +
@@ -421,10 +424,10 @@ def run_b200(a):
                 "achieved_is": "ALGORITHMIC fp32-equivalent FLOPs (2*M*N*K per GEMM, SURVEY 8d) / CUDA-event time of the GEMM launches"}
     if tc:
         # bf16-equivalent MMA work issued per algorithmic MAC: a TF32 pass costs 2 (half the bf16 rate), a BF16 pass 1
-        units = {"tc": 3.0, "tc-pair": 3.0, "tc-pair1": 3.0, "tc-bf16": 4.0, "tc-fast": 4.0}.get(a.gemm, 6.0)
+        units = {"tc": 3.0, "tc-pair2": 3.0, "tc-f32": 3.0, "tc-bf16": 4.0, "tc-fast": 4.0}.get(a.gemm, 6.0)
         roofline["tensor_pipe"] = {"bf16_equivalent_tflops_issued": units * gemm_tflops, "peak": pk["bf16_sustained"],
                                    "frac_of_peak": units * gemm_tflops / pk["bf16_sustained"],
-                                   "note": (("fp32-grade accuracy costs three FP16 passes (hi.hi, hi.lo, lo.hi)" if a.gemm in ("tc", "tc-pair", "tc-pair1") else
+                                   "note": (("fp32-grade accuracy costs three FP16 passes (hi.hi, hi.lo, lo.hi)" if a.gemm in ("tc", "tc-pair2", "tc-f32") else
                                              "fp32-grade accuracy costs one TF32 pass (2 bf16-equivalents) plus " +
                                              ("two BF16 correction passes" if a.gemm in ("tc-bf16", "tc-fast") else "two TF32 correction passes")) +
                                             f": {units:.0f} bf16-equivalent MACs per algorithmic MAC, so frac = achieved/peak is "
@@ -449,7 +452,7 @@ def run_b200(a):
     # rollout inference over the same sweep (BASELINE configs[4]); the trunk is 11.55 MFLOP per observation against
     # 116 bytes in and out, so it is held to the tensor roofline like the update, not to HBM
     inference = []
-    units = {"tc": 3.0, "tc-pair": 3.0, "tc-pair1": 3.0, "tc-bf16": 4.0, "tc-fast": 4.0}.get(a.gemm, 6.0) if tc else None
+    units = {"tc": 3.0, "tc-pair2": 3.0, "tc-f32": 3.0, "tc-bf16": 4.0, "tc-fast": 4.0}.get(a.gemm, 6.0) if tc else None
     for n in [int(x) for x in a.gae_sweep.split(",") if x]:
         ms = time_policy_step(agent, dev, D, n)
         tf = 2.0 * trunk_macs(D) * n / (ms * 1e-3) / 1e12

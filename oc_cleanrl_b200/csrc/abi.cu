@@ -296,6 +296,23 @@ static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_
                     OCPPO_TRY(ensure_act_amax(h, l - 1, B, s));
                     a.amax_a = h->amax + kAmaxAct + l - 1;
                 }
+                if (pre16 && !tc && l + 1 < h->n_layers && pair_ok(h, l, B) && L.out_dim % 128 == 0) {
+                    // an FMA layer (the K = frames x features first layer) feeding a tensor-core one: its epilogue writes the
+                    // fp16 pair and the ReLU decision bits itself, and no fp32 copy of the activation exists
+                    SgemmArgs n{};
+                    fwd_args(h, l + 1, B, h->act[l], &n);
+                    if (sgemm_uses_tc(SGEMM_FWD, n)) {
+                        if (l == 0) OCPPO_TRY(launch_absmax(x, B * L.row_mult, L.in_dim, L.in_dim, h->amax + kAmaxObs, h->sm_count, s));
+                        else OCPPO_TRY(ensure_act_amax(h, l - 1, B, s));
+                        a.c16_hi = h->act16_hi[l]; a.c16_lo = h->act16_lo[l];
+                        a.bnd_amax = l == 0 ? h->amax + kAmaxObs : h->amax + kAmaxAct + l - 1;
+                        a.bnd_wl1 = h->amax + kWRowL1 + l; a.bnd_bmax = h->amax + kBMax + l;
+                        a.c_scale_src = h->amax + kBndAct + l;
+                        a.fma_bits = a.relu_bits != nullptr;
+                        h->relu_bits_valid[l] = a.relu_bits != nullptr;
+                        pair_out = true;
+                    }
+                }
             }
         }
         OCPPO_TRY(sgemm_launch(SGEMM_FWD, a, s));

@@ -128,7 +128,8 @@ struct ocppo_handle {
 constexpr int kAmaxAct = 2, kAmaxW = 2 + 2 * OCPPO_MAX_LAYERS, kAmaxGrad = 2 + 4 * OCPPO_MAX_LAYERS;
 constexpr int kBndAct = 2 + 6 * OCPPO_MAX_LAYERS, kBndGrad = 2 + 8 * OCPPO_MAX_LAYERS;
 constexpr int kWRowL1 = 2 + 10 * OCPPO_MAX_LAYERS, kWColL1 = 2 + 12 * OCPPO_MAX_LAYERS, kBMax = 2 + 14 * OCPPO_MAX_LAYERS;
-constexpr int kAmaxSlots = 2 + 16 * OCPPO_MAX_LAYERS;
+constexpr int kAmaxObs = 2 + 16 * OCPPO_MAX_LAYERS;           // max |observation| of the current chunk
+constexpr int kAmaxSlots = 4 + 16 * OCPPO_MAX_LAYERS;
 
 namespace ocppo {
 
@@ -167,6 +168,7 @@ struct SgemmArgs {
     const float *bnd_wl1;          //   weights) + *bnd_bmax (largest |bias|, may be null);
     const float *bnd_bmax;
     float *c_scale_src;            //   the kernel stores the bound here: the consumers' amax_a / amax_b
+    int fma_bits;                  // FMA kernel, FWD: write relu_bits too (full 128-column tiles only)
     float *colsum_part;            // DGRAD, conversion-free kernel: [tc_gemm_ctas() * 4, N] column sums of C, pre-zeroed
 };
 

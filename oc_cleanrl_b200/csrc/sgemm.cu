@@ -139,10 +139,39 @@ __global__ void __launch_bounds__(kThreads, 2) sgemm_kernel(SgemmArgs p) {
     float *C = p.C;
     if (MODE == SGEMM_WGRAD) C += (int64_t)split * p.M * p.N;
     const bool c_vec = ((p.N & 3) == 0) && ((p.ldc & 3) == 0);
+    // fp16-pair storage (engine 6 / 8; the launcher only asks for it on full 128-column tiles): the FWD output leaves as
+    // (hi, lo) fp16 scaled by its a-priori bound plus one ReLU decision bit per element, and no fp32 copy is written
+    const bool pair = (MODE == SGEMM_FWD) && p.c16_hi != nullptr;
+    const bool bits_out = (MODE == SGEMM_FWD) && p.relu_bits != nullptr && p.fma_bits;
+    float scale_c = 1.f;
+    if (pair) {
+        const float bound = __ldg(p.bnd_amax) * __ldg(p.bnd_wl1) + (p.bnd_bmax != nullptr ? __ldg(p.bnd_bmax) : 0.f);
+        float inv_c;
+        f16_scale_of(bound, scale_c, inv_c);
+        if (blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) *p.c_scale_src = bound;
+    }
     float run_max = 0.f;                  // max |C| of this thread's stores (p.amax_out: the consumer's FP16 scale)
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         const int m = m0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
+        if (bits_out) {
+            // the 8 threads tx = 8 w .. 8 w + 7 of a row hold the 32 columns of one word: OR their nibbles together
+            // (all lanes take part; rows / columns past the edge contribute zeros and store nothing)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int n = n0 + h * 64 + tx * 4;
+                uint32_t word = 0;
+                if (m < p.M && n < p.N) {
+                    const float4 bb = *reinterpret_cast<const float4 *>(p.bias + n);
+                    word = ((acc[i][h * 4 + 0] + bb.x > 0.f ? 1u : 0u) | (acc[i][h * 4 + 1] + bb.y > 0.f ? 2u : 0u) |
+                            (acc[i][h * 4 + 2] + bb.z > 0.f ? 4u : 0u) | (acc[i][h * 4 + 3] + bb.w > 0.f ? 8u : 0u)) << (4 * (tx & 7));
+                }
+                word |= __shfl_xor_sync(0xffffffffu, word, 1);
+                word |= __shfl_xor_sync(0xffffffffu, word, 2);
+                word |= __shfl_xor_sync(0xffffffffu, word, 4);
+                if ((tx & 7) == 0 && m < p.M && n < p.N) p.relu_bits[(int64_t)m * (p.N >> 5) + (n >> 5)] = word;
+            }
+        }
         if (m >= p.M) continue;
         if (MODE == SGEMM_WGRAD && do_bias) p.bias_part[(int64_t)split * p.M + m] = bsum[i];
 #pragma unroll
@@ -156,6 +185,16 @@ __global__ void __launch_bounds__(kThreads, 2) sgemm_kernel(SgemmArgs p) {
                     const float4 bb = *reinterpret_cast<const float4 *>(p.bias + n);
                     v[0] = fmaxf(v[0] + bb.x, 0.f); v[1] = fmaxf(v[1] + bb.y, 0.f);
                     v[2] = fmaxf(v[2] + bb.z, 0.f); v[3] = fmaxf(v[3] + bb.w, 0.f);
+                    if (pair) {
+                        uint32_t h0, l0, h1, l1;
+                        split_f16x2(v[0], v[1], scale_c, h0, l0);
+                        split_f16x2(v[2], v[3], scale_c, h1, l1);
+                        const int64_t e = (int64_t)m * p.ldc + n;          // element offset; 8-byte aligned as fp16
+                        *reinterpret_cast<uint2 *>(reinterpret_cast<uint16_t *>(p.c16_hi) + e) = make_uint2(h0, h1);
+                        *reinterpret_cast<uint2 *>(reinterpret_cast<uint16_t *>(p.c16_lo) + e) = make_uint2(l0, l1);
+                        run_max = fmaxf(fmaxf(run_max, fmaxf(fabsf(v[0]), fabsf(v[1]))), fmaxf(fabsf(v[2]), fabsf(v[3])));
+                        continue;
+                    }
                 } else if (MODE == SGEMM_DGRAD) {
                     const float4 mk = *reinterpret_cast<const float4 *>(p.mask + (int64_t)m * p.ldc + n);
                     v[0] = mk.x > 0.f ? v[0] : 0.f; v[1] = mk.y > 0.f ? v[1] : 0.f;
@@ -197,7 +236,7 @@ int dispatch(const SgemmArgs &a, bool av, bool bv, dim3 grid, cudaStream_t s) {
 
 }  // namespace
 
-int g_gemm_mode = 5;   // tcgen05: three FP16 passes on power-of-two scaled operands; see ocppo_set_gemm_mode
+int g_gemm_mode = 8;   // tcgen05: three FP16 passes on fp16-pair stored operands, one accumulator; see ocppo_set_gemm_mode
 
 static int tc_ops_mask() {
     static const int ops_mask = getenv("OCPPO_TC_OPS") ? atoi(getenv("OCPPO_TC_OPS")) : 7;   // bring-up: bit per op

@@ -1120,7 +1120,7 @@ int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
     OCPPO_CHECK_ARG(!a.f16x3 || ((split || pre) && a.amax_a != nullptr && a.amax_b != nullptr), "tc_gemm: the FP16x3 engine needs both operands' max-abs");
     // fp16-pair storage with one accumulator (engine 8): FWD / DGRAD overlap their epilogue with the next tile's mainloop;
     // WGRAD drains only every 128 stages and keeps the split accumulators' 3x smaller rounding error
-    const int variant = a.f16x3 ? (pre ? ((split || mode == SGEMM_WGRAD) ? 5 : 6) : 4) : (split ? (a.corr_bf16 ? 2 : 1) : (a.corr_bf16 ? 3 : 0));
+    const int variant = a.f16x3 ? (pre ? ((split || (mode == SGEMM_WGRAD && !(dbg & 256))) ? 5 : 6) : 4) : (split ? (a.corr_bf16 ? 2 : 1) : (a.corr_bf16 ? 3 : 0));
     kerns[variant][mi]<<<grid, pre ? kProdTid0 : kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles, tmA, tmB, tmC, tmX, tmB2, tmA2, tmC2);
     OCPPO_LAUNCH_CHECK("tc_gemm_kernel");
     return OCPPO_OK;
