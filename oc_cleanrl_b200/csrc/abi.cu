@@ -440,7 +440,15 @@ static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, i
         OCPPO_CHECK_ARG(!db_done || pre_w, "layer %d: bias gradient formed twice", l);
         if ((pre_w || pre_d) && !dy16) {        // the loss head's (or an FMA layer's) fp32 gradient, split once for both GEMMs
             dy_scale = amax_dy;
-            OCPPO_TRY(launch_split16(dY, rows * L.out_dim, dy_scale, h->g16_hi[cur], h->g16_lo[cur], h->sm_count, s));
+            if (pre_w && !db_done && L.out_dim % 4 == 0) {      // ... and the bias gradient falls out of the same read
+                int blocks = 0;
+                OCPPO_TRY(launch_split16_colsum(dY, rows, L.out_dim, dy_scale, h->g16_hi[cur], h->g16_lo[cur], h->colsum_part, &blocks,
+                                                h->sm_count, s));
+                OCPPO_TRY(launch_colsum_reduce(h->colsum_part, blocks, L.out_dim, h->grads + L.b_off, accumulate, s));
+                db_done = true;
+            } else {
+                OCPPO_TRY(launch_split16(dY, rows * L.out_dim, dy_scale, h->g16_hi[cur], h->g16_lo[cur], h->sm_count, s));
+            }
             dy16 = true;
         }
         if ((!pre_w || (l > 0 && !pre_d)) && !dy32) {

@@ -223,6 +223,8 @@ int launch_split16(const float *x, int64_t n, const float *scale_src, void *hi, 
 int launch_merge16(const void *hi, const void *lo, int64_t n, const float *scale_src, float *out, int sm_count, cudaStream_t stream);
 int launch_colsum16(const void *hi, const void *lo, int64_t rows, int cols, const float *scale_src, float *part, int *blocks,
                     int sm_count, cudaStream_t stream);     // part: [kColsumBlocksMax][cols] at most; *blocks partial rows written
+int launch_split16_colsum(const float *x, int64_t rows, int cols, const float *scale_src, void *hi, void *lo, float *part, int *blocks,
+                          int sm_count, cudaStream_t stream);   // pair + column-sum partials of an fp32 tensor in one read
 int launch_colsum_reduce(const float *part, int parts, int cols, float *out, int accumulate, cudaStream_t stream);
 int launch_wnorm(const WnormSegs &segs, cudaStream_t stream);                     // outputs pre-zeroed
 int launch_absmax_multi(const AbsmaxSegs &segs, cudaStream_t stream);             // several small contiguous tensors, one launch; outs pre-zeroed

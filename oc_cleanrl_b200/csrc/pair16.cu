@@ -78,6 +78,46 @@ __global__ void __launch_bounds__(256) colsum16_kernel(const uint2 *__restrict__
     }
 }
 
+// the loss head's fp32 gradient [rows, cols]: pair AND column-sum partials in one read (same slab / order rules as above)
+__global__ void __launch_bounds__(256) split16_colsum_kernel(const float4 *__restrict__ x, int64_t rows, int cols, int64_t rows_per_block,
+                                                             const float *__restrict__ scale_src, uint2 *__restrict__ hi,
+                                                             uint2 *__restrict__ lo, float *__restrict__ part) {
+    float scale, inv;
+    f16_scale_of(__ldg(scale_src), scale, inv);
+    const int cq = cols >> 2;
+    const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+    const int64_t r1 = r0 + rows_per_block < rows ? r0 + rows_per_block : rows;
+    __shared__ float4 red[256];
+    for (int c0 = 0; c0 < cq; c0 += 256) {
+        const int lanes = cq - c0 < 256 ? cq - c0 : 256;
+        const int rstep = 256 / lanes > 0 ? 256 / lanes : 1;
+        const int cg = threadIdx.x % lanes, rl = threadIdx.x / lanes;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (rl < rstep)
+            for (int64_t r = r0 + rl; r < r1; r += rstep) {
+                const int64_t i = r * cq + c0 + cg;
+                const float4 v = __ldcs(x + i);
+                uint32_t h0, l0, h1, l1;
+                split_f16x2(v.x, v.y, scale, h0, l0);
+                split_f16x2(v.z, v.w, scale, h1, l1);
+                hi[i] = make_uint2(h0, h1);
+                lo[i] = make_uint2(l0, l1);
+                acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+            }
+        red[threadIdx.x] = acc;
+        __syncthreads();
+        if (threadIdx.x < lanes) {
+            float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int k = 0; k < rstep; ++k) {
+                const float4 v = red[k * lanes + threadIdx.x];
+                s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+            }
+            reinterpret_cast<float4 *>(part + (int64_t)blockIdx.x * cols)[c0 + threadIdx.x] = s;
+        }
+        __syncthreads();
+    }
+}
+
 // per weight matrix W[out, in] (+ bias[out]): largest row L1 norm, largest column L1 norm, largest |bias| as float bits
 // (atomicMax on pre-zeroed slots).  grid (slices, matrices)
 __global__ void __launch_bounds__(256) wnorm_kernel(WnormSegs segs) {
@@ -86,18 +126,36 @@ __global__ void __launch_bounds__(256) wnorm_kernel(WnormSegs segs) {
     const int out = segs.out_dim[m], in = segs.in_dim[m];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float rmax = 0.f;
-    for (int j = blockIdx.x * 8 + warp; j < out; j += gridDim.x * 8) {
+    for (int j = blockIdx.x * 8 + warp; j < out; j += gridDim.x * 8) {          // warp per row
         float s = 0.f;
         for (int k = lane; k < in; k += 32) s += fabsf(__ldg(W + (int64_t)j * in + k));
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
         rmax = fmaxf(rmax, s);
     }
+    // columns: block = 32 columns at a time, warp w adds rows w, w + 8, ..., the 8 partial sums fold in order
+    __shared__ float red[8][33];
     float cmax = 0.f;
-    for (int k = blockIdx.x * 256 + threadIdx.x; k < in; k += gridDim.x * 256) {
-        float s = 0.f;
-        for (int j = 0; j < out; ++j) s += fabsf(__ldg(W + (int64_t)j * in + k));
-        cmax = fmaxf(cmax, s);
+    for (int k0 = blockIdx.x * 32; k0 < in; k0 += gridDim.x * 32) {
+        const int k = k0 + lane;
+        float s0 = 0.f, s1 = 0.f;
+        if (k < in) {
+            int j = warp;
+            for (; j + 8 < out; j += 16) {
+                s0 += fabsf(__ldg(W + (int64_t)j * in + k));
+                s1 += fabsf(__ldg(W + (int64_t)(j + 8) * in + k));
+            }
+            if (j < out) s0 += fabsf(__ldg(W + (int64_t)j * in + k));
+        }
+        red[warp][lane] = s0 + s1;
+        __syncthreads();
+        if (warp == 0) {
+            float s = 0.f;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) s += red[w][lane];
+            cmax = fmaxf(cmax, s);
+        }
+        __syncthreads();
     }
     float bmax = 0.f;
     if (blockIdx.x == 0 && segs.b[m] != nullptr)
@@ -114,29 +172,29 @@ __global__ void __launch_bounds__(256) wnorm_kernel(WnormSegs segs) {
     }
 }
 
-// out[c] (+)= sum over p of part[p][c]: block = 32 columns, warp w adds rows w, w + 8, ... in order, then the 8 warps fold in
-// order -- a fixed summation tree whatever the launch looks like
-__global__ void __launch_bounds__(256) colsum_reduce_kernel(const float *__restrict__ part, int parts, int cols, float *__restrict__ out,
+// out[c] (+)= sum over p of part[p][c]: block = 32 columns, warp w adds rows w, w + 32, ... in order, then the 32 warps fold
+// in order -- a fixed summation tree whatever the launch looks like
+__global__ void __launch_bounds__(1024) colsum_reduce_kernel(const float *__restrict__ part, int parts, int cols, float *__restrict__ out,
                                                             int accumulate) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, c = blockIdx.x * 32 + lane;
     float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
     if (c < cols) {
         int r = warp;
-        for (; r + 24 < parts; r += 32) {
+        for (; r + 96 < parts; r += 128) {
             s0 += __ldg(part + (int64_t)r * cols + c);
-            s1 += __ldg(part + (int64_t)(r + 8) * cols + c);
-            s2 += __ldg(part + (int64_t)(r + 16) * cols + c);
-            s3 += __ldg(part + (int64_t)(r + 24) * cols + c);
+            s1 += __ldg(part + (int64_t)(r + 32) * cols + c);
+            s2 += __ldg(part + (int64_t)(r + 64) * cols + c);
+            s3 += __ldg(part + (int64_t)(r + 96) * cols + c);
         }
-        for (; r < parts; r += 8) s0 += __ldg(part + (int64_t)r * cols + c);
+        for (; r < parts; r += 32) s0 += __ldg(part + (int64_t)r * cols + c);
     }
-    __shared__ float red[8][33];
+    __shared__ float red[32][33];
     red[warp][lane] = (s0 + s1) + (s2 + s3);
     __syncthreads();
     if (warp == 0 && c < cols) {
         float s = 0.f;
 #pragma unroll
-        for (int w = 0; w < 8; ++w) s += red[w][lane];
+        for (int w = 0; w < 32; ++w) s += red[w][lane];
         out[c] = accumulate ? out[c] + s : s;
     }
 }
@@ -190,10 +248,24 @@ int launch_colsum16(const void *hi, const void *lo, int64_t rows, int cols, cons
     return OCPPO_OK;
 }
 
+int launch_split16_colsum(const float *x, int64_t rows, int cols, const float *scale_src, void *hi, void *lo, float *part, int *blocks,
+                          int sm_count, cudaStream_t stream) {
+    OCPPO_CHECK_ARG(x && hi && lo && scale_src && part && blocks && rows >= 1 && cols >= 4 && cols % 4 == 0 && (((uintptr_t)x) & 15) == 0,
+                    "split16_colsum: bad arguments");
+    const int g = colsum16_blocks(rows, sm_count);
+    const int64_t rpb = ceil_div(rows, g);
+    *blocks = (int)ceil_div(rows, rpb);
+    ProfScope ps(KC_AUX, 1, stream);
+    split16_colsum_kernel<<<*blocks, 256, 0, stream>>>(reinterpret_cast<const float4 *>(x), rows, cols, rpb, scale_src,
+                                                       reinterpret_cast<uint2 *>(hi), reinterpret_cast<uint2 *>(lo), part);
+    OCPPO_LAUNCH_CHECK("split16_colsum_kernel");
+    return OCPPO_OK;
+}
+
 int launch_colsum_reduce(const float *part, int parts, int cols, float *out, int accumulate, cudaStream_t stream) {
     OCPPO_CHECK_ARG(part && out && parts >= 1 && cols >= 1, "colsum_reduce: bad arguments");
     ProfScope ps(KC_AUX, 1, stream);
-    colsum_reduce_kernel<<<(unsigned)ceil_div(cols, 32), 256, 0, stream>>>(part, parts, cols, out, accumulate);
+    colsum_reduce_kernel<<<(unsigned)ceil_div(cols, 32), 1024, 0, stream>>>(part, parts, cols, out, accumulate);
     OCPPO_LAUNCH_CHECK("colsum_reduce_kernel");
     return OCPPO_OK;
 }
@@ -201,7 +273,7 @@ int launch_colsum_reduce(const float *part, int parts, int cols, float *out, int
 int launch_wnorm(const WnormSegs &segs, cudaStream_t stream) {
     if (segs.count <= 0) return OCPPO_OK;
     ProfScope ps(KC_AUX, 1, stream);
-    wnorm_kernel<<<dim3(16, (unsigned)segs.count), 256, 0, stream>>>(segs);
+    wnorm_kernel<<<dim3(32, (unsigned)segs.count), 256, 0, stream>>>(segs);
     OCPPO_LAUNCH_CHECK("wnorm_kernel");
     return OCPPO_OK;
 }
