@@ -91,7 +91,7 @@ int ocppo_profile_read(double *ms_by_class, int64_t *timed_by_class, int32_t n_c
 int ocppo_measure_fma_peak(double *tflops, void *stream);
 
 /* ---- GEMM engine selection + raw GEMM (tests / measurement) -------------- */
-/* The trunk GEMMs (nn.Linear forward, dgrad, wgrad of architectures/ppo.py:70-84) run on one of six engines
+/* The trunk GEMMs (nn.Linear forward, dgrad, wgrad of architectures/ppo.py:70-84) run on one of eight engines
  * (process-wide switch; shapes outside the 256x256x32 CTA-pair tile grid always use engine 0):
  *   0  fp32 CUDA-core FMA kernels (exact fp32 products);
  *   1  tcgen05 tensor cores, 3xTF32: x = hi + lo, hi.hi + hi.lo + lo.hi, fp32 accumulate in TMEM, main and correction
@@ -100,23 +100,33 @@ int ocppo_measure_fma_peak(double *tflops, void *stream);
  *   3  as 1, but the two correction products run as BF16 MMAs at twice the TF32 rate:
  *      trunc_tf32(a).trunc_tf32(b) + bf16(a - trunc_tf32(a)).bf16(b) + bf16(a).bf16(b - trunc_tf32(b));
  *   4  as 3 with a single, double-buffered accumulator (fastest of 1-4; misses the 1e-4 bar at the full minibatch);
- *   5  (default) three FP16 passes: each operand tensor is scaled by the power of two that puts its largest magnitude
+ *   5  three FP16 passes: each operand tensor is scaled by the power of two that puts its largest magnitude
  *      in [2^14, 2^15) (exact), split x s = h + l with h = fp16(x s), l = fp16(x s - h), and the product is
  *      h.h + (h.l + l.h) in two TMEM accumulators, unscaled by the epilogue.  Same 11 significant bits per part as
  *      TF32 at the BF16 rate (3 instead of 4 BF16-equivalent passes), per-product error 2^-22.  The max-abs of every
  *      operand is a device scalar: tracked by the epilogue of the GEMM that produced the tensor, measured once per call
  *      for the weights (which are also split once per call and TMA-loaded as FP16 tiles), one reduction pass otherwise.
  *      Elements below 2^-29 of their tensor's maximum keep an absolute, not a relative, accuracy (2^-40 of the maximum).
- * Measured error of one GEMM on the trunk shapes, relative to the result's max-norm (tools/gemm_diag.py): engine 5
- * 0.2e-6 .. 1.2e-6, engine 3 1.3e-6 .. 2.4e-6 (4e-6 / 5e-6 for a 65,536-row weight gradient); every parity test holds
- * each engine to the same 1e-4 bar. */
+ *   6  engine 5's arithmetic on fp16-PAIR STORAGE: every activation and every gradient that flows between two trunk GEMMs
+ *      lives in global memory as (hi, lo) fp16 tensors -- written directly by the epilogue of the GEMM (or FMA layer) that
+ *      produces it, scaled by the power of two of an a-priori bound (max|input| x largest row / column L1 norm of the
+ *      weights + max|bias|, all device scalars) -- and is TMA-loaded straight into the MMA tiles by a conversion-free,
+ *      six-stage kernel.  Same bytes as fp32 storage, no fp32 copy is written; bias gradients come out of the DGRAD
+ *      epilogue (column sums); the loss head's fp32 gradient is split (and column-summed) in one extra pass;
+ *   8  (default) as 6 with ONE 256-column accumulator per tile for FWD / DGRAD, double-buffered in TMEM so the epilogue of
+ *      a tile overlaps the mainloop of the next (WGRAD keeps the split accumulators).  (7 is reserved: the test hook's
+ *      "pair output" variant of ocppo_gemm.)
+ * Measured error of one GEMM on the trunk shapes, relative to the result's max-norm (tools/acc.sh, zero-mean operands):
+ * engines 5 / 6 0.7e-6 .. 0.9e-6 (FWD, DGRAD) and 2.5e-6 (65,536-row weight gradient), engine 8 1.3e-6 .. 2.3e-6 and 2.5e-6,
+ * engine 3 1.3e-6 .. 2.4e-6 (4e-6 / 5e-6 for the weight gradient); every parity test holds each engine to the same 1e-4 bar. */
 int ocppo_set_gemm_mode(int32_t mode);
 int ocppo_get_gemm_mode(void);
 /* One GEMM of the family.  op 0: C[M,N] = relu(A[M,K] B[N,K]^T + bias[N]);
  * op 1: C[M,N] = (mask[M,N] > 0) * (A[M,K] B[K,N]);
  * op 2: C[s][M,N] = sum over rows k of split s of A[k,M]^T B[k,N] (+ bias_part[s][M]
- * = column sums of A).  engine as above (1-5: the shape must be supported by the tensor-core kernel; engine 5 measures
- * the operand maxima itself, synchronously -- this is a test hook). */
+ * = column sums of A).  engine as above (1-8: the shape must be supported by the tensor-core kernel; engines 5-8 measure
+ * the operand maxima themselves, 6-8 also split contiguous operands into transient fp16 pairs, 7 writes C as a pair scaled
+ * by its bound and merges it back -- all synchronously: this is a test hook). */
 int ocppo_gemm(int32_t op, int32_t engine, int32_t M, int32_t N, int64_t K, const float *A, int64_t lda,
                const float *B, int64_t ldb, float *C, int64_t ldc, const float *bias, const float *mask,
                float *bias_part, int32_t splits, int64_t k_per_split, void *stream);
