@@ -169,6 +169,13 @@ int ocppo_policy_step(ocppo_handle *h, const float *obs, int64_t B, uint64_t see
                       float *logp, float *entropy, float *value, void *stream);
 /* PPObj.get_value(x), architectures/ppo.py:86-87 (ppo_atari_oc.py:534). */
 int ocppo_value(ocppo_handle *h, const float *obs, int64_t B, float *value, void *stream);
+/* Optional promise that lets forward calls skip the per-call weight preparation of the FP16 engines (max-abs, fp16 split,
+ * L1 norms: three small launches): `version` is any counter the caller bumps whenever it writes the parameter arena
+ * (the host side passes the sum of torch's version counters of the parameters, which every in-place op increments).
+ * Equal to the last value = unchanged; a negative value withdraws the promise.  Optimizer steps taken through
+ * ocppo_clip_adam and ocppo_bind_arena invalidate the preparation by themselves.  (The rollout loop of
+ * ppo_atari_oc.py:500-514 calls the policy 128 times per iteration on unchanged weights.) */
+int ocppo_weights_version(ocppo_handle *h, int64_t version);
 /* torch.distributions.Categorical(logits=...) on given logits (B,A):
  * sample / log_prob / entropy (architectures/ppo.py:92-95). */
 int ocppo_categorical(const float *logits, int64_t B, int32_t A, uint64_t seed,

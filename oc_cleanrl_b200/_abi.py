@@ -71,6 +71,7 @@ _SIGNATURES = {
     "ocppo_bind_workspace": (C.c_int, [_P, _P, _I64, _I64, _I32]),
     "ocppo_policy_step": (C.c_int, [_P, _P, _I64, _U64, _U64, _P, _P, _P, _P, _P, _P]),
     "ocppo_value": (C.c_int, [_P, _P, _I64, _P, _P]),
+    "ocppo_weights_version": (C.c_int, [_P, _I64]),
     "ocppo_categorical": (C.c_int, [_P, _I64, _I32, _U64, _U64, _P, _P, _P, _P, _P]),
     "ocppo_philox_increment": (_U64, [_I64, _I32, _I32]),
     "ocppo_exponential": (C.c_int, [_P, _I64, _U64, _U64, _P]),

@@ -21,6 +21,8 @@ from __future__ import annotations
 import ctypes as C
 
 import numpy as np
+import os
+
 import torch
 import torch.nn as nn
 from torch.distributions.categorical import Categorical
@@ -36,6 +38,7 @@ class _TrunkFunction(torch.autograd.Function):
     def forward(ctx, agent, x, *params):
         B = x.shape[0]
         agent._ensure_workspace(B, training=True)
+        agent._hint_weights()
         hidden = torch.empty((B, agent._hidden), dtype=torch.float32, device=x.device)
         _abi.check(_abi.lib().ocppo_trunk_forward(agent._handle.raw, _abi.ptr(x), B, _abi.ptr(hidden),
                                                  agent._stream()))
@@ -94,6 +97,7 @@ class PPObj(Predictor):
         self._ws_rows = 0
         self._ws_training = False
         self._fwd_version = 0
+        self._manual_version = 0
 
     # ---- arena management ---------------------------------------------------
     def _apply(self, fn, *args, **kwargs):
@@ -188,12 +192,30 @@ class PPObj(Predictor):
         trunk = list(self.parameters())[: self._n_trunk_tensors]
         return _TrunkFunction.apply(self, x, *trunk)
 
+    def _hint_weights(self):
+        """Tell the library whether the parameter arena changed since the last call (``ocppo_weights_version``): the
+        rollout loop (ppo_atari_oc.py:500-514) calls the policy 128 times on unchanged weights, and the FP16 engines
+        then skip their per-call weight preparation.  The counter is the sum of torch's version counters of the parameters,
+        which every in-place op on a parameter (optimizer steps, ``load_state_dict``, ``copy_``) increments; writes
+        through ``param.data`` or straight into ``self.arena`` bypass it -- call :meth:`weights_changed` after those."""
+        if os.environ.get("OCPPO_NOHINT"):        # bisecting knob
+            return
+        # the parameters were re-pointed at the arena through ``.data`` (which keeps each parameter's own version
+        # counter), so the arena's change counter is the sum of theirs
+        version = sum(p._version for p in self.parameters()) + self._manual_version
+        _abi.check(_abi.lib().ocppo_weights_version(self._handle.raw, int(version)))
+
+    def weights_changed(self):
+        """Invalidate the prepared weights by hand (only needed after writes torch does not track, e.g. ``p.data``)."""
+        self._manual_version += 1 << 40
+
     def get_value(self, x):
         x = self._check_obs(x)
         if self._needs_grad():
             return self.critic(self._hidden_with_grad(x))
         B = x.shape[0]
         self._ensure_workspace(B, training=False)
+        self._hint_weights()
         value = torch.empty((B, 1), dtype=torch.float32, device=x.device)
         _abi.check(_abi.lib().ocppo_value(self._handle.raw, _abi.ptr(x), B, _abi.ptr(value), self._stream()))
         return value
@@ -209,6 +231,7 @@ class PPObj(Predictor):
             return action, probs.log_prob(action), probs.entropy(), self.critic(hidden)
         B = x.shape[0]
         self._ensure_workspace(B, training=False)
+        self._hint_weights()
         dev = x.device
         out_action = torch.empty(B, dtype=torch.int64, device=dev)
         logp = torch.empty(B, dtype=torch.float32, device=dev)

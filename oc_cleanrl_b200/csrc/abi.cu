@@ -225,9 +225,13 @@ static void fwd_args(const ocppo_handle *h, int l, int64_t B, const float *in, S
 static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_t s) {
     const float *in = x;
     const bool f16 = g_gemm_mode >= 5, pre16 = g_gemm_mode >= 6;
-    if (f16) {
-        // operand scales of the FP16x3 engine: activations are tracked by the epilogue that writes them (slots zeroed
-        // here), the weights are measured now -- the arena is the caller's to modify between calls
+    // operand scales of the FP16x3 engine: activations are tracked by the epilogue that writes them (slots zeroed here);
+    // the weights are measured, split and normed now -- the arena is the caller's to modify between calls -- unless the
+    // caller vouched for an unchanged arena (ocppo_weights_version) and this engine prepared it last
+    const bool prepared = f16 && h->w_version >= 0 && h->w_prepared_mode == g_gemm_mode && h->w_amax_valid;
+    if (f16 && prepared) {
+        OCPPO_CUDA(cudaMemsetAsync(h->amax, 0, kAmaxW * sizeof(float), s));
+    } else if (f16) {
         OCPPO_CUDA(cudaMemsetAsync(h->amax, 0, kAmaxGrad * sizeof(float), s));
         AbsmaxSegs segs{};
         for (int l = 0; l < h->n_layers; ++l) {
@@ -249,6 +253,7 @@ static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_
             w.count = h->n_layers;
             OCPPO_TRY(launch_wnorm(w, s));
         }
+        h->w_prepared_mode = g_gemm_mode;
     } else {
         h->w_amax_valid = 0;
     }
@@ -718,6 +723,14 @@ int ocppo_bind_arena(ocppo_handle *h, float *params, float *grads, float *exp_av
                         ((uintptr_t)exp_avg & 127) == 0 && ((uintptr_t)exp_avg_sq & 127) == 0,
                     "arenas must be 128-byte aligned");
     h->params = params; h->grads = grads; h->exp_avg = exp_avg; h->exp_avg_sq = exp_avg_sq;
+    h->w_amax_valid = 0; h->w_version = -1; h->w_prepared_mode = -1;
+    return OCPPO_OK;
+}
+
+int ocppo_weights_version(ocppo_handle *h, int64_t version) {
+    OCPPO_CHECK_ARG(h != nullptr, "null handle");
+    if (version < 0 || version != h->w_version) h->w_amax_valid = 0;     // changed (or no promise): prepare again
+    h->w_version = version;
     return OCPPO_OK;
 }
 

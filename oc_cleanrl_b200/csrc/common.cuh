@@ -113,6 +113,9 @@ struct ocppo_handle {
     float *amax;
     int act_amax_valid[2 * OCPPO_MAX_LAYERS];
     int w_amax_valid;
+    // weight preparation of the FP16 engines (max-abs, fp16 split, norms) may be skipped by a forward call when the caller
+    // vouches that the arena is unchanged (ocppo_weights_version) and no optimizer step ran in between
+    int64_t w_version; int w_prepared_mode;
     void *w16_hi, *w16_lo;              // the trunk weights split into scaled fp16 hi / lo (indexed like params)
     // fp16-pair storage (GEMM engine 6): activations of every trunk layer but the last and the gradients flowing down the
     // trunk exist as (hi, lo) fp16 tensors; the fp32 buffers above are filled on demand only (merge16)

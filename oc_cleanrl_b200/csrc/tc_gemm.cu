@@ -948,10 +948,35 @@ EncodeTiledFn encode_fn() {
     return fn;
 }
 
+// Encoding a tensor map costs a driver call (~1-2 us); a rollout-inference step makes ~30 of them for the same few
+// (pointer, shape) combinations, so the encoded maps are memoised.  A map is a pure function of its key.
+struct MapKey { int kind; const void *base; int64_t a, b, ld; int box; };
+struct MapSlot { MapKey key; CUtensorMap map; bool used; };
+constexpr int kMapSlots = 256;
+MapSlot g_maps[kMapSlots];
+int g_map_next = 0;
+bool map_lookup(const MapKey &k, CUtensorMap *tm) {
+    static const bool off = getenv("OCPPO_NO_MAPCACHE") != nullptr;     // bisecting knob
+    if (off) return false;
+    for (int i = 0; i < kMapSlots; ++i) {
+        const MapSlot &m = g_maps[i];
+        if (m.used && m.key.kind == k.kind && m.key.base == k.base && m.key.a == k.a && m.key.b == k.b && m.key.ld == k.ld &&
+            m.key.box == k.box) { *tm = m.map; return true; }
+    }
+    return false;
+}
+void map_store(const MapKey &k, const CUtensorMap &tm) {
+    MapSlot &m = g_maps[g_map_next];
+    g_map_next = (g_map_next + 1) % kMapSlots;
+    m.key = k; m.map = tm; m.used = true;
+}
+
 // K-major operand [rows, K] (row stride ld floats): 2-D map {K, rows}, box 32 x box_mn, SWIZZLE_128B.
 // MN-major operand [K, cols]: 3-D map {32, K, cols/32}, box 32 x 32 x box_mn/32 -> smem [chunk][k][32 floats],
 // SWIZZLE_128B_ATOM_32B (the TMA name of UMMA's SWIZZLE_128B_BASE32B).
 int make_map(CUtensorMap *tm, const float *base, bool mn_major, int64_t rows_or_cols, int64_t K, int64_t ld, int box_mn) {
+    const MapKey key{0, base, rows_or_cols * 2 + (mn_major ? 1 : 0), K, ld, box_mn};
+    if (map_lookup(key, tm)) return OCPPO_OK;
     EncodeTiledFn fn = encode_fn();
     if (fn == nullptr) { set_error("cuTensorMapEncodeTiled entry point not available"); return OCPPO_ECUDA; }
     CUresult r;
@@ -971,12 +996,15 @@ int make_map(CUtensorMap *tm, const float *base, bool mn_major, int64_t rows_or_
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     }
     if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (%d)", (int)r); return OCPPO_ECUDA; }
+    map_store(key, *tm);
     return OCPPO_OK;
 }
 
 // fp16 operand that is already split and scaled in global memory (same shape / stride as the fp32 one): tiles arrive in
 // the layouts the producers write -- K-major [rows][32 k] = 64-byte rows, SWIZZLE_64B; MN-major [chunk][32 k][64], SWIZZLE_128B
 int make_map16(CUtensorMap *tm, const void *base, bool mn_major, int64_t rows_or_cols, int64_t K, int64_t ld, int box_mn) {
+    const MapKey key{1, base, rows_or_cols * 2 + (mn_major ? 1 : 0), K, ld, box_mn};
+    if (map_lookup(key, tm)) return OCPPO_OK;
     EncodeTiledFn fn = encode_fn();
     if (fn == nullptr) { set_error("cuTensorMapEncodeTiled entry point not available"); return OCPPO_ECUDA; }
     CUresult r;
@@ -996,12 +1024,15 @@ int make_map16(CUtensorMap *tm, const void *base, bool mn_major, int64_t rows_or
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     }
     if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (fp16 operand) failed (%d)", (int)r); return OCPPO_ECUDA; }
+    map_store(key, *tm);
     return OCPPO_OK;
 }
 
 // Output (and aux: DGRAD mask, WGRAD running partial) [rows, cols] row-major: 2-D map {cols, rows}, box 32 x 32,
 // SWIZZLE_128B -- one epilogue warp's chunk.  Rows past `rows` are clipped on store and zero-filled on load.
 int make_map_c(CUtensorMap *tm, const float *base, int64_t rows, int64_t cols, int64_t ld) {
+    const MapKey key{2, base, rows, cols, ld, 0};
+    if (map_lookup(key, tm)) return OCPPO_OK;
     EncodeTiledFn fn = encode_fn();
     if (fn == nullptr) { set_error("cuTensorMapEncodeTiled entry point not available"); return OCPPO_ECUDA; }
     const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
@@ -1011,11 +1042,14 @@ int make_map_c(CUtensorMap *tm, const float *base, int64_t rows, int64_t cols, i
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (output map) failed (%d)", (int)r); return OCPPO_ECUDA; }
+    map_store(key, *tm);
     return OCPPO_OK;
 }
 
 // fp16 half of an fp16-pair output [rows, cols]: box 32 x 32 = 64-byte rows, SWIZZLE_64B (what the epilogue writes)
 int make_map_c16(CUtensorMap *tm, const void *base, int64_t rows, int64_t cols, int64_t ld) {
+    const MapKey key{3, base, rows, cols, ld, 0};
+    if (map_lookup(key, tm)) return OCPPO_OK;
     EncodeTiledFn fn = encode_fn();
     if (fn == nullptr) { set_error("cuTensorMapEncodeTiled entry point not available"); return OCPPO_ECUDA; }
     const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
@@ -1025,6 +1059,7 @@ int make_map_c16(CUtensorMap *tm, const void *base, int64_t rows, int64_t cols, 
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (fp16 output map) failed (%d)", (int)r); return OCPPO_ECUDA; }
+    map_store(key, *tm);
     return OCPPO_OK;
 }
 

@@ -108,6 +108,7 @@ class RolloutCollector:
             raise _abi.OcppoError(f"step {step} outside [0, {self.T})")
         a = self.agent
         a._ensure_workspace(self.N, training=False)
+        a._hint_weights()
         seed, offset = a._philox_state(self.N * a._n_actions)     # consumes torch's CUDA generator like Categorical.sample()
         stream = torch.cuda.current_stream(self.device)
         _abi.check(_abi.lib().ocppo_policy_step(

@@ -643,3 +643,34 @@ def test_full_size_minibatch_properties(dev, gemm_engine):
         loss2.backward()
         assert rel_err(grads[4], ref_ppo.flat_grads(oracle).numpy()) < REL_TOL
     assert float(learner._stats[0, 3]) == pytest.approx(float(loss.detach()), rel=REL_TOL, abs=1e-6)
+
+
+def test_inference_reuses_prepared_weights_until_they_change(dev, gemm_engine):
+    """ocppo_weights_version: repeated no-grad calls on unchanged weights skip the FP16 engines' weight preparation
+    (max-abs, fp16 split, norms) and stay bit-identical; an in-place torch update of a parameter bumps the arena's
+    version, and the next call must see the new weights (checked against the oracle carrying the same change);
+    writes through ``.data`` need ``weights_changed()``."""
+    F, D, A = 4, 6, 6
+    enc, dec = (256, 512), (256,)
+    agent, oracle = make_pair(dev, F, D, A, enc, dec, seed=9)
+    data = make_rollout(4, 64, F, D, seed=21)
+    x = data["obs"].reshape(-1, F, D).to(dev)
+    with torch.no_grad():
+        a0, lp0, en0, v0 = agent.get_action_and_value(x, torch.zeros(x.shape[0], dtype=torch.int64, device=dev))
+        a1, lp1, en1, v1 = agent.get_action_and_value(x, torch.zeros(x.shape[0], dtype=torch.int64, device=dev))
+        assert torch.equal(lp0, lp1) and torch.equal(v0, v1) and torch.equal(en0, en1)
+        assert torch.equal(agent.get_value(x), v0)
+        # tracked in-place change of one trunk weight and one bias
+        params, oparams = list(agent.parameters()), list(oracle.parameters())
+        params[2].mul_(1.5); oparams[2].mul_(1.5)
+        params[3].add_(0.25); oparams[3].add_(0.25)
+        _, lp2, _, v2 = agent.get_action_and_value(x, torch.zeros(x.shape[0], dtype=torch.int64, device=dev))
+        _, lp_ref, _, v_ref = oracle.get_action_and_value(data["obs"].reshape(-1, F, D), torch.zeros(x.shape[0], dtype=torch.int64))
+        assert not torch.equal(v2, v0)
+        assert rel_err(lp2.cpu().numpy(), lp_ref.numpy()) < REL_TOL
+        assert rel_err(v2.cpu().numpy(), v_ref.numpy()) < REL_TOL
+        # untracked write: stale until the caller says so
+        params[2].data.mul_(2.0); oparams[2].data.mul_(2.0)
+        agent.weights_changed()
+        v3 = agent.get_value(x)
+        assert rel_err(v3.cpu().numpy(), oracle.get_value(data["obs"].reshape(-1, F, D)).numpy()) < REL_TOL

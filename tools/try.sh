@@ -9,7 +9,7 @@ OCPPO_TC_DBG=$d timeout 300 python bench.py --gemm $g --no-cpu-baseline --no-e2e
 python -c "
 import json
 d=json.loads(open('gpurun_out/bench_${g}_d$d.json').read().strip().splitlines()[-1])
-print('$g dbg$d', round(d['ms_per_step'],2), {k:round(v,1) for k,v in d['kernel_ms_per_step'].items()}, d['clocks']['sm_mhz'], d['clocks']['power_w_max'], d['last_stats']['loss'], d['last_stats']['grad_norm'])
+print('$g dbg$d', round(d['ms_per_step'],2), {k:round(v,1) for k,v in d['kernel_ms_per_step'].items()}, d['clocks']['sm_mhz'], d['clocks']['power_w_max'], d['last_stats']['loss'], d['last_stats']['grad_norm'], 'inf_ms', [round(i['ms_per_call'],3) for i in d['inference']])
 "
 tail -2 gpurun_out/bench_${g}_d$d.err
 done
