@@ -1,25 +1,34 @@
 // fp32-grade GEMM on the 5th-gen tensor cores (tcgen05.mma, fp32 accumulation in TMEM).  Every operand is split
-// x = hi + lo with hi = trunc_tf32(x); the product is hi.hi (kind::tf32, straight from the raw fp32 tile: the hardware
-// truncates) plus two correction products -- as BF16 MMAs (engine 3, default: bf16(a-hi_a).bf16(b) + bf16(a).bf16(b-hi_b))
-// or as TF32 MMAs (engines 1, 2: lo.hi + hi.lo).  Same three contractions as sgemm.cu:
+// x = hi + lo and the product is hi.hi plus two correction products (lo.lo, 2^-22, is dropped).  Same three contractions
+// as sgemm.cu:
 //   FWD   : Y[M,N]  = relu(X[M,K] . W[N,K]^T + b[N])      A K-major,  B K-major
 //   DGRAD : dX[M,N] = (mask > 0) * (dY[M,K] . W[K,N])      A K-major,  B MN-major
 //   WGRAD : dW[M,N] = dY[K,M]^T . X[K,N]  (split-K)        A MN-major, B MN-major
+// Engines (template parameter CORR; ocppo_set_gemm_mode):
+//   CORR 0  3xTF32: hi = trunc_tf32(x) (kind::tf32 on the raw fp32 tile: the hardware truncates), lo.hi + hi.lo as TF32 MMAs
+//   CORR 1  TF32 main product + two BF16 correction products
+//   CORR 2  FP16 x 3 on fp32-stored operands: x.s = h + l in fp16 (s a per-tensor power of two), three kind::f16 products;
+//           the weights of FWD / DGRAD arrive pre-split by TMA (four 48 KB stages), the rest is converted by producer warps
+//   CORR 3  FP16 x 3 on fp16-PAIR storage (the default, engines 6 / 8): both operands live in global memory as (hi, lo)
+//           fp16 tensors and are TMA-loaded straight into the MMA tiles -- six 32 KB stages, no producer warps (320 threads);
+//           FWD / DGRAD can write their output as a pair too (scaled by an a-priori bound), DGRAD adds the bias column sums
+// SPLIT: main product in TMEM columns [0,256), corrections in [256,512) (3x less rounding, one tile in flight) | one
+// 256-column accumulator per tile, two tiles in flight (the epilogue overlaps the next mainloop).
 //
 // Persistent, warp-specialised, CTA-pair kernel: a cluster of two CTAs (one SM each, same TPC) walks
 // 256 x 256 output tiles with tcgen05.mma.cta_group::2.  Each CTA stages its own 128 rows of A and its own
 // 128 columns of B (so the pair fetches every operand byte once), and holds the 128 x 256 fp32 accumulators of
-// its rows in its own TMEM (main product in columns 0-255, corrections in 256-511).  Per CTA, 16 warps:
-//   warps 0-7   epilogue : two per TMEM lane quarter; tcgen05.ld, main + corrections, bias/ReLU | ReLU decision |
-//                          k-segment accumulate, STS into a swizzled 4 KB tile, one bulk tensor store per 32 x 32 chunk
-//   warp  8     MMA      : one thread of the LEADER CTA issues the pair's MMAs: the main product as soon as the raw
-//                          tiles of both CTAs have landed, the corrections when the producers are done
-//   warp  9     TMA      : one thread per CTA loads the raw fp32 tiles (2-D maps for K-major operands, 3-D maps with
-//                          SWIZZLE_128B_ATOM_32B for MN-major ones: nothing is ever transposed in memory)
-//   warp  10    forwarder: tells the leader that this CTA's raw tiles have landed
-//   warps 12-15 producers: read the raw tiles back and write the correction operands in the canonical UMMA layouts
-// Three 64 KB stages.  Hand-offs are mbarriers: tma (per CTA), raw_full / full (leader; both CTAs arrive, the peer
-// remotely), empty (tcgen05.commit multicast to both CTAs), tmem_full / tmem_empty per accumulator.
+// its rows in its own TMEM.  Per CTA:
+//   warps 0-7   epilogue : two per TMEM lane quarter; tcgen05.ld, unscale, bias/ReLU/decision bits | ReLU mask + column
+//                          sums | k-segment accumulate, STS into a swizzled tile, bulk tensor store(s) per 32 x 32 chunk
+//   warp  8     MMA      : one thread of the LEADER CTA issues the pair's MMAs; in the peer CTA the same thread forwards
+//                          "my tiles have landed" to the leader (engines without conversion on the critical path)
+//   warp  9     TMA      : one thread per CTA loads this CTA's tiles (2-D maps for K-major operands, 3-D maps for MN-major
+//                          ones: nothing is ever transposed in memory)
+//   warps 10-17 producers: (CORR 0-2 only) read the raw fp32 tiles back and write the MMA operand tiles in the canonical
+//                          UMMA layouts
+// Hand-offs are mbarriers: tma (per CTA), raw_full / full (leader), empty (tcgen05.commit multicast to both CTAs),
+// tmem_full / tmem_empty per accumulator.
 #include "common.cuh"
 #include <cuda.h>
 #include <cuda_fp16.h>
