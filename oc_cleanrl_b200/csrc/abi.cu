@@ -126,6 +126,16 @@ static int64_t carve(ocppo_handle *h, void *base, int64_t R, int training, bool 
         if (L.in_dim > max_dim) max_dim = L.in_dim;
         if (L.out_dim > max_dim) max_dim = L.out_dim;
     }
+    {   // wide first layer (32 < D <= kPadCols): padded pair copies of its input and weight
+        const Layer &L0 = h->layers[0];
+        const bool pad0 = h->n_layers > 1 && L0.in_dim > 32 && L0.in_dim <= kPadCols && L0.out_dim % 256 == 0;
+        t->x0p_hi = pad0 ? cv.take<uint16_t>(R * L0.row_mult * kPadCols) : nullptr;
+        t->x0p_lo = pad0 ? cv.take<uint16_t>(R * L0.row_mult * kPadCols) : nullptr;
+        t->w0p_hi = pad0 ? cv.take<uint16_t>((int64_t)L0.out_dim * kPadCols) : nullptr;
+        t->w0p_lo = pad0 ? cv.take<uint16_t>((int64_t)L0.out_dim * kPadCols) : nullptr;
+        t->x0p_valid = 0;
+        if (pad0 && (int64_t)L0.out_dim * kPadCols > max_w) max_w = (int64_t)L0.out_dim * kPadCols;
+    }
     t->amax = cv.take<float>(kAmaxSlots);
     t->w_amax_valid = 0;
     t->w16_hi = cv.take<uint16_t>(h->param_floats);
@@ -154,9 +164,13 @@ static int64_t carve(ocppo_handle *h, void *base, int64_t R, int training, bool 
             const Layer &L0 = h->layers[0];
             const int64_t g0 = (int64_t)h->sm_count * 4, gh = g0;     // upper bound of the slab count
             int64_t need = gh * ((int64_t)h->hidden * 33 + 32);
-            if (L0.in_dim <= 32) {
-                const int64_t n0 = g0 * (int64_t)L0.out_dim * 33;
-                if (n0 > need) need = n0;
+            (void)L0;
+            for (int l = 0; l < h->n_layers; ++l) {            // every layer whose wgrad may take the skinny route
+                const Layer &L = h->layers[l];
+                if (L.in_dim <= kSkinnyMaxIn) {
+                    const int64_t n0 = g0 * (int64_t)L.out_dim * 33;
+                    if (n0 > need) need = n0;
+                }
             }
             t->skinny = cv.take<float>(need);
         }
@@ -268,6 +282,34 @@ static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_
         h->relu_bits_valid[l] = a.relu_bits != nullptr && tc;
         const bool w16 = L.w_off % 8 == 0 && L.in_dim % 8 == 0;
         bool pair_out = false;
+        if (l == 0) h->x0p_valid = 0;
+        if (pre16 && l == 0 && h->x0p_hi != nullptr && h->w_amax_valid) {
+            // wide object vectors (SpaceInvaders 88, Breakout 220 columns): the FMA route costs 0.5 - 1.2 ms forward and
+            // 2.8 ms backward per minibatch here.  Input and weight rows are zero-padded to one 256-wide tile in pair
+            // storage instead, and the layer runs on the conversion-free tensor-core kernel like the others.
+            const int64_t rows0 = B * L.row_mult;
+            OCPPO_TRY(launch_absmax(x, rows0, L.in_dim, L.in_dim, h->amax + kAmaxObs, h->sm_count, s));
+            OCPPO_TRY(launch_pad_split16(x, rows0, L.in_dim, L.in_dim, h->amax + kAmaxObs, h->x0p_hi, h->x0p_lo, h->sm_count, s));
+            if (!prepared)
+                OCPPO_TRY(launch_pad_split16(h->params + L.w_off, L.out_dim, L.in_dim, L.in_dim, h->amax + kAmaxW, h->w0p_hi,
+                                             h->w0p_lo, h->sm_count, s));
+            a.A = nullptr; a.lda = kPadCols; a.ldb = kPadCols; a.K = kPadCols; a.k_per_split = kPadCols;
+            a.a16_hi = h->x0p_hi; a.a16_lo = h->x0p_lo; a.amax_a = h->amax + kAmaxObs;
+            a.b16_hi = h->w0p_hi; a.b16_lo = h->w0p_lo; a.amax_b = h->amax + kAmaxW;
+            a.amax_scratch = h->amax;
+            a.amax_out = h->amax + kAmaxAct;
+            OCPPO_CHECK_ARG(sgemm_uses_tc(SGEMM_FWD, a), "padded first layer rejected by the tensor-core kernel");
+            h->relu_bits_valid[0] = a.relu_bits != nullptr;
+            SgemmArgs n{};
+            fwd_args(h, 1, B, h->act[0], &n);
+            if (pair_ok(h, 0, B) && sgemm_uses_tc(SGEMM_FWD, n)) {
+                a.c16_hi = h->act16_hi[0]; a.c16_lo = h->act16_lo[0];
+                a.bnd_amax = h->amax + kAmaxObs; a.bnd_wl1 = h->amax + kWRowL1; a.bnd_bmax = h->amax + kBMax;
+                a.c_scale_src = h->amax + kBndAct;
+                pair_out = true;
+            }
+            h->x0p_valid = 1;
+        } else
         if (f16) {
             a.amax_scratch = h->amax;
             a.amax_b = h->amax + kAmaxW + l;
@@ -366,14 +408,6 @@ static void pick_split(const ocppo_handle *h, int M, int N, int64_t K, int *spli
 static int wgrad(ocppo_handle *h, const float *dY, int out, const float *X, int in, int64_t rows, float *dW,
                  int64_t w_count, float *db, int64_t b_count, int accumulate, cudaStream_t s,
                  const float *amax_dy = nullptr, const float *amax_x = nullptr) {
-    if (in <= 32) {          // skinny contraction (first trunk layer): HBM-bound dedicated kernel
-        int G = 0, NS = 0;
-        float *part = h->skinny, *wsum = h->skinny + (int64_t)h->sm_count * 4 * out * 32;
-        OCPPO_TRY(launch_skinny_wgrad(dY, out, out, X, in, in, rows, h->sm_count, part, wsum, nullptr, &G, &NS, s));
-        OCPPO_TRY(launch_skinny_reduce(part, G, out, NS, 0, in, dW, 1, in, accumulate, s));
-        OCPPO_TRY(launch_skinny_reduce(wsum, G, out, 1, 0, 1, db, 1, 1, accumulate, s));
-        return OCPPO_OK;
-    }
     SgemmArgs a{};
     a.A = dY; a.lda = out;
     a.B = X; a.ldb = in;
@@ -382,6 +416,20 @@ static int wgrad(ocppo_handle *h, const float *dY, int out, const float *X, int 
     a.M = out; a.N = in; a.K = rows;
     a.amax_a = amax_dy; a.amax_b = amax_x; a.amax_scratch = h->amax;
     pick_split(h, out, in, rows, &a.splits, &a.k_per_split);
+    if (in <= 32 || (in <= kSkinnyMaxIn && !sgemm_uses_tc(SGEMM_WGRAD, a))) {
+        // skinny contraction (the first trunk layer: in = object-vector width): one thread per dY column, 32 input columns
+        // per pass -- HBM-bound for Pong's 6 columns, at the FMA peak for SpaceInvaders' 88 / Breakout's 220 (3 / 7 passes;
+        // the 128 x 128-tiled FMA GEMM took 3x as long on these)
+        float *part = h->skinny, *wsum = h->skinny + (int64_t)h->sm_count * 4 * out * 32;
+        for (int c0 = 0; c0 < in; c0 += 32) {
+            const int n = in - c0 < 32 ? in - c0 : 32;
+            int G = 0, NS = 0;
+            OCPPO_TRY(launch_skinny_wgrad(dY, out, out, X + c0, in, n, rows, h->sm_count, part, c0 == 0 ? wsum : nullptr, nullptr, &G, &NS, s));
+            OCPPO_TRY(launch_skinny_reduce(part, G, out, NS, 0, n, dW + c0, 1, in, accumulate, s));
+            if (c0 == 0) OCPPO_TRY(launch_skinny_reduce(wsum, G, out, 1, 0, 1, db, 1, 1, accumulate, s));
+        }
+        return OCPPO_OK;
+    }
     OCPPO_TRY(sgemm_launch(SGEMM_WGRAD, a, s));
     OCPPO_TRY(launch_splitk_reduce(h->splitk, a.splits, (int64_t)out * in, w_count, dW, accumulate, h->sm_count, s));
     OCPPO_TRY(launch_splitk_reduce(h->splitk_bias, a.splits, out, b_count, db, accumulate, h->sm_count, s));
@@ -426,9 +474,13 @@ static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, i
         // ---- plan: which of this layer's two GEMMs take fp16 pairs
         bool pre_w = false, pre_d = false;
         SgemmArgs wa{}, da{};
+        const bool pad0 = l == 0 && pre16 && h->x0p_valid;         // first layer on padded pair storage (see trunk_forward)
         if (l > 0 && L.in_dim > 32) {
             wgrad_args(h, dY, L.out_dim, X, L.in_dim, rows, &wa);
             pre_w = dy_pair_ok && sgemm_uses_tc(SGEMM_WGRAD, wa) && L.out_dim % 64 == 0 && pair_ok(h, l - 1, B);
+        } else if (pad0) {
+            wgrad_args(h, dY, L.out_dim, nullptr, kPadCols, rows, &wa);
+            pre_w = dy_pair_ok && sgemm_uses_tc(SGEMM_WGRAD, wa) && L.out_dim % 64 == 0;
         }
         if (l > 0) {
             da.A = dY; da.lda = L.out_dim;
@@ -463,13 +515,20 @@ static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, i
 
         // ---- weight and bias gradients
         if (pre_w) {
-            OCPPO_TRY(ensure_act16(h, l - 1, B, s));
             wa.a16_hi = h->g16_hi[cur]; wa.a16_lo = h->g16_lo[cur]; wa.amax_a = dy_scale;
-            wa.b16_hi = h->act16_hi[l - 1]; wa.b16_lo = h->act16_lo[l - 1]; wa.amax_b = h->act_scale[l - 1];
             wa.amax_scratch = h->amax;
-            OCPPO_TRY(sgemm_launch(SGEMM_WGRAD, wa, s));
-            OCPPO_TRY(launch_splitk_reduce(h->splitk, wa.splits, (int64_t)L.out_dim * L.in_dim, (int64_t)L.out_dim * L.in_dim,
-                                           h->grads + L.w_off, accumulate, h->sm_count, s));
+            if (l == 0) {          // padded input pair; the partial tiles are kPadCols wide, the gradient rows in_dim
+                wa.b16_hi = h->x0p_hi; wa.b16_lo = h->x0p_lo; wa.amax_b = h->amax + kAmaxObs;
+                OCPPO_TRY(sgemm_launch(SGEMM_WGRAD, wa, s));
+                OCPPO_TRY(launch_splitk_reduce_pad(h->splitk, wa.splits, L.out_dim, L.in_dim, h->grads + L.w_off, accumulate,
+                                                   h->sm_count, s));
+            } else {
+                OCPPO_TRY(ensure_act16(h, l - 1, B, s));
+                wa.b16_hi = h->act16_hi[l - 1]; wa.b16_lo = h->act16_lo[l - 1]; wa.amax_b = h->act_scale[l - 1];
+                OCPPO_TRY(sgemm_launch(SGEMM_WGRAD, wa, s));
+                OCPPO_TRY(launch_splitk_reduce(h->splitk, wa.splits, (int64_t)L.out_dim * L.in_dim, (int64_t)L.out_dim * L.in_dim,
+                                               h->grads + L.w_off, accumulate, h->sm_count, s));
+            }
             if (!db_done) {
                 int blocks = 0;
                 OCPPO_TRY(launch_colsum16(h->g16_hi[cur], h->g16_lo[cur], rows, L.out_dim, dy_scale, h->colsum_part, &blocks, h->sm_count, s));
@@ -508,10 +567,11 @@ static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, i
                     a.a16_hi = h->g16_hi[cur]; a.a16_lo = h->g16_lo[cur]; a.amax_a = dy_scale;
                     // the gradient leaves as a pair when both GEMMs of the layer below will take it that way
                     const Layer &Ln = h->layers[l - 1];
-                    bool next_pair = l - 1 >= 1 && Ln.in_dim > 32 && Ln.out_dim % 64 == 0 && (rows * L.in_dim) % 4 == 0 && pair_ok(h, l - 2, B);
+                    bool next_pair = Ln.out_dim % 64 == 0 && (rows * L.in_dim) % 4 == 0 &&
+                                     ((l - 1 >= 1 && Ln.in_dim > 32 && pair_ok(h, l - 2, B)) || (l - 1 == 0 && h->x0p_valid));
                     if (next_pair) {
                         SgemmArgs nw{};
-                        wgrad_args(h, h->gbuf[cur ^ 1], Ln.out_dim, h->act[l - 2], Ln.in_dim, B * Ln.row_mult, &nw);
+                        wgrad_args(h, h->gbuf[cur ^ 1], Ln.out_dim, nullptr, l - 1 == 0 ? kPadCols : Ln.in_dim, B * Ln.row_mult, &nw);
                         next_pair = sgemm_uses_tc(SGEMM_WGRAD, nw);
                     }
                     if (next_pair) {

@@ -59,6 +59,7 @@ static inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * 
 static inline int64_t ceil_div(int64_t x, int64_t m) { return (x + m - 1) / m; }
 
 constexpr int kArenaAlignFloats = 32;      // every tensor starts 128 B aligned
+constexpr int kSkinnyMaxIn = 96;           // widest layer input the skinny weight-gradient route takes (32 columns per pass; beyond 3 passes the tiled GEMM wins)
 constexpr int kSplitMax = 32;              // max split-K factor of the wgrad kernels
 constexpr int kLossBlocksMax = 4096;       // partial-sum slots of the loss head
 constexpr int kNormBlocks = 592;           // 148 SMs x 4 CTAs for the grad-norm pass
@@ -124,6 +125,11 @@ struct ocppo_handle {
     const float *act_scale[2 * OCPPO_MAX_LAYERS];   // device scalar the pair's power-of-two scale derives from
     void *g16_hi[2], *g16_lo[2];        // pair twins of gbuf[]
     float *colsum_part;                 // [kColsumBlocksMax, max(out)] bias-gradient partials
+    // first layer with a wide object vector (32 < D <= 256, e.g. SpaceInvaders 88, Breakout 220): input and weight rows
+    // zero-padded to kPadCols in pair storage, so the layer's FWD and WGRAD run on the conversion-free tensor-core kernel
+    void *x0p_hi, *x0p_lo;              // [max_rows * frames, kPadCols]
+    void *w0p_hi, *w0p_lo;              // [out_0, kPadCols]
+    int x0p_valid;
 };
 // device scalars in ocppo_handle::amax: true maxima (Act / W / Grad), the bounds the epilogues scale their fp16-pair outputs
 // by (BndAct + l: act[l]; BndGrad + l: gradient entering layer l's backward), and per layer the weights' largest row / column
@@ -222,6 +228,10 @@ struct WnormSegs {
     float *row_l1[2 * OCPPO_MAX_LAYERS], *col_l1[2 * OCPPO_MAX_LAYERS], *b_max[2 * OCPPO_MAX_LAYERS]; int count;
 };
 constexpr int kColsumBlocksMax = 1024;
+constexpr int kPadCols = 256;              // padded width of the first layer's input / weight rows in pair storage (one N tile)
+int launch_pad_split16(const float *x, int64_t rows, int cols, int64_t ld, const float *scale_src, void *hi, void *lo, int sm_count,
+                       cudaStream_t stream);
+int launch_splitk_reduce_pad(const float *part, int splits, int rows, int cols, float *out, int accumulate, int sm_count, cudaStream_t stream);
 int launch_split16(const float *x, int64_t n, const float *scale_src, void *hi, void *lo, int sm_count, cudaStream_t stream);
 int launch_merge16(const void *hi, const void *lo, int64_t n, const float *scale_src, float *out, int sm_count, cudaStream_t stream);
 int launch_colsum16(const void *hi, const void *lo, int64_t rows, int cols, const float *scale_src, float *part, int *blocks,

@@ -78,6 +78,43 @@ __global__ void __launch_bounds__(256) colsum16_kernel(const uint2 *__restrict__
     }
 }
 
+// fp32 [rows, cols] (row stride ld) -> pair [rows, kPadCols] with zero padding: the first trunk layer's input (and its weight)
+// when the object vector is wider than the skinny route likes -- padded to the tensor-core tile so that layer, too, runs
+// as a conversion-free GEMM.  One thread per 8 output columns.
+__global__ void __launch_bounds__(256) pad_split16_kernel(const float *__restrict__ x, int64_t rows, int cols, int64_t ld,
+                                                          const float *__restrict__ scale_src, uint4 *__restrict__ hi,
+                                                          uint4 *__restrict__ lo) {
+    float scale, inv;
+    f16_scale_of(__ldg(scale_src), scale, inv);
+    constexpr int G = kPadCols / 8;
+    const int64_t total = rows * G;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / G;
+        const int c0 = (int)(i - r * G) * 8;
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = (c0 + j < cols) ? __ldg(x + r * ld + c0 + j) : 0.f;
+        uint32_t h[4], l[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) split_f16x2(v[2 * j], v[2 * j + 1], scale, h[j], l[j]);
+        hi[i] = make_uint4(h[0], h[1], h[2], h[3]);
+        lo[i] = make_uint4(l[0], l[1], l[2], l[3]);
+    }
+}
+
+// out[r, c] (+)= sum_s part[s][r][c] for c < cols: split-K partials computed on kPadCols-wide rows, result rows `cols` wide
+__global__ void __launch_bounds__(256) splitk_reduce_pad_kernel(const float *__restrict__ part, int splits, int rows, int cols,
+                                                                float *__restrict__ out, int accumulate) {
+    const int64_t total = (int64_t)rows * cols;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / cols;
+        const int c = (int)(i - r * cols);
+        float s = 0.f;
+        for (int k = 0; k < splits; ++k) s += part[((int64_t)k * rows + r) * kPadCols + c];
+        out[i] = accumulate ? out[i] + s : s;
+    }
+}
+
 // the loss head's fp32 gradient [rows, cols]: pair AND column-sum partials in one read (same slab / order rules as above)
 __global__ void __launch_bounds__(256) split16_colsum_kernel(const float4 *__restrict__ x, int64_t rows, int cols, int64_t rows_per_block,
                                                              const float *__restrict__ scale_src, uint2 *__restrict__ hi,
@@ -259,6 +296,25 @@ int launch_split16_colsum(const float *x, int64_t rows, int cols, const float *s
     split16_colsum_kernel<<<*blocks, 256, 0, stream>>>(reinterpret_cast<const float4 *>(x), rows, cols, rpb, scale_src,
                                                        reinterpret_cast<uint2 *>(hi), reinterpret_cast<uint2 *>(lo), part);
     OCPPO_LAUNCH_CHECK("split16_colsum_kernel");
+    return OCPPO_OK;
+}
+
+int launch_pad_split16(const float *x, int64_t rows, int cols, int64_t ld, const float *scale_src, void *hi, void *lo, int sm_count,
+                       cudaStream_t stream) {
+    if (rows == 0) return OCPPO_OK;
+    OCPPO_CHECK_ARG(x && scale_src && hi && lo && cols >= 1 && cols <= kPadCols && ld >= cols, "pad_split16: bad arguments");
+    ProfScope ps(KC_AUX, 1, stream);
+    pad_split16_kernel<<<grid_of(rows * (kPadCols / 8) / 2, sm_count), 256, 0, stream>>>(x, rows, cols, ld, scale_src,
+                                                                                         reinterpret_cast<uint4 *>(hi), reinterpret_cast<uint4 *>(lo));
+    OCPPO_LAUNCH_CHECK("pad_split16_kernel");
+    return OCPPO_OK;
+}
+
+int launch_splitk_reduce_pad(const float *part, int splits, int rows, int cols, float *out, int accumulate, int sm_count, cudaStream_t stream) {
+    OCPPO_CHECK_ARG(part && out && splits >= 1 && rows >= 1 && cols >= 1 && cols <= kPadCols, "splitk_reduce_pad: bad arguments");
+    ProfScope ps(KC_AUX, 1, stream);
+    splitk_reduce_pad_kernel<<<grid_of((int64_t)rows * cols, sm_count), 256, 0, stream>>>(part, splits, rows, cols, out, accumulate);
+    OCPPO_LAUNCH_CHECK("splitk_reduce_pad_kernel");
     return OCPPO_OK;
 }
 
