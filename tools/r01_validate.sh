@@ -8,3 +8,4 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:tc_gemm_kernel -s 6 -c 3 -f -o gpurun_out/v_tc8_full \
   python tools/gemm_bench.py 8 1 131072 > gpurun_out/v_ncu_full.log 2>&1; echo "ncu full rc=$?"
 ls -la gpurun_out
+timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2
