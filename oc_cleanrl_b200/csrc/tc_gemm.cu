@@ -64,7 +64,7 @@ constexpr int kProdTid0 = (kEpiWarps + 2) * 32;             // 320
 constexpr int kTcThreads = kProdTid0 + kProdThreads;        // 576: at most 112 registers per thread
 constexpr int kProdQ = 1024 / kProdThreads;                 // 16-byte chunks of a 16 KB raw tile per producer thread (4)
 constexpr int kStageBytesA = TM * TK * 4;                   // 16 KB
-constexpr int kRingBytes = 192 * 1024;                      // 3 x 64 KB or 4 x 48 KB
+constexpr int kRingBytes = 192 * 1024;                      // 3 x 64 KB, 4 x 48 KB or 6 x 32 KB stages
 constexpr int kMaxStages = 6;
 constexpr int kTmemCols = 512;                              // two tiles' accumulators
 // The TMEM accumulator rounds TOWARD ZERO on every accumulate (tools/tc_probe.cu Q4): each chained MMA shrinks the running
