@@ -38,8 +38,9 @@ import torch  # noqa: E402
 ENC, DEC = (256, 512, 1024, 512), (512,)
 FRAMES = 4
 # dram__bytes_read.sum + dram__bytes_write.sum of one tc_gemm_kernel<FWD> launch (M=524288, N=512, K=1024) from the
-# ncu --set full capture profiles/r01_tc3_ncu_full.txt (algorithmic bytes of that launch: 3.22 GB)
-TRAFFIC_BYTES_PER_LAUNCH = 3196000000
+# ncu --set full capture profiles/r01_tc8_ncu_full.txt (engine 8; 2.247 GB read + 1.044 GB written; algorithmic bytes of that
+# launch: 3.22 GB = the A pair and the C pair once)
+TRAFFIC_BYTES_PER_LAUNCH = 3291000000
 
 
 def parse():
