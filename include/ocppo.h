@@ -9,7 +9,9 @@
  *  - plain C types only; all data pointers are DEVICE pointers owned by the
  *    caller (torch tensors), fp32 unless stated; `stream` is a cudaStream_t
  *    passed as void*; calls are asynchronous on that stream and never
- *    synchronise, allocate or start threads.
+ *    synchronise, allocate or start threads (so they can be captured into a
+ *    CUDA graph).  Every call makes the device of its handle (or of its first
+ *    data pointer) current for its own duration and restores the caller's.
  *  - every function returns 0 on success or a negative OCPPO_E* code;
  *    ocppo_last_error() returns a thread-local message.  Nothing throws.
  *  - there is no CPU fallback: a device that is not sm_100 is an error.
@@ -74,16 +76,25 @@ enum {
 
 const char *ocppo_last_error(void);
 int ocppo_version(void);
+/* 1 if the library was compiled with -DOCPPO_BRINGUP (the bisecting knobs OCPPO_TC_DBG / OCPPO_TC_OPS / OCPPO_TC_TRUNC /
+ * OCPPO_NO_MAPCACHE are then read from the environment), 0 for the release build, which has none of them. */
+int ocppo_bringup_build(void);
 
 /* ---- launch accounting / live kernel timing (measurement only) ---------- */
-/* Kernel classes: 0 GAE, 1 SGEMM fwd, 2 SGEMM dgrad, 3 SGEMM wgrad, 4 heads,
- * 5 aux (gather/reduce/stats), 6 clip+Adam.  ocppo_launch_count() = kernels
- * launched by this library since load.  With profiling enabled every launch is
- * bracketed by CUDA events on its own stream; ocppo_profile_read() waits for
- * them and returns the summed milliseconds and number of timed launches per
- * class (8 slots), then clears the log. */
+/* Kernel classes: 0 GAE, 1 trunk GEMM fwd (tcgen05), 2 trunk GEMM dgrad, 3 trunk
+ * GEMM wgrad, 4 heads, 5 aux (gather/reduce/stats/pair passes), 6 clip+Adam,
+ * 7 CUDA-core contraction kernels (first-layer FMA GEMM, skinny weight
+ * gradients, every shape the tensor-core tile rejects).  ocppo_launch_count()
+ * = kernels launched by this library since load.  With profiling enabled every
+ * launch is bracketed by CUDA events on its own stream; the event ring is
+ * drained into per-class sums whenever it fills, so NO launch is dropped:
+ * ocppo_profile_read() returns the summed milliseconds and the number of
+ * kernels timed per class (8 slots) since the last read / enable, then clears
+ * them.  Launches made while their stream is being captured into a CUDA graph
+ * cannot carry events; ocppo_launch_counts() reports them as `untimed`. */
 #define OCPPO_NUM_KERNEL_CLASSES 8
 int64_t ocppo_launch_count(void);
+int ocppo_launch_counts(int64_t *launches_by_class, int64_t *untimed_by_class, int32_t n_classes);
 int ocppo_profile_enable(int32_t on);
 int ocppo_profile_read(double *ms_by_class, int64_t *timed_by_class, int32_t n_classes);
 /* Synchronous micro-benchmark: achievable fp32 FMA TFLOP/s of the current device
@@ -167,6 +178,17 @@ int ocppo_bind_workspace(ocppo_handle *h, void *workspace, int64_t bytes, int64_
 int ocppo_policy_step(ocppo_handle *h, const float *obs, int64_t B, uint64_t seed,
                       uint64_t philox_offset, const int64_t *given_action, int64_t *action,
                       float *logp, float *entropy, float *value, void *stream);
+/* The same call with the Philox (seed, offset) pair read from DEVICE memory
+ * (philox_state[0] = seed, [1] = offset) by the head kernel instead of being
+ * kernel arguments: a CUDA graph captured around this call can be replayed
+ * for every rollout step (ppo_atari_oc.py:500-509 calls the policy num_steps
+ * times per iteration), the caller refreshing the two words before each
+ * replay. */
+int ocppo_policy_step_dev(ocppo_handle *h, const float *obs, int64_t B, const uint64_t *philox_state,
+                          const int64_t *given_action, int64_t *action, float *logp, float *entropy,
+                          float *value, void *stream);
+/* philox_state[0] = seed, [1] = offset (device memory), stream-ordered. */
+int ocppo_philox_set(uint64_t *philox_state, uint64_t seed, uint64_t philox_offset, void *stream);
 /* PPObj.get_value(x), architectures/ppo.py:86-87 (ppo_atari_oc.py:534). */
 int ocppo_value(ocppo_handle *h, const float *obs, int64_t B, float *value, void *stream);
 /* Optional promise that lets forward calls skip the per-call weight preparation of the FP16 engines (max-abs, fp16 split,
@@ -176,6 +198,18 @@ int ocppo_value(ocppo_handle *h, const float *obs, int64_t B, float *value, void
  * ocppo_clip_adam and ocppo_bind_arena invalidate the preparation by themselves.  (The rollout loop of
  * ppo_atari_oc.py:500-514 calls the policy 128 times per iteration on unchanged weights.) */
 int ocppo_weights_version(ocppo_handle *h, int64_t version);
+/* 1 when the next forward call will reuse the prepared weights (see above), else 0: the launch sequence of a forward
+ * call depends on it, so a caller that replays captured CUDA graphs keys them on this. */
+int ocppo_weights_prepared(const ocppo_handle *h);
+/* CUDA-graph support.  Every compute call is capturable (asynchronous on its stream, no allocation, no sync), but the
+ * handle also keeps HOST-side bookkeeping per call (which representation of each activation the last forward left,
+ * whether the weights are prepared, the row count of the last forward).  A replayed graph redoes the device work only:
+ * save the bookkeeping right after capturing a call sequence and restore it after every replay of that graph.
+ * `buf` is host memory of ocppo_host_state_bytes() bytes; the content is opaque and only valid for the handle,
+ * workspace binding and GEMM engine it was saved under. */
+int64_t ocppo_host_state_bytes(void);
+int ocppo_host_state_save(const ocppo_handle *h, void *buf, int64_t bytes);
+int ocppo_host_state_restore(ocppo_handle *h, const void *buf, int64_t bytes);
 /* torch.distributions.Categorical(logits=...) on given logits (B,A):
  * sample / log_prob / entropy (architectures/ppo.py:92-95). */
 int ocppo_categorical(const float *logits, int64_t B, int32_t A, uint64_t seed,
@@ -211,6 +245,18 @@ int ocppo_minibatch_fwd_bwd(ocppo_handle *h, const float *b_obs, const int64_t *
 int ocppo_clip_adam(ocppo_handle *h, float inv_world, float max_grad_norm, double lr,
                     double beta1, double beta2, double eps, int64_t step, float *grad_norm,
                     void *stream);
+
+/* Writes the eight fp32 scalars the clip+Adam kernels consume to DEVICE memory
+ * (scalars8), stream-ordered; they are formed in double on the host exactly as
+ * torch/optim/adam.py does and travel as kernel arguments of a one-block
+ * kernel (no host buffer to keep alive): inv_world, max_norm, 1-beta1, beta2,
+ * 1-beta2, lr/(1-beta1^t), sqrt(1-beta2^t), eps. */
+int ocppo_adam_scalars_set(float *scalars8, float inv_world, float max_grad_norm, double lr, double beta1,
+                           double beta2, double eps, int64_t step, void *stream);
+/* ocppo_clip_adam with those scalars read from DEVICE memory (scalars8) by the
+ * kernels: graph-replayable -- LR annealing (ppo_atari_oc.py:471-474) and the
+ * step count change every call, kernel arguments of a captured graph do not. */
+int ocppo_clip_adam_dev(ocppo_handle *h, const float *scalars8, float *grad_norm, void *stream);
 
 /* ---- logged statistics -------------------------------------------------- */
 /* The two population variances of the script's explained-variance line (ppo_atari_oc.py:620-623) over the flat

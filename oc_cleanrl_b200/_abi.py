@@ -55,7 +55,9 @@ _D = C.c_double
 _SIGNATURES = {
     "ocppo_last_error": (C.c_char_p, []),
     "ocppo_version": (C.c_int, []),
+    "ocppo_bringup_build": (C.c_int, []),
     "ocppo_launch_count": (_I64, []),
+    "ocppo_launch_counts": (C.c_int, [C.POINTER(_I64), C.POINTER(_I64), _I32]),
     "ocppo_profile_enable": (C.c_int, [_I32]),
     "ocppo_profile_read": (C.c_int, [C.POINTER(_D), C.POINTER(_I64), _I32]),
     "ocppo_measure_fma_peak": (C.c_int, [C.POINTER(_D), _P]),
@@ -70,14 +72,22 @@ _SIGNATURES = {
     "ocppo_workspace_bytes": (C.c_int, [_P, _I64, _I32, C.POINTER(_I64)]),
     "ocppo_bind_workspace": (C.c_int, [_P, _P, _I64, _I64, _I32]),
     "ocppo_policy_step": (C.c_int, [_P, _P, _I64, _U64, _U64, _P, _P, _P, _P, _P, _P]),
+    "ocppo_policy_step_dev": (C.c_int, [_P, _P, _I64, _P, _P, _P, _P, _P, _P, _P]),
     "ocppo_value": (C.c_int, [_P, _P, _I64, _P, _P]),
     "ocppo_weights_version": (C.c_int, [_P, _I64]),
+    "ocppo_weights_prepared": (C.c_int, [_P]),
+    "ocppo_host_state_bytes": (_I64, []),
+    "ocppo_host_state_save": (C.c_int, [_P, _P, _I64]),
+    "ocppo_host_state_restore": (C.c_int, [_P, _P, _I64]),
     "ocppo_categorical": (C.c_int, [_P, _I64, _I32, _U64, _U64, _P, _P, _P, _P, _P]),
     "ocppo_philox_increment": (_U64, [_I64, _I32, _I32]),
     "ocppo_exponential": (C.c_int, [_P, _I64, _U64, _U64, _P]),
     "ocppo_gae": (C.c_int, [_P, _P, _P, _P, _P, _I64, _I64, _D, _D, _P, _P, _P]),
     "ocppo_minibatch_fwd_bwd": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _I64, C.POINTER(HParams), _P, _P]),
     "ocppo_clip_adam": (C.c_int, [_P, _F, _F, _D, _D, _D, _D, _I64, _P, _P]),
+    "ocppo_adam_scalars_set": (C.c_int, [_P, _F, _F, _D, _D, _D, _D, _I64, _P]),
+    "ocppo_philox_set": (C.c_int, [_P, _U64, _U64, _P]),
+    "ocppo_clip_adam_dev": (C.c_int, [_P, _P, _P, _P]),
     "ocppo_trunk_forward": (C.c_int, [_P, _P, _I64, _P, _P]),
     "ocppo_explained_variance": (C.c_int, [_P, _P, _P, _I64, _P, _P]),
     "ocppo_read_activation": (C.c_int, [_P, C.c_int32, _I64, _P, _P]),
@@ -104,7 +114,7 @@ def lib():
     return _lib
 
 
-KERNEL_CLASSES = ("gae", "sgemm_fwd", "sgemm_dgrad", "sgemm_wgrad", "heads", "aux", "clip_adam", "reserved")
+KERNEL_CLASSES = ("gae", "gemm_fwd", "gemm_dgrad", "gemm_wgrad", "heads", "aux", "clip_adam", "gemm_cuda_core")
 
 
 def profile_read():
@@ -113,6 +123,14 @@ def profile_read():
     cnt = (_I64 * 8)()
     check(lib().ocppo_profile_read(ms, cnt, 8))
     return ({k: ms[i] for i, k in enumerate(KERNEL_CLASSES)}, {k: cnt[i] for i, k in enumerate(KERNEL_CLASSES)})
+
+
+def launch_counts():
+    """-> ({class: kernels launched since load}, {class: launched under graph capture while profiling, hence untimed})."""
+    n = (_I64 * 8)()
+    u = (_I64 * 8)()
+    check(lib().ocppo_launch_counts(n, u, 8))
+    return ({k: n[i] for i, k in enumerate(KERNEL_CLASSES)}, {k: u[i] for i, k in enumerate(KERNEL_CLASSES)})
 
 
 def exported_symbols():
@@ -142,6 +160,36 @@ def make_config(frames, obs_dim, n_actions, encoder_dims, decoder_dims, device):
         cfg.decoder_dims[i] = int(d)
     cfg.device = int(device)
     return cfg
+
+
+class CapturedCall:
+    """A CUDA graph of captured libocppo calls plus the handle's host-side bookkeeping as the captured calls left it
+    (``ocppo_host_state_save``): ``replay()`` launches the graph and restores the bookkeeping."""
+
+    def __init__(self, handle_raw, graph):
+        self.handle_raw, self.graph = handle_raw, graph
+        n = lib().ocppo_host_state_bytes()
+        self.state = C.create_string_buffer(n)
+        check(lib().ocppo_host_state_save(handle_raw, self.state, n))
+
+    def replay(self):
+        self.graph.replay()
+        check(lib().ocppo_host_state_restore(self.handle_raw, self.state, len(self.state)))
+
+
+def capture(handle_raw, device, fn):
+    """Run ``fn(stream_ptr)`` (libocppo calls on the given stream) under CUDA-graph capture on a side stream of `device`
+    and return the :class:`CapturedCall`.  The graph has not run yet: call ``replay()``."""
+    import torch
+    cur = torch.cuda.current_stream(device)
+    side = torch.cuda.Stream(device)
+    side.wait_stream(cur)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(g, stream=side, capture_error_mode="thread_local"):
+            fn(C.c_void_p(side.cuda_stream))
+    cur.wait_stream(side)
+    return CapturedCall(handle_raw, g)
 
 
 class Handle:

@@ -21,7 +21,6 @@ from __future__ import annotations
 import ctypes as C
 
 import numpy as np
-import os
 
 import torch
 import torch.nn as nn
@@ -98,6 +97,11 @@ class PPObj(Predictor):
         self._ws_training = False
         self._fwd_version = 0
         self._manual_version = 0
+        # forward passes over more rows than this run in chunks inside the library (ocppo_policy_step / ocppo_value), so
+        # one large no-grad call never sizes the workspace -- and with it the training chunk -- by its batch
+        self.inference_chunk_rows = 65536
+        self._graphs = {}           # CUDA graphs of the fused rollout step, keyed by the pointers they were captured on
+        self._philox_dev = None     # (seed, offset) the graph-replayed head kernel reads
 
     # ---- arena management ---------------------------------------------------
     def _apply(self, fn, *args, **kwargs):
@@ -145,17 +149,47 @@ class PPObj(Predictor):
                 "oc_cleanrl_b200.PPObj has no CPU path: move the agent to a CUDA (sm_100) device first")
         return self._handle
 
-    def _ensure_workspace(self, rows, training):
+    def _ensure_workspace(self, rows, training, exact=False):
+        """Bind a workspace for chunks of `rows` samples.
+
+        * inference (``training=False``): the library chunks ``ocppo_policy_step`` / ``ocppo_value`` by whatever is bound,
+          so a bound TRAINING workspace is used as it is, and otherwise the request is capped at ``inference_chunk_rows``
+          and only grows the binding -- one large no-grad call never sizes the workspace by its batch;
+        * ``exact=True`` (the fused learner): binds exactly `rows`, so the update runs with the chunk that was asked for,
+          whatever forward calls came before;
+        * training without ``exact`` (the autograd bridge): grows to at least `rows`."""
         h = self._require_handle()
-        if self._workspace is not None and rows <= self._ws_rows and (self._ws_training or not training):
-            return
-        rows = max(int(rows), self._ws_rows)
-        training = bool(training or self._ws_training)
+        rows = int(rows)
+        have = self._workspace is not None
+        if not training:
+            if have and self._ws_training:
+                return
+            rows = min(rows, int(self.inference_chunk_rows))
+            if have and rows <= self._ws_rows:
+                return
+            rows = max(rows, self._ws_rows)
+        elif exact:
+            if have and self._ws_training and self._ws_rows == rows:
+                return
+        else:
+            if have and self._ws_training and rows <= self._ws_rows:
+                return
+            rows = max(rows, self._ws_rows)
         nbytes = h.workspace_bytes(rows, training)
         self._workspace = None
+        self._graphs.clear()        # captured launches point into the old workspace
         ws = torch.empty(nbytes, dtype=torch.uint8, device=self._cuda_device)
         _abi.check(_abi.lib().ocppo_bind_workspace(h.raw, _abi.ptr(ws), nbytes, rows, int(training)))
-        self._workspace, self._ws_rows, self._ws_training = ws, rows, training
+        self._workspace, self._ws_rows, self._ws_training = ws, rows, bool(training)
+
+    @property
+    def workspace_rows(self):
+        """Rows per forward / backward chunk of the bound workspace (0: none bound yet)."""
+        return self._ws_rows
+
+    @property
+    def workspace_bytes(self):
+        return 0 if self._workspace is None else int(self._workspace.numel())
 
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self._cuda_device).cuda_stream)
@@ -198,8 +232,6 @@ class PPObj(Predictor):
         then skip their per-call weight preparation.  The counter is the sum of torch's version counters of the parameters,
         which every in-place op on a parameter (optimizer steps, ``load_state_dict``, ``copy_``) increments; writes
         through ``param.data`` or straight into ``self.arena`` bypass it -- call :meth:`weights_changed` after those."""
-        if os.environ.get("OCPPO_NOHINT"):        # bisecting knob
-            return
         # the parameters were re-pointed at the arena through ``.data`` (which keeps each parameter's own version
         # counter), so the arena's change counter is the sum of theirs
         version = sum(p._version for p in self.parameters()) + self._manual_version
@@ -230,20 +262,46 @@ class PPObj(Predictor):
                 action = probs.sample()
             return action, probs.log_prob(action), probs.entropy(), self.critic(hidden)
         B = x.shape[0]
-        self._ensure_workspace(B, training=False)
-        self._hint_weights()
         dev = x.device
         out_action = torch.empty(B, dtype=torch.int64, device=dev)
         logp = torch.empty(B, dtype=torch.float32, device=dev)
         entropy = torch.empty(B, dtype=torch.float32, device=dev)
         value = torch.empty((B, 1), dtype=torch.float32, device=dev)
-        given = None
+        self.policy_step_into(x, out_action, logp, entropy, value, given=action)
+        return out_action, logp, entropy, value
+
+    def policy_step_into(self, x, action, logp, entropy, value, given=None, graph=False):
+        """ppo.py:89-95 under ``no_grad`` with caller-owned outputs (int64 (B,), fp32 (B,), fp32 (B,), fp32 (B,) or
+        (B, 1)): the fused kernel writes e.g. ``actions[step]`` / ``logprobs[step]`` / ``values[step]`` of the rollout
+        buffers in place (ppo_atari_oc.py:506-509 are three copies).  ``graph=True`` replays the launches of the call from
+        a CUDA graph captured on first use for these pointers (buffers that persist across iterations, as the rollout
+        buffers do); the Philox (seed, offset) pair then lives in device memory and is refreshed before each replay."""
+        B = x.shape[0]
+        self._ensure_workspace(B, training=False)
+        self._hint_weights()
+        lib, h = _abi.lib(), self._handle.raw
         seed = offset = 0
-        if action is None:
+        if given is None:
             seed, offset = self._philox_state(B * self._n_actions)
         else:
-            given = action.to(device=dev, dtype=torch.int64).contiguous()
-        _abi.check(_abi.lib().ocppo_policy_step(self._handle.raw, _abi.ptr(x), B, seed, offset, _abi.ptr(given),
-                                               _abi.ptr(out_action), _abi.ptr(logp), _abi.ptr(entropy),
-                                               _abi.ptr(value), self._stream()))
-        return out_action, logp, entropy, value
+            given = given.to(device=x.device, dtype=torch.int64).contiguous()
+        if not graph or given is not None:
+            _abi.check(lib.ocppo_policy_step(h, _abi.ptr(x), B, seed, offset, _abi.ptr(given), _abi.ptr(action),
+                                             _abi.ptr(logp), _abi.ptr(entropy), _abi.ptr(value), self._stream()))
+            return
+        if self._philox_dev is None:
+            self._philox_dev = torch.zeros(2, dtype=torch.int64, device=self._cuda_device)
+        _abi.check(lib.ocppo_philox_set(_abi.ptr(self._philox_dev), seed, offset, self._stream()))
+        # the launch sequence depends on whether the prepared weights can be reused (ocppo_weights_version), so that
+        # state is part of the key: a graph captured with the preparation in it is replayed only when it is needed
+        prepared = bool(lib.ocppo_weights_prepared(h))
+        key = ("policy", x.data_ptr(), B, action.data_ptr(), logp.data_ptr(), entropy.data_ptr(), value.data_ptr(), prepared,
+               lib.ocppo_get_gemm_mode())
+        g = self._graphs.get(key)
+        if g is None:
+            if len(self._graphs) >= 1024:
+                self._graphs.clear()
+            g = self._graphs[key] = _abi.capture(h, self._cuda_device, lambda stream: _abi.check(
+                lib.ocppo_policy_step_dev(h, _abi.ptr(x), B, _abi.ptr(self._philox_dev), None, _abi.ptr(action),
+                                          _abi.ptr(logp), _abi.ptr(entropy), _abi.ptr(value), stream)))
+        g.replay()

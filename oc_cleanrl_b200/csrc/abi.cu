@@ -16,28 +16,77 @@ void set_error(const char *fmt, ...) {
     va_end(ap);
 }
 
-// Live timing: when enabled every launch wrapper is bracketed by a pair of events on
-// its own stream; ocppo_profile_read() sums elapsed time per kernel class.
-static const int kProfMaxPairs = 8192;
+// Live timing: when enabled every launch wrapper is bracketed by a pair of events on its own stream.  The pairs sit
+// in a small ring; whenever it fills (and on ocppo_profile_read) the ring is DRAINED into per-class sums -- a host-side
+// wait, taken in measurement runs only -- so no launch is ever dropped: timed[] always equals the launches made while
+// profiling was on.  Launches issued while their stream is being captured into a CUDA graph cannot carry events; they
+// are counted in uncaptured[] so a reader can tell.
+static const int kProfRing = 2048;
 static struct {
     bool on = false;
     int n = 0;
-    cudaEvent_t start[kProfMaxPairs], stop[kProfMaxPairs];
-    int cls[kProfMaxPairs];
+    bool open = false;                 // prof_begin recorded a start event that prof_end has to close
+    cudaEvent_t start[kProfRing], stop[kProfRing];
+    int cls[kProfRing], nk[kProfRing];
     bool created = false;
     int64_t launches[KC_COUNT] = {0};
+    double ms[KC_COUNT] = {0};
+    int64_t timed[KC_COUNT] = {0};
+    int64_t skipped[KC_COUNT] = {0};   // profiling on, but the stream was capturing
 } g_prof;
+
+static int prof_drain() {
+    for (int i = 0; i < g_prof.n; ++i) {
+        OCPPO_CUDA(cudaEventSynchronize(g_prof.stop[i]));
+        float ms = 0;
+        OCPPO_CUDA(cudaEventElapsedTime(&ms, g_prof.start[i], g_prof.stop[i]));
+        g_prof.ms[g_prof.cls[i]] += ms;
+        g_prof.timed[g_prof.cls[i]] += g_prof.nk[i];
+    }
+    g_prof.n = 0;
+    return OCPPO_OK;
+}
 
 void prof_begin(int cls, int n_kernels, cudaStream_t s) {
     g_prof.launches[cls] += n_kernels;
-    if (!g_prof.on || g_prof.n >= kProfMaxPairs) return;
+    g_prof.open = false;
+    if (!g_prof.on) return;
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) {
+        g_prof.skipped[cls] += n_kernels;
+        return;
+    }
+    if (g_prof.n >= kProfRing) prof_drain();
     g_prof.cls[g_prof.n] = cls;
+    g_prof.nk[g_prof.n] = n_kernels;
     cudaEventRecord(g_prof.start[g_prof.n], s);
+    g_prof.open = true;
 }
 void prof_end(cudaStream_t s) {
-    if (!g_prof.on || g_prof.n >= kProfMaxPairs) return;
+    if (!g_prof.open) return;
     cudaEventRecord(g_prof.stop[g_prof.n], s);
     ++g_prof.n;
+    g_prof.open = false;
+}
+
+// Every entry point that takes a handle makes the handle's device current for the duration of the call (and restores
+// the caller's): a drop-in agent on cuda:k must work without the caller ever calling cudaSetDevice (the reference's
+// multi-GPU script never does, ppo_atari_multigpu.py:216-222).
+struct DeviceGuard {
+    int prev = -1;
+    bool switched = false;
+    explicit DeviceGuard(int dev) {
+        if (dev < 0) return;
+        if (cudaGetDevice(&prev) == cudaSuccess && prev != dev) switched = cudaSetDevice(dev) == cudaSuccess;
+    }
+    ~DeviceGuard() { if (switched) cudaSetDevice(prev); }
+};
+// stateless entry points (no handle): the device that owns the first data pointer
+static int device_of(const void *p) {
+    cudaPointerAttributes at;
+    if (p != nullptr && cudaPointerGetAttributes(&at, p) == cudaSuccess && at.type == cudaMemoryTypeDevice) return at.device;
+    cudaGetLastError();
+    return -1;
 }
 
 static inline cudaStream_t as_stream(void *s) { return reinterpret_cast<cudaStream_t>(s); }
@@ -138,8 +187,8 @@ static int64_t carve(ocppo_handle *h, void *base, int64_t R, int training, bool 
     }
     t->amax = cv.take<float>(kAmaxSlots);
     t->w_amax_valid = 0;
-    t->w16_hi = cv.take<uint16_t>(h->param_floats);
-    t->w16_lo = cv.take<uint16_t>(h->param_floats);
+    t->w16_hi = cv.take<uint16_t>(h->arena_floats);     // indexed by ARENA offsets (alignment padding included)
+    t->w16_lo = cv.take<uint16_t>(h->arena_floats);
     const int AP = (int)round_up(c.n_actions + 1, 4);
     if ((int64_t)AP * h->hidden > max_w) max_w = (int64_t)AP * h->hidden;
     if (AP > max_out) max_out = AP;
@@ -611,7 +660,14 @@ using namespace ocppo;
 extern "C" {
 
 const char *ocppo_last_error(void) { return g_err; }
-int ocppo_version(void) { return 100; }
+int ocppo_version(void) { return 200; }
+int ocppo_bringup_build(void) {
+#ifdef OCPPO_BRINGUP
+    return 1;
+#else
+    return 0;
+#endif
+}
 
 int64_t ocppo_launch_count(void) {
     int64_t t = 0;
@@ -631,6 +687,7 @@ int ocppo_gemm(int32_t op, int32_t engine, int32_t M, int32_t N, int64_t K, cons
                float *bias_part, int32_t splits, int64_t k_per_split, void *stream) {
     OCPPO_CHECK_ARG(op >= 0 && op <= 2 && engine >= 0 && engine <= 8, "bad op/engine");
     OCPPO_CHECK_ARG(A && B && C, "null pointer");
+    DeviceGuard dg(device_of(C));
     SgemmArgs a{};
     a.A = A; a.lda = lda; a.B = B; a.ldb = ldb; a.C = C; a.ldc = ldc; a.bias = bias; a.mask = mask;
     a.bias_part = bias_part; a.M = M; a.N = N; a.K = K; a.splits = splits < 1 ? 1 : splits;
@@ -699,28 +756,36 @@ int ocppo_measure_fma_peak(double *tflops, void *stream) {
 
 int ocppo_profile_enable(int32_t on) {
     if (on && !g_prof.created) {
-        for (int i = 0; i < kProfMaxPairs; ++i) {
+        for (int i = 0; i < kProfRing; ++i) {
             OCPPO_CUDA(cudaEventCreate(&g_prof.start[i]));
             OCPPO_CUDA(cudaEventCreate(&g_prof.stop[i]));
         }
         g_prof.created = true;
     }
+    if (g_prof.n > 0) OCPPO_TRY(prof_drain());
     g_prof.on = on != 0;
-    g_prof.n = 0;
+    g_prof.open = false;
+    for (int i = 0; i < KC_COUNT; ++i) { g_prof.ms[i] = 0; g_prof.timed[i] = 0; g_prof.skipped[i] = 0; }
     return OCPPO_OK;
 }
 
 int ocppo_profile_read(double *ms_by_class, int64_t *timed_by_class, int32_t n_classes) {
     OCPPO_CHECK_ARG(ms_by_class != nullptr && n_classes >= KC_COUNT, "need %d class slots", (int)KC_COUNT);
-    for (int i = 0; i < n_classes; ++i) { ms_by_class[i] = 0; if (timed_by_class) timed_by_class[i] = 0; }
-    for (int i = 0; i < g_prof.n; ++i) {
-        OCPPO_CUDA(cudaEventSynchronize(g_prof.stop[i]));
-        float ms = 0;
-        OCPPO_CUDA(cudaEventElapsedTime(&ms, g_prof.start[i], g_prof.stop[i]));
-        ms_by_class[g_prof.cls[i]] += ms;
-        if (timed_by_class) timed_by_class[g_prof.cls[i]] += 1;
+    OCPPO_TRY(prof_drain());
+    for (int i = 0; i < n_classes; ++i) {
+        ms_by_class[i] = i < KC_COUNT ? g_prof.ms[i] : 0;
+        if (timed_by_class) timed_by_class[i] = i < KC_COUNT ? g_prof.timed[i] : 0;
     }
-    g_prof.n = 0;
+    for (int i = 0; i < KC_COUNT; ++i) { g_prof.ms[i] = 0; g_prof.timed[i] = 0; }
+    return OCPPO_OK;
+}
+
+int ocppo_launch_counts(int64_t *launches_by_class, int64_t *untimed_by_class, int32_t n_classes) {
+    OCPPO_CHECK_ARG(launches_by_class != nullptr && n_classes >= KC_COUNT, "need %d class slots", (int)KC_COUNT);
+    for (int i = 0; i < n_classes; ++i) {
+        launches_by_class[i] = i < KC_COUNT ? g_prof.launches[i] : 0;
+        if (untimed_by_class) untimed_by_class[i] = i < KC_COUNT ? g_prof.skipped[i] : 0;
+    }
     return OCPPO_OK;
 }
 
@@ -794,6 +859,53 @@ int ocppo_weights_version(ocppo_handle *h, int64_t version) {
     return OCPPO_OK;
 }
 
+int ocppo_weights_prepared(const ocppo_handle *h) {
+    if (h == nullptr) return 0;
+    return g_gemm_mode >= 5 && h->w_version >= 0 && h->w_prepared_mode == g_gemm_mode && h->w_amax_valid;
+}
+
+// Host-side bookkeeping a forward / backward / optimizer call leaves in the handle (which representation of each
+// activation is valid, whether the weights are prepared, ...).  A CUDA graph replays the device work of a captured
+// call but not this; the caller saves it right after capture and restores it after every replay.
+namespace {
+struct HostState {
+    int w_amax_valid, w_prepared_mode, last_forward_rows, x0p_valid;
+    int act_amax_valid[2 * OCPPO_MAX_LAYERS], act16_valid[2 * OCPPO_MAX_LAYERS], act32_valid[2 * OCPPO_MAX_LAYERS];
+    int relu_bits_valid[2 * OCPPO_MAX_LAYERS];
+    const float *act_scale[2 * OCPPO_MAX_LAYERS];
+};
+}  // namespace
+
+int64_t ocppo_host_state_bytes(void) { return (int64_t)sizeof(HostState); }
+
+int ocppo_host_state_save(const ocppo_handle *h, void *buf, int64_t bytes) {
+    OCPPO_CHECK_ARG(h != nullptr && buf != nullptr && bytes >= (int64_t)sizeof(HostState), "host_state_save: bad argument");
+    HostState st{};
+    st.w_amax_valid = h->w_amax_valid; st.w_prepared_mode = h->w_prepared_mode;
+    st.last_forward_rows = h->last_forward_rows; st.x0p_valid = h->x0p_valid;
+    for (int l = 0; l < 2 * OCPPO_MAX_LAYERS; ++l) {
+        st.act_amax_valid[l] = h->act_amax_valid[l]; st.act16_valid[l] = h->act16_valid[l];
+        st.act32_valid[l] = h->act32_valid[l]; st.relu_bits_valid[l] = h->relu_bits_valid[l];
+        st.act_scale[l] = h->act_scale[l];
+    }
+    memcpy(buf, &st, sizeof(st));
+    return OCPPO_OK;
+}
+
+int ocppo_host_state_restore(ocppo_handle *h, const void *buf, int64_t bytes) {
+    OCPPO_CHECK_ARG(h != nullptr && buf != nullptr && bytes >= (int64_t)sizeof(HostState), "host_state_restore: bad argument");
+    HostState st;
+    memcpy(&st, buf, sizeof(st));
+    h->w_amax_valid = st.w_amax_valid; h->w_prepared_mode = st.w_prepared_mode;
+    h->last_forward_rows = st.last_forward_rows; h->x0p_valid = st.x0p_valid;
+    for (int l = 0; l < 2 * OCPPO_MAX_LAYERS; ++l) {
+        h->act_amax_valid[l] = st.act_amax_valid[l]; h->act16_valid[l] = st.act16_valid[l];
+        h->act32_valid[l] = st.act32_valid[l]; h->relu_bits_valid[l] = st.relu_bits_valid[l];
+        h->act_scale[l] = st.act_scale[l];
+    }
+    return OCPPO_OK;
+}
+
 int ocppo_workspace_bytes(const ocppo_handle *h, int64_t max_rows, int32_t training, int64_t *bytes) {
     OCPPO_CHECK_ARG(h != nullptr && bytes != nullptr, "null argument");
     OCPPO_CHECK_ARG(max_rows >= 1, "max_rows must be >= 1");
@@ -814,17 +926,18 @@ int ocppo_bind_workspace(ocppo_handle *h, void *workspace, int64_t bytes, int64_
     return OCPPO_OK;
 }
 
-int ocppo_policy_step(ocppo_handle *h, const float *obs, int64_t B, uint64_t seed, uint64_t philox_offset,
-                      const int64_t *given_action, int64_t *action, float *logp, float *entropy, float *value,
-                      void *stream) {
+static int policy_step(ocppo_handle *h, const float *obs, int64_t B, uint64_t seed, uint64_t philox_offset,
+                       const uint64_t *philox_dev, const int64_t *given_action, int64_t *action, float *logp,
+                       float *entropy, float *value, void *stream) {
     OCPPO_TRY(require_ready(h, false));
+    DeviceGuard dg(h->cfg.device);
     OCPPO_CHECK_ARG(B >= 0 && (obs != nullptr || B == 0), "bad obs/B");
     cudaStream_t s = as_stream(stream);
     const int64_t row_floats = (int64_t)h->cfg.frames * h->cfg.obs_dim;
     for (int64_t c0 = 0; c0 < B; c0 += h->max_rows) {
         const int64_t rows = B - c0 < h->max_rows ? B - c0 : h->max_rows;
         OCPPO_TRY(trunk_forward(h, obs + c0 * row_floats, rows, s));
-        OCPPO_TRY(launch_policy_head(h, h->act[h->n_layers - 1], rows, c0, B, seed, philox_offset,
+        OCPPO_TRY(launch_policy_head(h, h->act[h->n_layers - 1], rows, c0, B, seed, philox_offset, philox_dev,
                                      given_action ? given_action + c0 : nullptr, action ? action + c0 : nullptr,
                                      logp ? logp + c0 : nullptr, entropy ? entropy + c0 : nullptr,
                                      value ? value + c0 : nullptr, 1, s));
@@ -832,15 +945,29 @@ int ocppo_policy_step(ocppo_handle *h, const float *obs, int64_t B, uint64_t see
     return OCPPO_OK;
 }
 
+int ocppo_policy_step(ocppo_handle *h, const float *obs, int64_t B, uint64_t seed, uint64_t philox_offset,
+                      const int64_t *given_action, int64_t *action, float *logp, float *entropy, float *value,
+                      void *stream) {
+    return policy_step(h, obs, B, seed, philox_offset, nullptr, given_action, action, logp, entropy, value, stream);
+}
+
+int ocppo_policy_step_dev(ocppo_handle *h, const float *obs, int64_t B, const uint64_t *philox_state,
+                          const int64_t *given_action, int64_t *action, float *logp, float *entropy, float *value,
+                          void *stream) {
+    OCPPO_CHECK_ARG(philox_state != nullptr || given_action != nullptr, "policy_step_dev: null philox_state");
+    return policy_step(h, obs, B, 0, 0, philox_state, given_action, action, logp, entropy, value, stream);
+}
+
 int ocppo_value(ocppo_handle *h, const float *obs, int64_t B, float *value, void *stream) {
     OCPPO_TRY(require_ready(h, false));
+    DeviceGuard dg(h->cfg.device);
     OCPPO_CHECK_ARG(B >= 0 && value != nullptr && (obs != nullptr || B == 0), "bad argument");
     cudaStream_t s = as_stream(stream);
     const int64_t row_floats = (int64_t)h->cfg.frames * h->cfg.obs_dim;
     for (int64_t c0 = 0; c0 < B; c0 += h->max_rows) {
         const int64_t rows = B - c0 < h->max_rows ? B - c0 : h->max_rows;
         OCPPO_TRY(trunk_forward(h, obs + c0 * row_floats, rows, s));
-        OCPPO_TRY(launch_policy_head(h, h->act[h->n_layers - 1], rows, c0, B, 0, 0, nullptr, nullptr, nullptr,
+        OCPPO_TRY(launch_policy_head(h, h->act[h->n_layers - 1], rows, c0, B, 0, 0, nullptr, nullptr, nullptr, nullptr,
                                      nullptr, value + c0, 0, s));
     }
     return OCPPO_OK;
@@ -850,6 +977,7 @@ int ocppo_categorical(const float *logits, int64_t B, int32_t A, uint64_t seed, 
                       const int64_t *given_action, int64_t *action, float *logp, float *entropy, void *stream) {
     OCPPO_CHECK_ARG(B >= 0 && A >= 1 && A <= 32, "bad B/A");
     OCPPO_CHECK_ARG(logits != nullptr || B == 0, "null logits");
+    DeviceGuard dg(device_of(logits));
     return launch_categorical(logits, B, A, seed, philox_offset, given_action, action, logp, entropy,
                               as_stream(stream));
 }
@@ -864,6 +992,7 @@ uint64_t ocppo_philox_increment(int64_t numel, int32_t sm_count, int32_t max_thr
 
 int ocppo_exponential(float *out, int64_t numel, uint64_t seed, uint64_t philox_offset, void *stream) {
     OCPPO_CHECK_ARG(numel >= 0 && (out != nullptr || numel == 0), "bad argument");
+    DeviceGuard dg(device_of(out));
     return launch_exponential(out, numel, seed, philox_offset, as_stream(stream));
 }
 
@@ -874,6 +1003,7 @@ int ocppo_gae(const float *rewards, const float *values, const float *dones, con
     if (T == 0 || N == 0) return OCPPO_OK;
     OCPPO_CHECK_ARG(rewards && values && dones && next_value && next_done && advantages && returns,
                     "null pointer");
+    DeviceGuard dg(device_of(rewards));
     return launch_gae(rewards, values, dones, next_value, next_done, T, N, (float)gamma,
                       (float)(gamma * gae_lambda), advantages, returns, as_stream(stream));
 }
@@ -882,6 +1012,7 @@ int ocppo_minibatch_fwd_bwd(ocppo_handle *h, const float *b_obs, const int64_t *
                             const float *b_advantages, const float *b_returns, const float *b_values,
                             const int64_t *idx, int64_t mb, const ocppo_hparams *hp, float *stats, void *stream) {
     OCPPO_TRY(require_ready(h, true));
+    DeviceGuard dg(h->cfg.device);
     OCPPO_CHECK_ARG(mb >= 1, "minibatch size must be >= 1");
     OCPPO_CHECK_ARG(b_obs && b_actions && b_logprobs && b_advantages && b_returns && b_values && idx && hp && stats,
                     "null pointer");
@@ -952,21 +1083,51 @@ int ocppo_minibatch_fwd_bwd(ocppo_handle *h, const float *b_obs, const int64_t *
 int ocppo_clip_adam(ocppo_handle *h, float inv_world, float max_grad_norm, double lr, double beta1, double beta2,
                     double eps, int64_t step, float *grad_norm, void *stream) {
     OCPPO_TRY(require_ready(h, true));
+    DeviceGuard dg(h->cfg.device);
     OCPPO_CHECK_ARG(step >= 1, "Adam step is 1-based");
     OCPPO_CHECK_ARG(h->grads && h->exp_avg && h->exp_avg_sq, "grad/Adam arenas not bound");
     h->w_amax_valid = 0;
-    return launch_clip_adam(h, inv_world, max_grad_norm, lr, beta1, beta2, eps, step, grad_norm, as_stream(stream));
+    float sc[8];
+    adam_scalars(inv_world, max_grad_norm, lr, beta1, beta2, eps, step, sc);
+    return launch_clip_adam(h, sc, nullptr, grad_norm, as_stream(stream));
+}
+
+int ocppo_adam_scalars_set(float *scalars8, float inv_world, float max_grad_norm, double lr, double beta1, double beta2,
+                           double eps, int64_t step, void *stream) {
+    OCPPO_CHECK_ARG(scalars8 != nullptr && step >= 1, "adam_scalars_set: bad argument");
+    DeviceGuard dg(device_of(scalars8));
+    float sc[8];
+    adam_scalars(inv_world, max_grad_norm, lr, beta1, beta2, eps, step, sc);
+    return launch_store_words(scalars8, sc, 8, as_stream(stream));
+}
+
+int ocppo_philox_set(uint64_t *philox_state, uint64_t seed, uint64_t philox_offset, void *stream) {
+    OCPPO_CHECK_ARG(philox_state != nullptr, "philox_set: null pointer");
+    DeviceGuard dg(device_of(philox_state));
+    const uint64_t w[2] = {seed, philox_offset};
+    return launch_store_words(philox_state, w, 4, as_stream(stream));
+}
+
+int ocppo_clip_adam_dev(ocppo_handle *h, const float *scalars8, float *grad_norm, void *stream) {
+    OCPPO_TRY(require_ready(h, true));
+    DeviceGuard dg(h->cfg.device);
+    OCPPO_CHECK_ARG(scalars8 != nullptr, "clip_adam_dev: null scalars");
+    OCPPO_CHECK_ARG(h->grads && h->exp_avg && h->exp_avg_sq, "grad/Adam arenas not bound");
+    h->w_amax_valid = 0;
+    return launch_clip_adam(h, nullptr, scalars8, grad_norm, as_stream(stream));
 }
 
 int ocppo_explained_variance(ocppo_handle *h, const float *values, const float *returns, int64_t n, float *out2,
                              void *stream) {
     OCPPO_TRY(require_ready(h, true));
+    DeviceGuard dg(h->cfg.device);
     OCPPO_CHECK_ARG(values && returns && out2 && n >= 1, "explained_variance: bad argument");
     return launch_explained_var(h, values, returns, n, out2, as_stream(stream));
 }
 
 int ocppo_trunk_forward(ocppo_handle *h, const float *obs, int64_t B, float *hidden, void *stream) {
     OCPPO_TRY(require_ready(h, false));
+    DeviceGuard dg(h->cfg.device);
     OCPPO_CHECK_ARG(B >= 1 && B <= h->max_rows, "trunk_forward: B=%lld must be in [1,%lld]", (long long)B,
                     (long long)h->max_rows);
     OCPPO_CHECK_ARG(obs && hidden, "null pointer");
@@ -979,6 +1140,7 @@ int ocppo_trunk_forward(ocppo_handle *h, const float *obs, int64_t B, float *hid
 
 int ocppo_trunk_backward(ocppo_handle *h, const float *obs, int64_t B, const float *d_hidden, void *stream) {
     OCPPO_TRY(require_ready(h, true));
+    DeviceGuard dg(h->cfg.device);
     OCPPO_CHECK_ARG(B >= 1 && B == h->last_forward_rows, "trunk_backward: B=%lld does not match last forward (%d)",
                     (long long)B, h->last_forward_rows);
     OCPPO_CHECK_ARG(obs && d_hidden, "null pointer");
@@ -989,6 +1151,7 @@ int ocppo_trunk_backward(ocppo_handle *h, const float *obs, int64_t B, const flo
 
 int ocppo_read_activation(const ocppo_handle *h, int32_t layer, int64_t B, float *out, void *stream) {
     OCPPO_TRY(require_ready(h, false));
+    DeviceGuard dg(h->cfg.device);
     OCPPO_CHECK_ARG(out, "null pointer");
     OCPPO_CHECK_ARG(layer >= 0 && layer < h->n_layers, "read_activation: layer %d not in [0,%d)", layer, h->n_layers);
     OCPPO_CHECK_ARG(B >= 1 && B == h->last_forward_rows, "read_activation: B=%lld does not match last forward (%d)",

@@ -46,7 +46,7 @@ void set_error(const char *fmt, ...);
 
 // ---- launch accounting / live per-class kernel timing (bench.py roofline) ----
 enum KernelClass { KC_GAE = 0, KC_SGEMM_FWD = 1, KC_SGEMM_DGRAD = 2, KC_SGEMM_WGRAD = 3, KC_HEAD = 4,
-                   KC_AUX = 5, KC_ADAM = 6, KC_COUNT = 8 };
+                   KC_AUX = 5, KC_ADAM = 6, KC_GEMM_CUDA_CORE = 7, KC_COUNT = 8 };
 void prof_begin(int cls, int n_kernels, cudaStream_t s);
 void prof_end(cudaStream_t s);
 struct ProfScope {
@@ -58,6 +58,7 @@ struct ProfScope {
 static inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
 static inline int64_t ceil_div(int64_t x, int64_t m) { return (x + m - 1) / m; }
 
+constexpr int kMaxDevices = 64;           // per-device caches of function attributes / SM counts
 constexpr int kArenaAlignFloats = 32;      // every tensor starts 128 B aligned
 constexpr int kSkinnyMaxIn = 96;           // widest layer input the skinny weight-gradient route takes (32 columns per pass; beyond 3 passes the tiled GEMM wins)
 constexpr int kSplitMax = 32;              // max split-K factor of the wgrad kernels
@@ -265,8 +266,8 @@ struct LossArgs {
 };
 
 int launch_policy_head(const ocppo_handle *h, const float *hidden, int64_t B, int64_t row_base, int64_t total_B,
-                       uint64_t seed, uint64_t offset, const int64_t *given, int64_t *action, float *logp,
-                       float *entropy, float *value, int want_policy, cudaStream_t stream);
+                       uint64_t seed, uint64_t offset, const uint64_t *philox_dev, const int64_t *given, int64_t *action,
+                       float *logp, float *entropy, float *value, int want_policy, cudaStream_t stream);
 int launch_categorical(const float *logits, int64_t B, int A, uint64_t seed, uint64_t offset, const int64_t *given,
                        int64_t *action, float *logp, float *entropy, cudaStream_t stream);
 int launch_exponential(float *out, int64_t numel, uint64_t seed, uint64_t offset, cudaStream_t stream);
@@ -290,7 +291,9 @@ int launch_skinny_reduce(const float *part, int G, int nw, int NS, int i0, int i
                          int accumulate, cudaStream_t stream);
 int launch_relu_mask(const float *g, const float *act, int64_t n, float *out, int sm_count, cudaStream_t stream);
 int measure_fma_peak(double *tflops, cudaStream_t stream);
-int launch_clip_adam(ocppo_handle *h, float inv_world, float max_norm, double lr, double beta1, double beta2,
-                     double eps, int64_t step, float *grad_norm, cudaStream_t stream);
+int launch_store_words(void *dst, const void *words, int n, cudaStream_t stream);     // n <= 8 32-bit words
+void adam_scalars(float inv_world, float max_norm, double lr, double beta1, double beta2, double eps, int64_t step, float *out8);
+// exactly one of host8 / dev8 (device memory, read by the kernels: graph-replayable) carries the eight scalars
+int launch_clip_adam(ocppo_handle *h, const float *host8, const float *dev8, float *grad_norm, cudaStream_t stream);
 
 }  // namespace ocppo

@@ -206,7 +206,11 @@ int launch_gae(const float *rewards, const float *values, const float *dones,
     OCPPO_CHECK_ARG(grid <= 0x7fffffff, "gae: num_envs too large");
     const bool vec = (N % 4 == 0) && ((((uintptr_t)rewards | (uintptr_t)values | (uintptr_t)dones | (uintptr_t)adv |
                                        (uintptr_t)ret) & 15) == 0);
-    static bool attr_done = false;
+    static bool attr_done_of[kMaxDevices] = {false};     // a function attribute lives in the device's context
+    int dev = 0;
+    OCPPO_CUDA(cudaGetDevice(&dev));
+    OCPPO_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "gae: device ordinal %d out of range", dev);
+    bool &attr_done = attr_done_of[dev];
     if (!attr_done) {
         OCPPO_CUDA(cudaFuncSetAttribute(gae_scan_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         OCPPO_CUDA(cudaFuncSetAttribute(gae_scan_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

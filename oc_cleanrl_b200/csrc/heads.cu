@@ -7,6 +7,7 @@
 #include "common.cuh"
 #include "philox.cuh"
 #include <math_constants.h>
+#include <string.h>
 
 namespace ocppo {
 
@@ -127,10 +128,12 @@ __device__ __forceinline__ void head_forward_vec(const float4 (&hv)[NV], const f
 template <int HV>
 __global__ void __launch_bounds__(kHeadThreads)
 policy_head_kernel(const float *__restrict__ hidden, int64_t B, int H, int A, const float *Wa, const float *ba,
-                   const float *Wc, const float *bc, PhiloxLayout L, int64_t row_base,
+                   const float *Wc, const float *bc, PhiloxLayout L, const uint64_t *__restrict__ philox_dev, int64_t row_base,
                    const int64_t *__restrict__ given, int64_t *__restrict__ action, float *__restrict__ logp,
                    float *__restrict__ entropy, float *__restrict__ value, int want_policy) {
     extern __shared__ __align__(16) float sm[];
+    // graph-replayable calls keep (seed, offset) in device memory: kernel arguments are frozen at capture time
+    if (philox_dev != nullptr) { L.seed = __ldg(philox_dev); L.offset = __ldg(philox_dev + 1); }
     float *sW = sm, *sB = sm + (size_t)(A + 1) * H;
     stage_head_weights(sW, sB, Wa, ba, Wc, bc, A, H);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -537,7 +540,9 @@ __global__ void relu_mask_kernel(const float *__restrict__ g, const float *__res
 namespace {
 
 __global__ void __launch_bounds__(256)
-sumsq_kernel(const float *__restrict__ g, int64_t n, float inv_world, double *__restrict__ part) {
+sumsq_kernel(const float *__restrict__ g, int64_t n, float inv_world, const float *__restrict__ dev_scalars,
+             double *__restrict__ part) {
+    if (dev_scalars != nullptr) inv_world = __ldg(dev_scalars);
     double s = 0;
     const int64_t n4 = n >> 2;
     const float4 *g4 = reinterpret_cast<const float4 *>(g);
@@ -565,10 +570,16 @@ struct AdamArgs {
     int n_part;
     float inv_world, max_norm, one_minus_b1, b2, one_minus_b2, step_size, bc2_sqrt, eps;
     float *grad_norm;
+    const float *dev_scalars;     // graph-replayable calls: the eight scalars above in device memory (ocppo_adam_scalars order)
 };
 
 __global__ void __launch_bounds__(256) adam_kernel(AdamArgs a) {
     __shared__ float s_coef;
+    if (a.dev_scalars != nullptr) {
+        a.inv_world = __ldg(a.dev_scalars + 0); a.max_norm = __ldg(a.dev_scalars + 1); a.one_minus_b1 = __ldg(a.dev_scalars + 2);
+        a.b2 = __ldg(a.dev_scalars + 3); a.one_minus_b2 = __ldg(a.dev_scalars + 4); a.step_size = __ldg(a.dev_scalars + 5);
+        a.bc2_sqrt = __ldg(a.dev_scalars + 6); a.eps = __ldg(a.dev_scalars + 7);
+    }
     if (threadIdx.x < 32) {
         double s = 0;
         for (int i = threadIdx.x; i < a.n_part; i += 32) s += a.norm_part[i];
@@ -673,8 +684,8 @@ static int ensure_head_smem(const void *fn, int bytes) {
 }
 
 int launch_policy_head(const ocppo_handle *h, const float *hidden, int64_t B, int64_t row_base, int64_t total_B,
-                       uint64_t seed, uint64_t offset, const int64_t *given, int64_t *action, float *logp,
-                       float *entropy, float *value, int want_policy, cudaStream_t stream) {
+                       uint64_t seed, uint64_t offset, const uint64_t *philox_dev, const int64_t *given, int64_t *action,
+                       float *logp, float *entropy, float *value, int want_policy, cudaStream_t stream) {
     if (B == 0) return OCPPO_OK;
     const int A = h->cfg.n_actions, H = h->hidden;
     PhiloxLayout L{seed, offset, torch_philox_grid(total_B * A, h->sm_count, h->max_threads_per_sm) * 256};
@@ -690,7 +701,7 @@ int launch_policy_head(const ocppo_handle *h, const float *hidden, int64_t B, in
     ProfScope ps(KC_HEAD, 1, stream);
     kern<<<grid, kHeadThreads, smem, stream>>>(
         hidden, B, H, A, h->params + h->actor.w_off, h->params + h->actor.b_off, h->params + h->critic.w_off,
-        h->params + h->critic.b_off, L, row_base, given, action, logp, entropy, value, want_policy);
+        h->params + h->critic.b_off, L, philox_dev, row_base, given, action, logp, entropy, value, want_policy);
     OCPPO_LAUNCH_CHECK("policy_head_kernel");
     return OCPPO_OK;
 }
@@ -806,22 +817,49 @@ int launch_relu_mask(const float *g, const float *act, int64_t n, float *out, in
     return OCPPO_OK;
 }
 
-int launch_clip_adam(ocppo_handle *h, float inv_world, float max_norm, double lr, double beta1, double beta2,
-                     double eps, int64_t step, float *grad_norm, cudaStream_t stream) {
+// torch/optim/adam.py _single_tensor_adam forms its scalars in python double; so does this (host) helper, in the
+// order adam_kernel reads them: inv_world, max_norm, 1 - beta1, beta2, 1 - beta2, lr / (1 - beta1^t), sqrt(1 - beta2^t), eps
+void adam_scalars(float inv_world, float max_norm, double lr, double beta1, double beta2, double eps, int64_t step, float *out8) {
+    const double bc1 = 1.0 - pow(beta1, (double)step);
+    const double bc2 = 1.0 - pow(beta2, (double)step);
+    out8[0] = inv_world; out8[1] = max_norm;
+    out8[2] = (float)(1.0 - beta1); out8[3] = (float)beta2; out8[4] = (float)(1.0 - beta2);
+    out8[5] = (float)(lr / bc1); out8[6] = (float)sqrt(bc2); out8[7] = (float)eps;
+}
+
+namespace {
+struct Words8 { uint32_t w[8]; };
+__global__ void store_words_kernel(uint32_t *dst, Words8 v, int n) {
+    if (threadIdx.x < n) dst[threadIdx.x] = v.w[threadIdx.x];
+}
+}  // namespace
+
+// dst[0..n) = words (n <= 8), stream-ordered: the values travel as kernel arguments, so the caller's host memory is
+// free again when this returns (an H2D copy from pageable memory would synchronise, one from pinned memory would need
+// a ring of slots).  Refreshes the device-resident scalars of graph-replayed calls.
+int launch_store_words(void *dst, const void *words, int n, cudaStream_t stream) {
+    Words8 v{};
+    memcpy(v.w, words, (size_t)n * 4);
+    ProfScope ps(KC_AUX, 1, stream);
+    store_words_kernel<<<1, 32, 0, stream>>>(reinterpret_cast<uint32_t *>(dst), v, n);
+    OCPPO_LAUNCH_CHECK("store_words_kernel");
+    return OCPPO_OK;
+}
+
+int launch_clip_adam(ocppo_handle *h, const float *host8, const float *dev8, float *grad_norm, cudaStream_t stream) {
     const int64_t n = h->arena_floats;   // multiple of kArenaAlignFloats, padding is zero
     const int blocks = kNormBlocks < h->sm_count * 4 ? kNormBlocks : h->sm_count * 4;
     ProfScope ps(KC_ADAM, 2, stream);
-    sumsq_kernel<<<blocks, 256, 0, stream>>>(h->grads, n, inv_world, h->norm_part);
+    sumsq_kernel<<<blocks, 256, 0, stream>>>(h->grads, n, host8 ? host8[0] : 1.f, dev8, h->norm_part);
     OCPPO_LAUNCH_CHECK("sumsq_kernel");
-    // torch/optim/adam.py _single_tensor_adam: scalars formed in python double
-    const double bc1 = 1.0 - pow(beta1, (double)step);
-    const double bc2 = 1.0 - pow(beta2, (double)step);
-    AdamArgs a;
+    AdamArgs a{};
     a.p = h->params; a.g = h->grads; a.m = h->exp_avg; a.v = h->exp_avg_sq;
     a.n = n; a.norm_part = h->norm_part; a.n_part = blocks;
-    a.inv_world = inv_world; a.max_norm = max_norm;
-    a.one_minus_b1 = (float)(1.0 - beta1); a.b2 = (float)beta2; a.one_minus_b2 = (float)(1.0 - beta2);
-    a.step_size = (float)(lr / bc1); a.bc2_sqrt = (float)sqrt(bc2); a.eps = (float)eps;
+    if (host8 != nullptr) {
+        a.inv_world = host8[0]; a.max_norm = host8[1]; a.one_minus_b1 = host8[2]; a.b2 = host8[3]; a.one_minus_b2 = host8[4];
+        a.step_size = host8[5]; a.bc2_sqrt = host8[6]; a.eps = host8[7];
+    }
+    a.dev_scalars = dev8;
     a.grad_norm = grad_norm;
     adam_kernel<<<h->sm_count * 4, 256, 0, stream>>>(a);
     OCPPO_LAUNCH_CHECK("adam_kernel");

@@ -225,7 +225,7 @@ inline bool aligned16(const void *p) { return (((uintptr_t)p) & 15) == 0; }
 
 template <int MODE>
 int dispatch(const SgemmArgs &a, bool av, bool bv, dim3 grid, cudaStream_t s) {
-    ProfScope ps(MODE == SGEMM_FWD ? KC_SGEMM_FWD : (MODE == SGEMM_DGRAD ? KC_SGEMM_DGRAD : KC_SGEMM_WGRAD), 1, s);
+    ProfScope ps(KC_GEMM_CUDA_CORE, 1, s);
     if (av && bv) sgemm_kernel<MODE, true, true><<<grid, kThreads, 0, s>>>(a);
     else if (av) sgemm_kernel<MODE, true, false><<<grid, kThreads, 0, s>>>(a);
     else if (bv) sgemm_kernel<MODE, false, true><<<grid, kThreads, 0, s>>>(a);
@@ -239,8 +239,12 @@ int dispatch(const SgemmArgs &a, bool av, bool bv, dim3 grid, cudaStream_t s) {
 int g_gemm_mode = 8;   // tcgen05: three FP16 passes on fp16-pair stored operands, one accumulator; see ocppo_set_gemm_mode
 
 static int tc_ops_mask() {
+#ifdef OCPPO_BRINGUP
     static const int ops_mask = getenv("OCPPO_TC_OPS") ? atoi(getenv("OCPPO_TC_OPS")) : 7;   // bring-up: bit per op
     return ops_mask;
+#else
+    return 7;        // release build: no environment knobs
+#endif
 }
 
 void sgemm_engine_flags(int engine, SgemmArgs *b) {

@@ -108,7 +108,7 @@ int launch_skinny_wgrad(const float *wide, int64_t ldw, int nw, const float *ski
     const int G = skinny_slabs(rows, sm_count, &per);
     const int NS = ns <= 8 ? 8 : 32;
     dim3 grid((unsigned)G, (unsigned)ceil_div(nw, kSkThreads));
-    ProfScope ps(KC_SGEMM_WGRAD, 1, stream);
+    ProfScope ps(KC_GEMM_CUDA_CORE, 1, stream);
     if (NS == 8)
         skinny_wgrad_kernel<8><<<grid, kSkThreads, 0, stream>>>(wide, ldw, nw, skinny, lds, ns, rows, per, part, wsum_part, ssum_part);
     else

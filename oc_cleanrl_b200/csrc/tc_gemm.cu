@@ -965,8 +965,10 @@ constexpr int kMapSlots = 256;
 MapSlot g_maps[kMapSlots];
 int g_map_next = 0;
 bool map_lookup(const MapKey &k, CUtensorMap *tm) {
+#ifdef OCPPO_BRINGUP
     static const bool off = getenv("OCPPO_NO_MAPCACHE") != nullptr;     // bisecting knob
     if (off) return false;
+#endif
     for (int i = 0; i < kMapSlots; ++i) {
         const MapSlot &m = g_maps[i];
         if (m.used && m.key.kind == k.kind && m.key.base == k.base && m.key.a == k.a && m.key.b == k.b && m.key.ld == k.ld &&
@@ -1081,8 +1083,13 @@ int tc_gemm_ctas(SgemmMode mode, const SgemmArgs &a, int sm_count) {
 }
 
 int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
+#ifdef OCPPO_BRINGUP
     static const int dbg = getenv("OCPPO_TC_DBG") ? atoi(getenv("OCPPO_TC_DBG")) : 0;   // bring-up knob only
     static const float trunc_scale = getenv("OCPPO_TC_TRUNC") ? (float)atof(getenv("OCPPO_TC_TRUNC")) : 1.f;   // calibration knob
+#else
+    constexpr int dbg = 0;               // release build: the knobs do not exist
+    constexpr float trunc_scale = 1.f;
+#endif
     SgemmArgs a = a_in;
     a.dbg = dbg;
     a.trunc_scale = trunc_scale;
@@ -1105,15 +1112,20 @@ int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
         {tc_gemm_kernel<SGEMM_FWD, true, 2>, tc_gemm_kernel<SGEMM_DGRAD, true, 2>, tc_gemm_kernel<SGEMM_WGRAD, true, 2>},
         {tc_gemm_kernel<SGEMM_FWD, true, 3>, tc_gemm_kernel<SGEMM_DGRAD, true, 3>, tc_gemm_kernel<SGEMM_WGRAD, true, 3>},
         {tc_gemm_kernel<SGEMM_FWD, false, 3>, tc_gemm_kernel<SGEMM_DGRAD, false, 3>, tc_gemm_kernel<SGEMM_WGRAD, false, 3>}};
-    static int sms = 0;
-    if (sms == 0) {
-        int dev = 0;
-        OCPPO_CUDA(cudaGetDevice(&dev));
-        OCPPO_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    // per device: SM count, and the opt-in shared-memory size (a function attribute lives in the device's context)
+    static int sms_of[kMaxDevices] = {0};
+    int dev = 0;
+    OCPPO_CUDA(cudaGetDevice(&dev));
+    OCPPO_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "tc_gemm: device ordinal %d out of range", dev);
+    if (sms_of[dev] == 0) {
+        int n = 0;
+        OCPPO_CUDA(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
         for (int i = 0; i < kVariants; ++i)
             for (int j = 0; j < 3; ++j)
                 OCPPO_CUDA(cudaFuncSetAttribute(kerns[i][j], cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes));
+        sms_of[dev] = n;
     }
+    const int sms = sms_of[dev];
     const int grid = 2 * (ntiles < sms / 2 ? ntiles : sms / 2);     // CTA pairs
     CUtensorMap tmA, tmB, tmC, tmX, tmB2, tmA2, tmC2;
     // operands that already live in global memory as fp16 hi / lo pairs: both (PRE kernel: no conversion warps), or only

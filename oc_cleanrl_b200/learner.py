@@ -95,8 +95,17 @@ def make_permutations(batch_size, update_epochs, rng=None, pinned=True):
 
 
 class PPOLearner:
+    """``use_graphs``: the ~45 launches of one minibatch (gather, forward, loss head, backward, reductions, clip + Adam)
+    are captured into a CUDA graph the first time a minibatch slot is seen with a given set of buffer pointers and
+    replayed afterwards -- the rollout buffers, the permutation buffer and the statistics rows persist across
+    iterations, so after the first update every minibatch is one graph launch.  What changes from step to step (learning
+    rate, Adam bias corrections) lives in device memory (``ocppo_adam_scalars_set`` / ``ocppo_clip_adam_dev``).  With
+    ``world_size > 1`` the gradient all-reduce sits between two graphs (``graph_collective=False``, the default) or is
+    captured with them.  If the caller hands over new buffers every iteration the graphs never hit and the learner
+    falls back to plain launches by itself."""
+
     def __init__(self, agent: PPObj, args: LearnerArgs, world_size: int = 1, process_group=None,
-                 chunk_rows: int = 32768, np_rng=None):
+                 chunk_rows: int = 32768, np_rng=None, use_graphs: bool = True, graph_collective: bool = False):
         if agent._handle is None:
             raise _abi.OcppoError("move the agent to its CUDA device before building the learner")
         self.agent = agent
@@ -107,8 +116,13 @@ class PPOLearner:
         self.device = agent._cuda_device
         self.adam_step = 0                      # torch Adam's `step`, never reset
         self.chunk_rows = int(chunk_rows)
-        self._stats = self._gn = None
+        self.use_graphs = bool(use_graphs)
+        self.graph_collective = bool(graph_collective)
+        self._graphs = {}
+        self._graph_hits = self._graph_misses = 0
+        self._stats = self._gn = self._adam_dev = None
         self._perm_host = self._perm_dev = None
+        self._gae_out = None
         self._ensure_slots(args.update_epochs * (args.num_minibatches + 1))
         self._hp = _abi.HParams(float(args.clip_coef), float(args.ent_coef), float(args.vf_coef),
                                 int(bool(args.norm_adv)), int(bool(args.clip_vloss)))
@@ -119,6 +133,8 @@ class PPOLearner:
         if self._stats is None or self._stats.shape[0] < n:
             self._stats = torch.zeros((n, _abi.OCPPO_NUM_STATS), dtype=torch.float32, device=self.device)
             self._gn = torch.zeros(n, dtype=torch.float32, device=self.device)
+            self._adam_dev = torch.zeros((n, 8), dtype=torch.float32, device=self.device)
+            self._graphs.clear()
 
     # -- ppo_atari_oc.py:471-474 -------------------------------------------------
     def anneal_lr(self, iteration: int, num_iterations: int):
@@ -129,9 +145,14 @@ class PPOLearner:
 
     # -- ppo_atari_oc.py:533-547 -------------------------------------------------
     def compute_gae(self, rewards, values, dones, next_obs, next_done):
+        """-> (advantages, returns), two learner-owned (T, N) buffers that the next call overwrites (the script
+        allocates fresh ones every iteration, :535,:547; persistent buffers keep the update's CUDA graphs valid)."""
         with torch.no_grad():
             next_value = self.agent.get_value(next_obs).reshape(-1)
-        return compute_gae(rewards, values, dones, next_value, next_done, self.args.gamma, self.args.gae_lambda)
+        if self._gae_out is None or self._gae_out[0].shape != rewards.shape:
+            self._gae_out = (torch.empty_like(rewards), torch.empty_like(rewards))
+        return compute_gae(rewards, values, dones, next_value, next_done, self.args.gamma, self.args.gae_lambda,
+                           out=self._gae_out)
 
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
@@ -155,21 +176,67 @@ class PPOLearner:
         b_obs, b_actions, b_logprobs, b_advantages, b_returns, b_values = flat
         a = self.args
         mb = idx_dev.numel()
-        self.agent._ensure_workspace(min(mb, self.chunk_rows), training=True)
+        self.agent._ensure_workspace(min(mb, self.chunk_rows), training=True, exact=True)
         lib, h = _abi.lib(), self.agent._handle.raw
-        stream = self._stream()
-        _abi.check(lib.ocppo_minibatch_fwd_bwd(h, _abi.ptr(b_obs), _abi.ptr(b_actions), _abi.ptr(b_logprobs),
-                                               _abi.ptr(b_advantages), _abi.ptr(b_returns), _abi.ptr(b_values),
-                                               _abi.ptr(idx_dev), mb, C.byref(self._hp),
-                                               _abi.ptr(self._stats[slot]), stream))
-        if self.world_size > 1:
+        self.adam_step += 1
+        stats, gn = self._stats[slot], self._gn[slot:slot + 1]
+
+        def fwd_bwd(stream):
+            _abi.check(lib.ocppo_minibatch_fwd_bwd(h, _abi.ptr(b_obs), _abi.ptr(b_actions), _abi.ptr(b_logprobs),
+                                                   _abi.ptr(b_advantages), _abi.ptr(b_returns), _abi.ptr(b_values),
+                                                   _abi.ptr(idx_dev), mb, C.byref(self._hp), _abi.ptr(stats), stream))
+
+        def allreduce():
             # ppo_atari_multigpu.py:360-367: one SUM all-reduce of the flat gradient
             torch.distributed.all_reduce(self.agent.grad_arena, op=torch.distributed.ReduceOp.SUM,
                                          group=self.process_group)
-        self.adam_step += 1
-        _abi.check(lib.ocppo_clip_adam(h, 1.0 / self.world_size, float(a.max_grad_norm), float(self.lr),
-                                       a.adam_beta1, a.adam_beta2, a.adam_eps, self.adam_step,
-                                       _abi.ptr(self._gn[slot:slot + 1]), stream))
+
+        if not self.use_graphs:
+            stream = self._stream()
+            fwd_bwd(stream)
+            if self.world_size > 1:
+                allreduce()
+            _abi.check(lib.ocppo_clip_adam(h, 1.0 / self.world_size, float(a.max_grad_norm), float(self.lr),
+                                           a.adam_beta1, a.adam_beta2, a.adam_eps, self.adam_step, _abi.ptr(gn), stream))
+            return
+
+        scal = self._adam_dev[slot]
+        _abi.check(lib.ocppo_adam_scalars_set(_abi.ptr(scal), 1.0 / self.world_size, float(a.max_grad_norm),
+                                              float(self.lr), a.adam_beta1, a.adam_beta2, a.adam_eps, self.adam_step,
+                                              self._stream()))
+
+        def adam(stream):
+            _abi.check(lib.ocppo_clip_adam_dev(h, _abi.ptr(scal), _abi.ptr(gn), stream))
+
+        key = (tuple(t.data_ptr() for t in flat), idx_dev.data_ptr(), mb, slot, self.agent._workspace.data_ptr(),
+               self.agent._ws_rows, lib.ocppo_get_gemm_mode())
+        entry = self._graphs.get(key)
+        if entry is None:
+            self._graph_misses += 1
+            if self._graph_misses > 256 and self._graph_hits < self._graph_misses:
+                self.use_graphs = False      # the caller's buffers never repeat: capturing costs more than it saves
+                self._graphs.clear()
+            elif len(self._graphs) >= 256:
+                self._graphs.clear()
+            # the captured sequence must not depend on whether a rollout left prepared weights behind
+            _abi.check(lib.ocppo_weights_version(h, -1))
+            dev = self.device
+            if self.world_size > 1 and not self.graph_collective:
+                entry = (_abi.capture(h, dev, fwd_bwd), _abi.capture(h, dev, adam))
+            else:
+                def whole(stream):
+                    fwd_bwd(stream)
+                    if self.world_size > 1:
+                        allreduce()
+                    adam(stream)
+                entry = (_abi.capture(h, dev, whole),)
+            self._graphs[key] = entry
+        else:
+            self._graph_hits += 1
+        entry[0].replay()
+        if len(entry) == 2:
+            allreduce()
+            entry[1].replay()
 
     def update(self, obs, actions, logprobs, advantages, returns, values, permutations=None):
         """ppo_atari_oc.py:549-617.  Buffers are the (T, N, ...) rollout tensors.
@@ -186,15 +253,15 @@ class PPOLearner:
         # (:558-561), each into its own pinned row and copied asynchronously: the shuffle of epoch e+1 runs on the
         # host while the device is busy with epoch e.
         lazy = permutations is None
+        if self._perm_dev is None or tuple(self._perm_dev.shape) != (a.update_epochs, batch_size):
+            self._perm_host = torch.empty((a.update_epochs, batch_size), dtype=torch.int64, pin_memory=True)
+            self._perm_dev = torch.empty((a.update_epochs, batch_size), dtype=torch.int64, device=self.device)
+        perm_dev = self._perm_dev            # persistent: the minibatch graphs are keyed on its rows
         if lazy:
-            if self._perm_host is None or tuple(self._perm_host.shape) != (a.update_epochs, batch_size):
-                self._perm_host = torch.empty((a.update_epochs, batch_size), dtype=torch.int64, pin_memory=True)
-                self._perm_dev = torch.empty((a.update_epochs, batch_size), dtype=torch.int64, device=self.device)
             shuffle = np.random.shuffle if self.np_rng is None else self.np_rng.shuffle
             b_inds = np.arange(batch_size)
-            perm_dev = self._perm_dev
         else:
-            perm_dev = permutations.to(self.device, non_blocking=True)
+            perm_dev.copy_(permutations, non_blocking=True)
         self._ensure_slots(a.update_epochs * (-(-batch_size // minibatch_size)))
         slot, epochs_run = 0, 0
         for epoch in range(a.update_epochs):

@@ -34,14 +34,17 @@ class RolloutCollector:
         col.reset(envs.reset())                                   # :463-465
         for iteration in ...:
             for step in range(num_steps):
-                actions = col.act(step)                           # :502-509 (+ the D2H of :511)
+                actions = col.act(step)                           # :502-509 (+ the D2H of :511); act(0) first carries
+                                                                  # next_obs / next_done of the previous iteration into row 0
                 next_obs, reward, done, infos = envs.step(actions)
                 col.observe(step, next_obs, reward, done)         # :512-514
             adv, ret = learner.compute_gae(col.rewards, col.values, col.dones, col.next_obs, col.next_done)
             learner.update(col.obs, col.actions, col.logprobs, adv, ret, col.values)
     """
 
-    def __init__(self, agent: PPObj, num_steps: int, num_envs: int):
+    def __init__(self, agent: PPObj, num_steps: int, num_envs: int, use_graphs: bool = True):
+        """``use_graphs``: replay the launches of each rollout step from a CUDA graph (one per buffer row, captured on
+        first use; see ``PPObj.policy_step_into``)."""
         if agent._handle is None:
             raise _abi.OcppoError("move the agent to its CUDA device before building the collector")
         self.agent = agent
@@ -63,6 +66,8 @@ class RolloutCollector:
         self._h_reward = torch.empty(N, dtype=torch.float32, pin_memory=True)
         self._h_done = torch.empty(N, dtype=torch.float32, pin_memory=True)
         self._h_action = torch.empty(N, dtype=torch.int64, pin_memory=True)
+        self.use_graphs = bool(use_graphs)
+        self._carry_pending = False               # rows T hold next_obs / next_done that row 0 has not received yet
         self._action_ready = torch.cuda.Event()
         self._staging_free = torch.cuda.Event()
         self._staging_free.record(torch.cuda.current_stream(dev))
@@ -90,6 +95,7 @@ class RolloutCollector:
         """First observation of the run (``envs.reset()``); ``next_done`` starts at zero."""
         self._upload_obs(first_obs, 0)
         self._dones[0].zero_()
+        self._carry_pending = False
 
     def _upload_obs(self, obs_np, row):
         self._staging_free.synchronize()          # the previous upload has left the staging buffers
@@ -98,6 +104,7 @@ class RolloutCollector:
             raise _abi.OcppoError(f"observation batch {src.shape} does not match {tuple(self._h_obs.shape)}")
         self._h_obs.numpy()[...] = src.reshape(self._h_obs.shape)   # host cast to fp32 like torch.tensor(..., dtype=float32) (:513)
         self._obs[row].copy_(self._h_obs, non_blocking=True)
+        self._staging_free.record(torch.cuda.current_stream(self.device))
 
     # -- ppo_atari_oc.py:502-509, 511 -------------------------------------------------
     def act(self, step: int) -> np.ndarray:
@@ -106,15 +113,12 @@ class RolloutCollector:
         next call)."""
         if not 0 <= step < self.T:
             raise _abi.OcppoError(f"step {step} outside [0, {self.T})")
-        a = self.agent
-        a._ensure_workspace(self.N, training=False)
-        a._hint_weights()
-        seed, offset = a._philox_state(self.N * a._n_actions)     # consumes torch's CUDA generator like Categorical.sample()
+        if step == 0 and self._carry_pending:
+            self.start_next_iteration()
         stream = torch.cuda.current_stream(self.device)
-        _abi.check(_abi.lib().ocppo_policy_step(
-            a._handle.raw, _abi.ptr(self._obs[step]), self.N, seed, offset, None, _abi.ptr(self.actions[step]),
-            _abi.ptr(self.logprobs[step]), _abi.ptr(self._entropy), _abi.ptr(self.values[step]),
-            C.c_void_p(stream.cuda_stream)))
+        # consumes torch's CUDA generator like Categorical.sample(); writes rows `step` of the buffers in place
+        self.agent.policy_step_into(self._obs[step], self.actions[step], self.logprobs[step], self._entropy,
+                                    self.values[step], graph=self.use_graphs)
         self._h_action.copy_(self.actions[step], non_blocking=True)
         self._action_ready.record(stream)
         self._action_ready.synchronize()          # the environment needs the actions now (:511)
@@ -131,9 +135,15 @@ class RolloutCollector:
         self.rewards[step].copy_(self._h_reward, non_blocking=True)
         self._dones[step + 1].copy_(self._h_done, non_blocking=True)
         self._staging_free.record(torch.cuda.current_stream(self.device))
+        if step == self.T - 1:
+            self._carry_pending = True
 
     def start_next_iteration(self):
         """Carry ``next_obs`` / ``next_done`` into row 0 (the reference does this implicitly: its loop variables
-        survive the iteration, :502-503)."""
+        survive the iteration, :502-503).  ``act(0)`` calls this by itself when an iteration has completed; calling it
+        explicitly (after the learner has consumed ``next_obs``) is harmless."""
+        if not self._carry_pending:
+            return
         self._obs[0].copy_(self._obs[self.T], non_blocking=True)
         self._dones[0].copy_(self._dones[self.T], non_blocking=True)
+        self._carry_pending = False

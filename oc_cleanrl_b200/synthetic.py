@@ -9,7 +9,17 @@ CPU oracle and the device path see the same bytes.
 """
 from __future__ import annotations
 
+from types import SimpleNamespace
+
 import torch
+
+
+def stub_envs(frames: int, obs_dim: int, n_actions: int):
+    """A vector-env stand-in carrying the three attributes ``PPObj.__init__`` reads (architectures/ppo.py:65,83):
+    ``observation_space.shape == (frames, obs_dim)`` and ``action_space.n``."""
+    return SimpleNamespace(observation_space=SimpleNamespace(shape=(int(frames), int(obs_dim))),
+                           action_space=SimpleNamespace(n=int(n_actions)))
+
 
 GAME_SHAPES = {            # (obs_dim D, n_actions A): ocatari/ram/{pong,spaceinvaders,breakout}.py
     "pong": (6, 6),

@@ -25,7 +25,7 @@ def test_header_symbols_exported_and_bound(built_lib):
     for name in declared:
         assert hasattr(built_lib, name), f"{name} declared in ocppo.h but not exported"
     assert sorted(_abi.exported_symbols()) == declared
-    assert built_lib.ocppo_version() == 100
+    assert built_lib.ocppo_version() == 200
 
 
 def test_library_is_sm100a_only(built_lib):

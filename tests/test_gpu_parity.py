@@ -645,6 +645,21 @@ def test_full_size_minibatch_properties(dev, gemm_engine):
     assert float(learner._stats[0, 3]) == pytest.approx(float(loss.detach()), rel=REL_TOL, abs=1e-6)
 
 
+@pytest.mark.parametrize("game", ["pong", "spaceinvaders", "breakout"])
+@pytest.mark.parametrize("seed", [0, 1, 2, 3, 4])
+def test_full_size_minibatch_over_seeds_and_games(dev, game, seed):
+    """The default engine at the full 131,072-sample minibatch over five rollout / permutation / init seeds and the three
+    game shapes of BASELINE configs[1] / [2] (SpaceInvaders and Breakout take the padded first layer on the tensor
+    cores); seeds 3 and 4 run on disturbed, trained-like weights (non-orthogonal, non-zero biases).  Every gradient
+    tensor within 1e-4 (max-norm) of the oracle's operator sequence in torch fp32, and of fp64 up to the fp32
+    reference's own distance.  tools/fullsize_sweep.py prints the whole table (profiles/r02_fullsize_err.txt)."""
+    from fullsize import fullsize_case
+    r = fullsize_case(dev, game, seed, 8, trained_like=seed >= 3)
+    for i, (e32, e64, ref) in enumerate(zip(r["e32"], r["e64"], r["ref"])):
+        assert e32 < REL_TOL, f"{game} seed {seed} tensor {i}: {e32:.3e} vs torch fp32 (vs fp64 {e64:.3e}; torch fp32 vs fp64 {ref:.3e})"
+        assert e64 < REL_TOL + ref, f"{game} seed {seed} tensor {i}: {e64:.3e} vs fp64 (torch fp32 vs fp64 {ref:.3e})"
+
+
 def test_inference_reuses_prepared_weights_until_they_change(dev, gemm_engine):
     """ocppo_weights_version: repeated no-grad calls on unchanged weights skip the FP16 engines' weight preparation
     (max-abs, fp16 split, norms) and stay bit-identical; an in-place torch update of a parameter bumps the arena's
