@@ -265,6 +265,34 @@ int ocppo_clip_adam_dev(ocppo_handle *h, const float *scalars8, float *grad_norm
 int ocppo_explained_variance(ocppo_handle *h, const float *values, const float *returns, int64_t n, float *out2,
                              void *stream);
 
+/* ---- host env feed (pure host code, host pointers) ---------- */
+/* Batched replacement of the per-env Python observation assembly and of VecNormalize's reward scaling:
+ *  - submodules/OC_Atari/ocatari/core.py:444-448 (ns_state: chain of every slot's _nsrepr),
+ *    ocatari/ram/game_objects.py:184-188 (_nsrepr = [x, y], [0, 0] when not visible),
+ *    core.py:152-153,274-283 (deque(maxlen=buffer_window_size), append per step), core.py:241-244 (a reset fills every
+ *    entry with the initial state), core.py:213-214 (np.array(deque): oldest frame first);
+ *  - cleanrl/ppo_atari_oc.py:411-414 VecNormalize(envs, norm_obs=False, norm_reward=True) -- stable-baselines3==2.0.0
+ *    (requirements pin; not vendored): returns = returns*gamma + reward; RunningMeanStd.update(returns);
+ *    reward / sqrt(var + 1e-8) clipped to +-10; returns[done] = 0;
+ *  - cleanrl/ppo_atari_oc.py:512-514 (float32 casts of reward / next_obs / next_done).
+ * ALE / OCAtari are not available on this box: the emulator side (RAM -> object slots) stays with the env workers;
+ * these calls take the slots of all N envs of one step and write straight into the caller's (pinned) buffers. */
+typedef struct ocppo_feed ocppo_feed;
+/* slots = object slots per env (Pong 3, SpaceInvaders 44, Breakout 110); obs_dim = 2 * slots.  gamma / epsilon /
+ * clip_reward are VecNormalize's (0.99, 1e-8, 10 by default). */
+int ocppo_feed_create(int32_t num_envs, int32_t frames, int32_t slots, double gamma, double epsilon, double clip_reward,
+                      ocppo_feed **out);
+int ocppo_feed_destroy(ocppo_feed *f);
+/* One env step of all envs.  xy int32 [N, slots, 2]; visible uint8 [N, slots]; refill uint8 [N] or NULL (1: the env was
+ * reset, all `frames` entries become this state; an env's first push always fills).  obs_out fp32 [N, frames, 2*slots]. */
+int ocppo_feed_push(ocppo_feed *f, const int32_t *xy, const uint8_t *visible, const uint8_t *refill, float *obs_out);
+/* reward float64 [N] as the envs return it, done uint8 [N] -> reward_out fp32 [N] (normalised, clipped), done_out fp32 [N]
+ * (may be NULL).  Updates the running statistics (training mode). */
+int ocppo_feed_normalize_reward(ocppo_feed *f, const double *reward, const uint8_t *done, float *reward_out,
+                                float *done_out);
+/* ret_rms (mean, var, count) and the per-env discounted returns (either may be NULL). */
+int ocppo_feed_state(const ocppo_feed *f, double *mean_var_count3, double *returns);
+
 /* ---- autograd bridge (compat tier: script's own loss/optimizer) --------- */
 /* Trunk forward keeping activations: hidden (B, decoder_dims[-1]). */
 int ocppo_trunk_forward(ocppo_handle *h, const float *obs, int64_t B, float *hidden,

@@ -42,9 +42,11 @@ class RolloutCollector:
             learner.update(col.obs, col.actions, col.logprobs, adv, ret, col.values)
     """
 
-    def __init__(self, agent: PPObj, num_steps: int, num_envs: int, use_graphs: bool = True):
+    def __init__(self, agent: PPObj, num_steps: int, num_envs: int, use_graphs: bool = True, feed=None):
         """``use_graphs``: replay the launches of each rollout step from a CUDA graph (one per buffer row, captured on
-        first use; see ``PPObj.policy_step_into``)."""
+        first use; see ``PPObj.policy_step_into``).  ``feed``: an :class:`oc_cleanrl_b200.feed.ObjectFeed` for
+        ``reset_objects`` / ``observe_objects`` (object slots in, frame-stacked block written straight into the pinned
+        staging buffer, rewards normalised like ``VecNormalize``)."""
         if agent._handle is None:
             raise _abi.OcppoError("move the agent to its CUDA device before building the collector")
         self.agent = agent
@@ -67,6 +69,9 @@ class RolloutCollector:
         self._h_done = torch.empty(N, dtype=torch.float32, pin_memory=True)
         self._h_action = torch.empty(N, dtype=torch.int64, pin_memory=True)
         self.use_graphs = bool(use_graphs)
+        self.feed = feed
+        if feed is not None and tuple(feed.obs_shape) != (self.N, F, D):
+            raise _abi.OcppoError(f"feed produces {tuple(feed.obs_shape)}, the agent expects {(self.N, F, D)}")
         self._carry_pending = False               # rows T hold next_obs / next_done that row 0 has not received yet
         self._action_ready = torch.cuda.Event()
         self._staging_free = torch.cuda.Event()
@@ -105,6 +110,41 @@ class RolloutCollector:
         self._h_obs.numpy()[...] = src.reshape(self._h_obs.shape)   # host cast to fp32 like torch.tensor(..., dtype=float32) (:513)
         self._obs[row].copy_(self._h_obs, non_blocking=True)
         self._staging_free.record(torch.cuda.current_stream(self.device))
+
+    # -- the same two entry points fed with OBJECT SLOTS ---------------------
+    def _require_feed(self):
+        if self.feed is None:
+            raise _abi.OcppoError("this collector was built without a feed (pass feed=ObjectFeed(...))")
+        return self.feed
+
+    def reset_objects(self, xy, visible):
+        """``envs.reset()`` in object slots: xy ``(N, slots, 2)``, visible ``(N, slots)``; every env's frame stack is
+        filled with its initial state (ocatari/core.py:241-244)."""
+        feed = self._require_feed()
+        self._staging_free.synchronize()
+        feed.push(xy, visible, refill=np.ones(self.N, dtype=np.uint8), out=self._h_obs.numpy())
+        self._obs[0].copy_(self._h_obs, non_blocking=True)
+        self._staging_free.record(torch.cuda.current_stream(self.device))
+        self._dones[0].zero_()
+        self._carry_pending = False
+
+    def observe_objects(self, step: int, xy, visible, reward, done):
+        """``envs.step`` results of `step` as the env workers read them off the emulator: object slots, raw float64
+        rewards, episode-end flags.  The frame-stacked observation block is assembled by ``ocppo_feed_push`` directly in
+        the pinned staging buffer (an env that finished its episode was auto-reset by the vector env, so its stack is
+        refilled), the rewards pass through ``VecNormalize``'s running-return scaling (``ocppo_feed_normalize_reward``),
+        and the three uploads of ppo_atari_oc.py:512-514 follow."""
+        feed = self._require_feed()
+        self._staging_free.synchronize()
+        done = np.asarray(done).astype(np.uint8).reshape(-1)
+        feed.push(xy, visible, refill=done, out=self._h_obs.numpy())
+        feed.normalize_reward(reward, done, out_reward=self._h_reward.numpy(), out_done=self._h_done.numpy())
+        self._obs[step + 1].copy_(self._h_obs, non_blocking=True)
+        self.rewards[step].copy_(self._h_reward, non_blocking=True)
+        self._dones[step + 1].copy_(self._h_done, non_blocking=True)
+        self._staging_free.record(torch.cuda.current_stream(self.device))
+        if step == self.T - 1:
+            self._carry_pending = True
 
     # -- ppo_atari_oc.py:502-509, 511 -------------------------------------------------
     def act(self, step: int) -> np.ndarray:

@@ -119,6 +119,49 @@ def test_collector_feeds_the_learner_and_rejects_bad_input(dev):
         col.observe(0, np.zeros((N + 1, F, D)), np.zeros(N), np.zeros(N))
 
 
+def test_collector_fed_with_object_slots_equals_the_reference_env_side(dev):
+    """object slots in (what an env worker reads off the emulator), through ``ocppo_feed_push`` /
+    ``ocppo_feed_normalize_reward`` into the pinned staging buffers, against the reference's env side restated in
+    oracle/ref_feed.py (per-env list chain + deque, SB3 VecNormalize reward path) feeding the array entry points."""
+    from oracle import ref_feed
+    from oc_cleanrl_b200.architectures.ppo import PPObj
+    from oc_cleanrl_b200.feed import ObjectFeed
+    from oc_cleanrl_b200.rollout import RolloutCollector
+    F, S, A, T, N = 4, 3, 6, 12, 48
+    D = 2 * S
+    rng = np.random.RandomState(5)
+    script = [(np.stack([rng.randint(0, 160, (N, S)), rng.randint(0, 210, (N, S))], -1), rng.rand(N, S) > 0.2,
+               (rng.rand(N) < 0.1) * rng.choice([1.0, -1.0, 20.0], N), rng.rand(N) < 0.1) for _ in range(2 * T + 1)]
+    bufs = []
+    for use_feed in (False, True):
+        torch.manual_seed(3)
+        agent = PPObj(ref_ppo.stub_envs(F, D, A), dev, (32, 64), (32,)).to(dev)
+        torch.cuda.manual_seed(4)
+        if use_feed:
+            col = RolloutCollector(agent, T, N, feed=ObjectFeed(N, S, F))
+            col.reset_objects(script[0][0], script[0][1])
+        else:
+            col = RolloutCollector(agent, T, N)
+            envs = [ref_feed.RefObjectEnv(S, F) for _ in range(N)]
+            norm = ref_feed.RefVecNormalizeReward(N)
+            col.reset(np.stack([e.reset(script[0][0][n], script[0][1][n]) for n, e in enumerate(envs)]))
+        k = 1
+        for it in range(2):
+            for step in range(T):
+                col.act(step)
+                xy, vis, reward, done = script[k]
+                k += 1
+                if use_feed:
+                    col.observe_objects(step, xy, vis, reward, done)
+                else:
+                    obs = np.stack([e.reset(xy[n], vis[n]) if done[n] else e.step(xy[n], vis[n]) for n, e in enumerate(envs)])
+                    col.observe(step, obs, norm.step_wait(reward.copy(), done), done)
+        torch.cuda.synchronize()
+        bufs.append([t.clone() for t in (col.obs, col.actions, col.logprobs, col.rewards, col.dones, col.values, col.next_obs, col.next_done)])
+    for a, b in zip(*bufs):
+        assert torch.equal(a, b)
+
+
 @pytest.mark.parametrize("n,const", [(128 * 4096, False), (1000, False), (77, True)])
 def test_explained_variance_matches_the_numpy_line(dev, n, const):
     """ppo_atari_oc.py:620-623 (np.var on host copies) against the device reduction."""
