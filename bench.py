@@ -317,7 +317,8 @@ def graph_timed(dev, launch, iters):
 
 
 def time_gae_isolated(dev, T, N, iters=200, min_bytes=192 << 20):
-    """-> (us per GAE launch, us per same-bytes device copy): both rotate through more than an L2's worth of distinct
+    """-> (us per GAE launch, us per same-bytes device copy, us per GAE launch in a chain of programmatic dependent
+    launches -- how the learner launches it behind the bootstrap value kernel): all rotate through more than an L2's worth of distinct
     buffers so no launch finds its inputs in L2.  The copy (5 x T x N floats read + written = the GAE's algorithmic bytes)
     is the floor of any kernel that moves these bytes once at this size: launch + one DRAM round trip."""
     from oc_cleanrl_b200.learner import compute_gae
@@ -335,6 +336,11 @@ def time_gae_isolated(dev, T, N, iters=200, min_bytes=192 << 20):
         s = sets[i % n_sets]
         compute_gae(s["r"], s["v"], s["d"], s["nv"], s["nd"], 0.99, 0.95, out=s["out"])
     us = graph_timed(dev, launch, iters)
+
+    def launch_overlapped(i):          # each launch a programmatic dependent of the one before it (other buffers)
+        s = sets[i % n_sets]
+        compute_gae(s["r"], s["v"], s["d"], s["nv"], s["nd"], 0.99, 0.95, out=s["out"], overlap_previous=True)
+    us_pdl = graph_timed(dev, launch_overlapped, iters)
     # same bytes through cudaMemcpyAsync: 2.5 x T x N floats copied (read + write = 20 T N bytes)
     half = (5 * T * N) // 2
     flat = [torch.cat([s["r"].reshape(-1), s["v"].reshape(-1), s["d"].reshape(-1)])[:half].contiguous() for s in sets]
@@ -344,7 +350,7 @@ def time_gae_isolated(dev, T, N, iters=200, min_bytes=192 << 20):
         dst[i % n_sets].copy_(flat[i % n_sets], non_blocking=True)
     us_copy = graph_timed(dev, copy, iters)
     del sets, flat, dst
-    return us, us_copy
+    return us, us_copy, us_pdl
 
 
 def time_policy_step(agent, dev, D, n_envs, iters=20):
@@ -583,17 +589,22 @@ def run_b200(a):
     sweep_n = [int(x) for x in a.gae_sweep.split(",") if x]
     sweep = []
     for n in sweep_n:
-        us, us_copy = time_gae_isolated(dev, T, n)
+        us, us_copy, us_pdl = time_gae_isolated(dev, T, n)
         gbs = gae_bytes(T, n) / (us * 1e-6) / 1e9
         sweep.append({"num_envs": n, "num_steps": T, "us_per_launch": us, "bytes": gae_bytes(T, n), "GB/s": gbs,
                       "frac": gbs / pk["hbm"], "same_bytes_copy_us": us_copy,
-                      "same_bytes_copy_frac": gae_bytes(T, n) / (us_copy * 1e-6) / 1e9 / pk["hbm"]})
+                      "same_bytes_copy_frac": gae_bytes(T, n) / (us_copy * 1e-6) / 1e9 / pk["hbm"],
+                      "overlapped_us_per_launch": us_pdl, "overlapped_frac": gae_bytes(T, n) / (us_pdl * 1e-6) / 1e9 / pk["hbm"]})
     own = next((s for s in sweep if s["num_envs"] == N), sweep[0] if sweep else None)
     roofline_gae = None
     if own:
         tg = NCU_TRAFFIC_GAE.get((own["num_envs"], T))
         roofline_gae = {"bound": "hbm", "achieved": own["GB/s"], "peak": pk["hbm"], "unit": "GB/s", "frac": own["frac"],
                         "traffic": tg["bytes"] if tg else None, "traffic_source": tg["source"] if tg else None,
+                        "overlapped": {"us": own["overlapped_us_per_launch"], "frac": own["overlapped_frac"],
+                                       "what": "the same launches as programmatic dependents of each other (ocppo_gae_overlapped, how the "
+                                               "learner launches the scan behind the bootstrap value kernel): launch latency and the "
+                                               "first DRAM round trip overlap the previous kernel's tail"},
                         "floor": {"us": own["same_bytes_copy_us"], "frac": own["same_bytes_copy_frac"],
                                   "what": "cudaMemcpyAsync D2D moving the same bytes, timed the same way (graph replay over >L2 of "
                                           "rotating buffers): launch + one DRAM round trip"},

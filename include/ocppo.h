@@ -229,6 +229,21 @@ int ocppo_gae(const float *rewards, const float *values, const float *dones,
               double gamma, double gae_lambda, float *advantages, float *returns,
               void *stream);
 
+/* The same scan launched as a PROGRAMMATIC DEPENDENT of the kernel before it on the stream: it may start while that
+ * kernel is still draining, puts its tile loads of rewards / values / dones in flight, and waits for that kernel's
+ * completion only before it reads next_value.  The caller guarantees that the preceding kernel writes none of
+ * rewards / values / dones / advantages / returns -- true for the bootstrap ocppo_value call of ppo_atari_oc.py:534,
+ * whose only output is next_value.  Hides the launch latency and most of the first DRAM round trip of a kernel whose
+ * whole run time is a few microseconds.  Falls back to a plain launch where the TMA kernel is not eligible. */
+int ocppo_gae_overlapped(const float *rewards, const float *values, const float *dones,
+                         const float *next_value, const float *next_done, int64_t T, int64_t N,
+                         double gamma, double gae_lambda, float *advantages, float *returns,
+                         void *stream);
+/* Kernel selection for tests / measurement: 0 (default) = the TMA, warp-specialised kernel whenever N % 4 == 0 and the
+ * buffers are 16-byte aligned; 1 = always the first-generation cp.async kernel (the fallback for ragged buffers).
+ * Both are bit-exact. */
+int ocppo_set_gae_variant(int32_t variant);
+
 /* ---- PPO update ---------------------------------------------------------- */
 /* One minibatch of cleanrl/ppo_atari_oc.py:563-608: gather rows `idx` (int64,
  * mb of them; flat index t*N+n) of the flattened rollout buffers, forward,

@@ -83,6 +83,8 @@ _SIGNATURES = {
     "ocppo_philox_increment": (_U64, [_I64, _I32, _I32]),
     "ocppo_exponential": (C.c_int, [_P, _I64, _U64, _U64, _P]),
     "ocppo_gae": (C.c_int, [_P, _P, _P, _P, _P, _I64, _I64, _D, _D, _P, _P, _P]),
+    "ocppo_gae_overlapped": (C.c_int, [_P, _P, _P, _P, _P, _I64, _I64, _D, _D, _P, _P, _P]),
+    "ocppo_set_gae_variant": (C.c_int, [_I32]),
     "ocppo_minibatch_fwd_bwd": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, _I64, C.POINTER(HParams), _P, _P]),
     "ocppo_clip_adam": (C.c_int, [_P, _F, _F, _D, _D, _D, _D, _I64, _P, _P]),
     "ocppo_adam_scalars_set": (C.c_int, [_P, _F, _F, _D, _D, _D, _D, _I64, _P]),

@@ -177,7 +177,7 @@ static int64_t carve(ocppo_handle *h, void *base, int64_t R, int training, bool 
     }
     {   // wide first layer (32 < D <= kPadCols): padded pair copies of its input and weight
         const Layer &L0 = h->layers[0];
-        const bool pad0 = h->n_layers > 1 && L0.in_dim > 32 && L0.in_dim <= kPadCols && L0.out_dim % 256 == 0;
+        const bool pad0 = h->n_layers > 1 && L0.in_dim > 32 && L0.in_dim <= kPadCols && L0.out_dim % 128 == 0;
         t->x0p_hi = pad0 ? cv.take<uint16_t>(R * L0.row_mult * kPadCols) : nullptr;
         t->x0p_lo = pad0 ? cv.take<uint16_t>(R * L0.row_mult * kPadCols) : nullptr;
         t->w0p_hi = pad0 ? cv.take<uint16_t>((int64_t)L0.out_dim * kPadCols) : nullptr;
@@ -327,9 +327,10 @@ static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_
         SgemmArgs a{};
         fwd_args(h, l, B, in, &a);
         a.relu_bits = h->training ? h->relu_bits[l] : nullptr;
+        const bool w16 = L.w_off % 8 == 0 && L.in_dim % 8 == 0;
+        a.want_pre = pre16 && l > 0 && w16 && pair_ok(h, l - 1, B);     // both operands will arrive as pairs (below)
         const bool tc = sgemm_uses_tc(SGEMM_FWD, a);
         h->relu_bits_valid[l] = a.relu_bits != nullptr && tc;
-        const bool w16 = L.w_off % 8 == 0 && L.in_dim % 8 == 0;
         bool pair_out = false;
         if (l == 0) h->x0p_valid = 0;
         if (pre16 && l == 0 && h->x0p_hi != nullptr && h->w_amax_valid) {
@@ -351,6 +352,7 @@ static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_
             h->relu_bits_valid[0] = a.relu_bits != nullptr;
             SgemmArgs n{};
             fwd_args(h, 1, B, h->act[0], &n);
+            n.want_pre = pair_ok(h, 0, B) && h->layers[1].w_off % 8 == 0;
             if (pair_ok(h, 0, B) && sgemm_uses_tc(SGEMM_FWD, n)) {
                 a.c16_hi = h->act16_hi[0]; a.c16_lo = h->act16_lo[0];
                 a.bnd_amax = h->amax + kAmaxObs; a.bnd_wl1 = h->amax + kWRowL1; a.bnd_bmax = h->amax + kBMax;
@@ -376,6 +378,7 @@ static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_
                 if (l + 1 < h->n_layers && pair_ok(h, l, B)) {
                     SgemmArgs n{};
                     fwd_args(h, l + 1, B, h->act[l], &n);
+                    n.want_pre = h->layers[l + 1].w_off % 8 == 0 && L.out_dim % 8 == 0;
                     next_tc = sgemm_uses_tc(SGEMM_FWD, n);
                 }
                 if (next_tc) {                            // ... and so does the output: no fp32 copy of it is ever written
@@ -397,6 +400,7 @@ static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_
                     // fp16 pair and the ReLU decision bits itself, and no fp32 copy of the activation exists
                     SgemmArgs n{};
                     fwd_args(h, l + 1, B, h->act[l], &n);
+                    n.want_pre = h->layers[l + 1].w_off % 8 == 0 && L.out_dim % 8 == 0;
                     if (sgemm_uses_tc(SGEMM_FWD, n)) {
                         if (l == 0) OCPPO_TRY(launch_absmax(x, B * L.row_mult, L.in_dim, L.in_dim, h->amax + kAmaxObs, h->sm_count, s));
                         else OCPPO_TRY(ensure_act_amax(h, l - 1, B, s));
@@ -421,9 +425,10 @@ static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_
     return OCPPO_OK;
 }
 
-static void pick_split(const ocppo_handle *h, int M, int N, int64_t K, int *splits, int64_t *k_per) {
-    const int tn = tc_tile_n(g_gemm_mode == 2 || g_gemm_mode == 4 || g_gemm_mode == 8);
-    const bool tc = g_gemm_mode >= 1 && M % 128 == 0 && N % tn == 0;
+static void pick_split(const ocppo_handle *h, int M, int N, int64_t K, int *splits, int64_t *k_per, bool pre = false) {
+    // N tile: 256, or 128 for the conversion-free kernel (`pre`: both operands will be fp16 pairs) when N % 256 != 0
+    const int tn = N % 256 == 0 ? 256 : ((pre && g_gemm_mode >= 6 && N % 128 == 0) ? 128 : 0);
+    const bool tc = g_gemm_mode >= 1 && M % 128 == 0 && tn != 0;
     int64_t S;
     const int64_t s_cap0 = K / 256 > 1 ? K / 256 : 1;
     const int64_t s_cap = s_cap0 < kSplitMax ? s_cap0 : kSplitMax;
@@ -491,12 +496,15 @@ static void wgrad_args(const ocppo_handle *h, const float *dY, int out, const fl
     a->B = X; a->ldb = in;
     a->C = h->splitk; a->ldc = in;
     a->M = out; a->N = in; a->K = rows;
-    pick_split(h, out, in, rows, &a->splits, &a->k_per_split);
+    a->want_pre = 1;                  // planned for the conversion-free kernel; the caller launches it only with both pairs
+    pick_split(h, out, in, rows, &a->splits, &a->k_per_split, true);
 }
 
 // g0 holds d loss / d pre-activation of the last trunk layer, [B, hidden].
+// top_pair_scale != nullptr: the loss head left the top gradient as an fp16 pair in g16[cur] (scale from this device scalar)
+// and `top_colsum_blocks` partial rows of its column sums in colsum_part; no fp32 copy of it exists.
 static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, int accumulate, cudaStream_t s,
-                          bool top_amax_tracked = false) {
+                          bool top_amax_tracked = false, const float *top_pair_scale = nullptr, int top_colsum_blocks = 0) {
     const bool f16 = g_gemm_mode >= 5, pre16 = g_gemm_mode >= 6;
     bool dy_amax_valid = f16 && top_amax_tracked;   // the caller zeroed the gradient slots and the loss head filled the top one
     if (f16 && !top_amax_tracked) {
@@ -508,9 +516,9 @@ static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, i
         dy_amax_valid = true;
     }
     // which representations of the gradient entering layer l exist: fp32 in gbuf[cur], fp16 pair in g16[cur]
-    bool dy32 = true, dy16 = false;
+    bool dy32 = top_pair_scale == nullptr, dy16 = top_pair_scale != nullptr;
     bool db_done = false;                 // the dgrad above already reduced this layer's bias gradient (fused column sums)
-    const float *dy_scale = nullptr;
+    const float *dy_scale = top_pair_scale;
     for (int l = h->n_layers - 1; l >= 0; --l) {
         const Layer &L = h->layers[l];
         const int64_t rows = B * L.row_mult;
@@ -540,8 +548,9 @@ static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, i
             da.k_per_split = round_up(L.out_dim, 8); da.splits = 1;
             // the layer below left its ReLU decisions as one bit per element (same row-major element order, so the
             // encoder -> decoder flatten does not matter): the tensor-core dgrad reads those instead of the activations
-            if (h->relu_bits_valid[l - 1] && L.in_dim % 256 == 0) da.relu_bits = h->relu_bits[l - 1];
-            pre_d = dy_pair_ok && w16 && h->w_amax_valid && sgemm_uses_tc(SGEMM_DGRAD, da);
+            if (h->relu_bits_valid[l - 1] && L.in_dim % 128 == 0) da.relu_bits = h->relu_bits[l - 1];
+            da.want_pre = dy_pair_ok && w16 && h->w_amax_valid;
+            pre_d = da.want_pre && sgemm_uses_tc(SGEMM_DGRAD, da);
         }
         OCPPO_CHECK_ARG(!db_done || pre_w, "layer %d: bias gradient formed twice", l);
         if ((pre_w || pre_d) && !dy16) {        // the loss head's (or an FMA layer's) fp32 gradient, split once for both GEMMs
@@ -580,7 +589,8 @@ static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, i
             }
             if (!db_done) {
                 int blocks = 0;
-                OCPPO_TRY(launch_colsum16(h->g16_hi[cur], h->g16_lo[cur], rows, L.out_dim, dy_scale, h->colsum_part, &blocks, h->sm_count, s));
+                if (l == h->n_layers - 1 && top_colsum_blocks > 0) blocks = top_colsum_blocks;      // left by the loss head
+                else OCPPO_TRY(launch_colsum16(h->g16_hi[cur], h->g16_lo[cur], rows, L.out_dim, dy_scale, h->colsum_part, &blocks, h->sm_count, s));
                 OCPPO_TRY(launch_colsum_reduce(h->colsum_part, blocks, L.out_dim, h->grads + L.b_off, accumulate, s));
             }
             db_done = false;
@@ -996,16 +1006,34 @@ int ocppo_exponential(float *out, int64_t numel, uint64_t seed, uint64_t philox_
     return launch_exponential(out, numel, seed, philox_offset, as_stream(stream));
 }
 
-int ocppo_gae(const float *rewards, const float *values, const float *dones, const float *next_value,
-              const float *next_done, int64_t T, int64_t N, double gamma, double gae_lambda, float *advantages,
-              float *returns, void *stream) {
+static int gae_entry(const float *rewards, const float *values, const float *dones, const float *next_value,
+                     const float *next_done, int64_t T, int64_t N, double gamma, double gae_lambda, float *advantages,
+                     float *returns, int overlap_previous, void *stream) {
     OCPPO_CHECK_ARG(T >= 0 && N >= 0, "negative T/N");
     if (T == 0 || N == 0) return OCPPO_OK;
     OCPPO_CHECK_ARG(rewards && values && dones && next_value && next_done && advantages && returns,
                     "null pointer");
     DeviceGuard dg(device_of(rewards));
     return launch_gae(rewards, values, dones, next_value, next_done, T, N, (float)gamma,
-                      (float)(gamma * gae_lambda), advantages, returns, as_stream(stream));
+                      (float)(gamma * gae_lambda), advantages, returns, overlap_previous, as_stream(stream));
+}
+
+int ocppo_gae(const float *rewards, const float *values, const float *dones, const float *next_value,
+              const float *next_done, int64_t T, int64_t N, double gamma, double gae_lambda, float *advantages,
+              float *returns, void *stream) {
+    return gae_entry(rewards, values, dones, next_value, next_done, T, N, gamma, gae_lambda, advantages, returns, 0, stream);
+}
+
+int ocppo_gae_overlapped(const float *rewards, const float *values, const float *dones, const float *next_value,
+                         const float *next_done, int64_t T, int64_t N, double gamma, double gae_lambda,
+                         float *advantages, float *returns, void *stream) {
+    return gae_entry(rewards, values, dones, next_value, next_done, T, N, gamma, gae_lambda, advantages, returns, 1, stream);
+}
+
+int ocppo_set_gae_variant(int32_t variant) {
+    OCPPO_CHECK_ARG(variant == 0 || variant == 1, "gae variant must be 0 (TMA kernel where eligible) or 1 (cp.async kernel)");
+    g_gae_variant = variant;
+    return OCPPO_OK;
 }
 
 int ocppo_minibatch_fwd_bwd(ocppo_handle *h, const float *b_obs, const int64_t *b_actions, const float *b_logprobs,
@@ -1039,14 +1067,38 @@ int ocppo_minibatch_fwd_bwd(ocppo_handle *h, const float *b_obs, const int64_t *
         a.norm_adv = hp->norm_adv; a.clip_vloss = hp->clip_vloss;
         a.dh = h->gbuf[0]; a.gz = h->gz;
         const bool f16 = g_gemm_mode >= 5;
+        // fp16-pair storage: the loss head runs as two kernels -- forward (gz, statistics, the bound ingredient), then
+        // d(hidden) written straight as the pair the top layer's dgrad / wgrad load, with its column sums -- whenever
+        // the top layer's backward will run on pairs; otherwise one kernel leaves the fp32 gradient as before
+        const Layer &LT = h->layers[h->n_layers - 1];
+        const bool pair_top = g_gemm_mode >= 6 && h->n_layers >= 2 && loss_head_pair_supported(H, A) && h->g16_hi[0] != nullptr &&
+                              LT.out_dim % 64 == 0 && h->w_amax_valid && pair_ok(h, h->n_layers - 2, rows) &&
+                              (((uintptr_t)a.hidden) & 15) == 0;
         if (f16) {
             OCPPO_CUDA(cudaMemsetAsync(h->amax + kAmaxGrad, 0, 2 * OCPPO_MAX_LAYERS * sizeof(float), s));
             a.dh_amax = h->amax + kAmaxGrad + h->n_layers - 1;
         }
         a.part = h->loss_part + (int64_t)used * 8;
-        int blocks = 0;
+        int blocks = 0, top_colsum_blocks = 0;
         const int avail = (int)((kLossBlocksMax - used) / (n_chunks - ci));
-        OCPPO_TRY(launch_loss_head(h, a, &blocks, avail, s));
+        if (pair_top) {
+            OCPPO_CUDA(cudaMemsetAsync(h->amax, 0, sizeof(float), s));           // scratch slot 0: max (|dv| + sum |dz|)
+            a.gz_l1max = h->amax;
+            OCPPO_TRY(launch_loss_head(h, a, &blocks, avail, s, true));
+            LossBwdPairArgs b{};
+            b.gz = h->gz;
+            b.relu_bits = h->relu_bits_valid[h->n_layers - 1] ? h->relu_bits[h->n_layers - 1] : nullptr;
+            b.hidden = a.hidden;
+            b.Wa = a.Wa; b.Wc = a.Wc; b.gz_l1max = h->amax;
+            b.rows = rows; b.H = H; b.A = A; b.AP = AP;
+            b.dh_hi = h->g16_hi[0]; b.dh_lo = h->g16_lo[0];
+            b.bound = h->amax + kBndGrad + h->n_layers - 1;
+            b.dh_amax = a.dh_amax;
+            b.colsum_part = h->colsum_part;
+            OCPPO_TRY(launch_loss_head_bwd_pair(h, b, &top_colsum_blocks, s));
+        } else {
+            OCPPO_TRY(launch_loss_head(h, a, &blocks, avail, s));
+        }
         used += blocks;
         const int acc = ci > 0;
         // heads: d[Wa;Wc] = gz^T hidden, d[ba;bc] = colsum(gz)
@@ -1074,7 +1126,8 @@ int ocppo_minibatch_fwd_bwd(ocppo_handle *h, const float *b_obs, const int64_t *
             OCPPO_TRY(launch_splitk_reduce(h->splitk_bias, g.splits, AP, A, h->grads + h->actor.b_off, acc, h->sm_count, s));
             OCPPO_TRY(launch_splitk_reduce(h->splitk_bias + A, g.splits, AP, 1, h->grads + h->critic.b_off, acc, h->sm_count, s));
         }
-        OCPPO_TRY(trunk_backward(h, h->x0, rows, 0, acc, s, g_gemm_mode >= 5));
+        OCPPO_TRY(trunk_backward(h, h->x0, rows, 0, acc, s, g_gemm_mode >= 5,
+                                 pair_top ? h->amax + kBndGrad + h->n_layers - 1 : nullptr, top_colsum_blocks));
     }
     OCPPO_TRY(launch_loss_finalize(h->loss_part, used, mb, (float)hp->ent_coef, (float)hp->vf_coef, stats, s));
     return OCPPO_OK;

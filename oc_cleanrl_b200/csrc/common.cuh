@@ -178,6 +178,8 @@ struct SgemmArgs {
     const float *bnd_wl1;          //   weights) + *bnd_bmax (largest |bias|, may be null);
     const float *bnd_bmax;
     float *c_scale_src;            //   the kernel stores the bound here: the consumers' amax_a / amax_b
+    int want_pre;                  // planning hint for tc_gemm_supported(): the launch will carry both operands as fp16 pairs
+                                   // (that alone admits the 128-column tile for N % 256 != 0)
     int fma_bits;                  // FMA kernel, FWD: write relu_bits too (full 128-column tiles only)
     float *colsum_part;            // DGRAD, conversion-free kernel: [tc_gemm_ctas() * 4, N] column sums of C, pre-zeroed
 };
@@ -190,7 +192,7 @@ int tc_gemm_ctas(SgemmMode mode, const SgemmArgs &a, int sm_count);             
 void sgemm_engine_flags(int engine, SgemmArgs *b);                               // engine number -> tc_gemm variant flags
 int sgemm_fill_amax(SgemmMode mode, SgemmArgs *b, cudaStream_t stream);          // FP16x3: measure missing operand maxima
 bool sgemm_uses_tc(SgemmMode mode, const SgemmArgs &a);                          // what sgemm_launch will pick
-int tc_tile_n(bool single_acc);                                                   // N tile of the CTA pair: 128 (split accumulators) / 256
+int tc_tile_n(const SgemmArgs &a);                                                // N tile of the CTA pair: 256, 128 (pair operands, N % 256 != 0) or 0 (unsupported)
 // 0: fp32 FMA kernels only; 1: tcgen05 3xTF32 wherever the shape fits (fp32-grade accuracy; main and
 // correction products in separate TMEM accumulators); 2: same with a single, double-buffered accumulator
 extern int g_gemm_mode;
@@ -245,9 +247,12 @@ int launch_absmax_multi(const AbsmaxSegs &segs, cudaStream_t stream);           
 // out[0] = max |x[r, c]| over an [rows, cols] view with row stride ld (zeroed first); absmax.cu
 int launch_absmax(const float *x, int64_t rows, int64_t cols, int64_t ld, float *out, int sm_count, cudaStream_t stream);
 
+// tc_gemm.cu: plain 2-D fp32 TMA tile map (128-byte CUtensorMap written to tm_out), memoised
+int tma_map_2d_f32_plain(void *tm_out, const float *base, int64_t rows, int64_t cols, int box_rows, int box_cols);
+extern int g_gae_variant;
 int launch_gae(const float *rewards, const float *values, const float *dones,
                const float *next_value, const float *next_done, int64_t T, int64_t N, float g,
-               float c, float *adv, float *ret, cudaStream_t stream);
+               float c, float *adv, float *ret, int overlap_previous, cudaStream_t stream);
 
 struct LossArgs {
     const float *hidden;        // [rows, H] post-ReLU output of the last trunk layer
@@ -263,6 +268,23 @@ struct LossArgs {
     float *gz;                  // [rows, AP] d loss / d (logits, value), zero padded
     float *dh_amax;             // optional: atomicMax of |dh| as float bits (FP16x3 engine's operand scale); caller zeroes it
     double *part;               // [gridDim.x, 8] partial sums of the logged statistics
+    // two-kernel variant (fp16-pair storage): the first kernel stops at gz and records max_i (|dv_i| + sum_k |dz_ik|) here
+    // (float bits, caller zeroes it); the second kernel (launch_loss_head_bwd_pair) turns gz into d(hidden) as an fp16 pair
+    float *gz_l1max;
+};
+
+struct LossBwdPairArgs {
+    const float *gz;            // [rows, AP] from the forward kernel
+    const uint32_t *relu_bits;  // ReLU decisions of the last trunk layer, [rows, H/32] words; null -> `hidden` is read instead
+    const float *hidden;        // [rows, H] (only read when relu_bits is null)
+    const float *Wa, *Wc;       // head weights [A, H], [1, H]
+    const float *gz_l1max;      // device scalar written by the forward kernel
+    int64_t rows;
+    int H, A, AP;
+    void *dh_hi, *dh_lo;        // [rows, H] fp16 each, scaled by the power of two of  *bound = gz_l1max * max|W_head|
+    float *bound;               // written by block 0: what the consumers derive the pair's scale from
+    float *dh_amax;             // atomicMax of the true |dh| (float bits; caller zeroes it)
+    float *colsum_part;         // [blocks, H] column sums of dh (bias gradient of the last trunk layer)
 };
 
 int launch_policy_head(const ocppo_handle *h, const float *hidden, int64_t B, int64_t row_base, int64_t total_B,
@@ -275,7 +297,10 @@ int launch_gather(const ocppo_handle *h, const float *b_obs, const int64_t *b_ac
                   const float *b_adv, const float *b_ret, const float *b_val, const int64_t *idx, int64_t rows,
                   cudaStream_t stream);
 int launch_adv_stats(const ocppo_handle *h, const float *b_adv, const int64_t *idx, int64_t mb, cudaStream_t stream);
-int launch_loss_head(const ocppo_handle *h, LossArgs a, int *blocks_used, int blocks_avail, cudaStream_t stream);
+int launch_loss_head(const ocppo_handle *h, LossArgs a, int *blocks_used, int blocks_avail, cudaStream_t stream,
+                     bool forward_only = false);
+bool loss_head_pair_supported(int H, int A);
+int launch_loss_head_bwd_pair(const ocppo_handle *h, LossBwdPairArgs a, int *colsum_blocks, cudaStream_t stream);
 int launch_explained_var(const ocppo_handle *h, const float *y_pred, const float *y_true, int64_t n, float *out2,
                          cudaStream_t stream);
 int launch_loss_finalize(const double *part, int n_part, int64_t mb, float ent_coef, float vf_coef, float *stats,

@@ -132,6 +132,9 @@ policy_head_kernel(const float *__restrict__ hidden, int64_t B, int H, int A, co
                    const int64_t *__restrict__ given, int64_t *__restrict__ action, float *__restrict__ logp,
                    float *__restrict__ entropy, float *__restrict__ value, int want_policy) {
     extern __shared__ __align__(16) float sm[];
+    // a kernel launched as a programmatic dependent of this one (the GAE scan after the bootstrap ocppo_value call) may
+    // start its prologue now; it waits for this grid's completion before it reads the values written below
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     // graph-replayable calls keep (seed, offset) in device memory: kernel arguments are frozen at capture time
     if (philox_dev != nullptr) { L.seed = __ldg(philox_dev); L.offset = __ldg(philox_dev + 1); }
     float *sW = sm, *sB = sm + (size_t)(A + 1) * H;
@@ -281,7 +284,9 @@ __device__ __forceinline__ void ppo_sample_loss(const LossArgs &p, int64_t i, fl
 // HV > 0: H == 128 * HV, the sample's hidden row lives in registers (HV float4 per lane, read once with 16-byte
 // loads, the next sample's row prefetched while this one is processed) and d(hidden) leaves as float4 stores: the
 // kernel then runs at HBM rate (8*H bytes per sample).  HV == 0: any H, scalar loops.
-template <int HV>
+// BWD = false: the forward half only (logits, value, losses, gz = d loss / d (logits, value)) plus the bound ingredient
+// max_i (|dv_i| + sum_k |dz_ik|); loss_bwd_pair_kernel then writes d(hidden) straight as an fp16 pair.
+template <int HV, bool BWD>
 __global__ void __launch_bounds__(kHeadThreads) loss_head_kernel(LossArgs p) {
     extern __shared__ __align__(16) float sm[];
     const int A = p.A, H = p.H;
@@ -294,6 +299,7 @@ __global__ void __launch_bounds__(kHeadThreads) loss_head_kernel(LossArgs p) {
 
     double acc[6] = {0, 0, 0, 0, 0, 0};   // pg, vmax, entropy, -logratio, (ratio-1)-logratio, clipped
     float dmax = 0.f;                     // max |dh| written by this lane
+    float l1max = 0.f;                    // forward-only: max over this warp's samples of |dv| + sum_k |dz_k|
     const int64_t i0 = (int64_t)blockIdx.x * kWarpsPerBlock + warp, istep = (int64_t)gridDim.x * kWarpsPerBlock;
     if (HV > 0) {
         constexpr int NV = HV > 0 ? HV : 1;
@@ -319,6 +325,10 @@ __global__ void __launch_bounds__(kHeadThreads) loss_head_kernel(LossArgs p) {
             head_forward_vec<NV>(hv, sW, sB, A, H, lane, 0, z, v);
             float dz, dv;
             ppo_sample_loss(p, i, sc, z, v, lane, inv_mb, mean, stdv, dz, dv, acc);
+            if (!BWD) {
+                l1max = fmaxf(l1max, fabsf(dv) + warp_sum(fabsf(dz)));
+                continue;
+            }
             // d hidden = dv * Wc + sum_k dz_k * Wa[k], masked by the ReLU of the last trunk layer
             float4 s[NV];
 #pragma unroll
@@ -356,6 +366,10 @@ __global__ void __launch_bounds__(kHeadThreads) loss_head_kernel(LossArgs p) {
             warp_head_forward(h, sW, sB, A, H, lane, z, v);
             float dz, dv;
             ppo_sample_loss(p, i, load_sample_scalar(p, i, lane), z, v, lane, inv_mb, mean, stdv, dz, dv, acc);
+            if (!BWD) {
+                l1max = fmaxf(l1max, fabsf(dv) + warp_sum(fabsf(dz)));
+                continue;
+            }
             // d hidden, masked by ReLU of the last trunk layer
             // (warp-uniform trip count: the shuffles below need all 32 lanes, also when H % 32 != 0)
             for (int j0 = 0; j0 < H; j0 += 32) {
@@ -374,9 +388,13 @@ __global__ void __launch_bounds__(kHeadThreads) loss_head_kernel(LossArgs p) {
             }
         }
     }
-    if (p.dh_amax != nullptr) {
+    if (BWD && p.dh_amax != nullptr) {
         const unsigned m = __reduce_max_sync(kFull, __float_as_uint(dmax));
         if (lane == 0 && m != 0u) atomicMax(reinterpret_cast<unsigned int *>(p.dh_amax), m);
+    }
+    if (!BWD && p.gz_l1max != nullptr) {
+        const unsigned m = __reduce_max_sync(kFull, __float_as_uint(l1max));
+        if (lane == 0 && m != 0u) atomicMax(reinterpret_cast<unsigned int *>(p.gz_l1max), m);
     }
     __shared__ double red[kWarpsPerBlock][6];
     if (lane == 0)
@@ -389,14 +407,127 @@ __global__ void __launch_bounds__(kHeadThreads) loss_head_kernel(LossArgs p) {
     }
 }
 
+// d(hidden) = mask * (dv * Wc + sum_k dz_k * Wa[k]) written as the fp16 pair the trunk's backward GEMMs load, plus its column
+// sums (the last trunk layer's bias gradient) -- no fp32 copy of the gradient exists and no separate split pass runs.
+// The pair's scale must be fixed before the first element exists: |dh_j| <= (|dv| + sum_k |dz_k|) * max|W_head|, with the
+// first factor maximised over the minibatch chunk by the forward kernel.  Warp per sample, lane <-> 4 columns per
+// 128-column group; ReLU decisions come as the packed words the last trunk GEMM left (16 bytes per sample instead of
+// re-reading 2 KB of activations).  HBM-bound: 8 * H / 2 ... it writes 4 * H bytes and reads 4 * AP + H / 8 per sample.
+template <int HV>
+__global__ void __launch_bounds__(kHeadThreads) loss_bwd_pair_kernel(LossBwdPairArgs p) {
+    extern __shared__ __align__(16) float sm[];
+    const int A = p.A, H = p.H;
+    float *sW = sm;                                            // [(A + 1)][H], row A = critic
+    __shared__ float s_wmax[kWarpsPerBlock];
+    float wmax = 0.f;
+    for (int i = threadIdx.x; i < (A + 1) * H; i += blockDim.x) {
+        const float w = i < A * H ? p.Wa[i] : p.Wc[i - A * H];
+        sW[i] = w;
+        wmax = fmaxf(wmax, fabsf(w));
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    wmax = __uint_as_float(__reduce_max_sync(kFull, __float_as_uint(wmax)));
+    if (lane == 0) s_wmax[warp] = wmax;
+    __syncthreads();
+    wmax = 0.f;
+#pragma unroll
+    for (int w = 0; w < kWarpsPerBlock; ++w) wmax = fmaxf(wmax, s_wmax[w]);
+    const float bound = __ldg(p.gz_l1max) * wmax;
+    float scale, inv;
+    f16_scale_of(bound, scale, inv);
+    if (blockIdx.x == 0 && threadIdx.x == 0) *p.bound = bound;
+    constexpr int NV = HV;
+    const int wpr = H >> 5;                                    // ReLU decision words per sample
+    float4 csum[NV];
+#pragma unroll
+    for (int g = 0; g < NV; ++g) csum[g] = make_float4(0.f, 0.f, 0.f, 0.f);
+    float dmax = 0.f;
+    const int64_t i0 = (int64_t)blockIdx.x * kWarpsPerBlock + warp, istep = (int64_t)gridDim.x * kWarpsPerBlock;
+    float gz_next = 0.f;
+    uint32_t bits_next = 0u;
+    if (i0 < p.rows) {
+        if (lane < p.AP) gz_next = __ldg(p.gz + i0 * p.AP + lane);
+        if (p.relu_bits != nullptr && lane < wpr) bits_next = __ldg(p.relu_bits + i0 * wpr + lane);
+    }
+    for (int64_t i = i0; i < p.rows; i += istep) {
+        const float gzv = gz_next;
+        const uint32_t bitsv = bits_next;
+        if (i + istep < p.rows) {                              // next sample's 48 bytes while this one is processed
+            if (lane < p.AP) gz_next = __ldg(p.gz + (i + istep) * p.AP + lane);
+            if (p.relu_bits != nullptr && lane < wpr) bits_next = __ldg(p.relu_bits + (i + istep) * wpr + lane);
+        }
+        const float dv = __shfl_sync(kFull, gzv, A);
+        float4 s[NV];
+#pragma unroll
+        for (int g = 0; g < NV; ++g) {
+            const float4 w = *(reinterpret_cast<const float4 *>(sW + A * H + g * 128) + lane);
+            s[g] = make_float4(dv * w.x, dv * w.y, dv * w.z, dv * w.w);
+        }
+        for (int k = 0; k < A; ++k) {
+            const float dzk = __shfl_sync(kFull, gzv, k);
+#pragma unroll
+            for (int g = 0; g < NV; ++g) {
+                const float4 w = *(reinterpret_cast<const float4 *>(sW + k * H + g * 128) + lane);
+                s[g].x = fmaf(dzk, w.x, s[g].x);
+                s[g].y = fmaf(dzk, w.y, s[g].y);
+                s[g].z = fmaf(dzk, w.z, s[g].z);
+                s[g].w = fmaf(dzk, w.w, s[g].w);
+            }
+        }
+#pragma unroll
+        for (int g = 0; g < NV; ++g) {
+            uint32_t nib;
+            if (p.relu_bits != nullptr) {
+                // columns g * 128 + 4 * lane .. + 3 sit in word g * 4 + lane / 8, bits 4 * (lane % 8) ..
+                nib = (__shfl_sync(kFull, bitsv, g * 4 + (lane >> 3)) >> ((lane & 7) * 4)) & 0xFu;
+            } else {
+                const float4 hv = __ldcs(reinterpret_cast<const float4 *>(p.hidden + i * H + g * 128) + lane);
+                nib = (hv.x > 0.f ? 1u : 0u) | (hv.y > 0.f ? 2u : 0u) | (hv.z > 0.f ? 4u : 0u) | (hv.w > 0.f ? 8u : 0u);
+            }
+            const float4 o = make_float4((nib & 1u) ? s[g].x : 0.f, (nib & 2u) ? s[g].y : 0.f, (nib & 4u) ? s[g].z : 0.f,
+                                         (nib & 8u) ? s[g].w : 0.f);
+            uint32_t h0, l0, h1, l1;
+            split_f16x2(o.x, o.y, scale, h0, l0);
+            split_f16x2(o.z, o.w, scale, h1, l1);
+            const int64_t e = (i * H + g * 128) / 4 + lane;    // uint2 index: 4 fp16 per lane
+            __stcs(reinterpret_cast<uint2 *>(p.dh_hi) + e, make_uint2(h0, h1));
+            __stcs(reinterpret_cast<uint2 *>(p.dh_lo) + e, make_uint2(l0, l1));
+            csum[g].x += o.x; csum[g].y += o.y; csum[g].z += o.z; csum[g].w += o.w;
+            dmax = fmaxf(fmaxf(dmax, fmaxf(fabsf(o.x), fabsf(o.y))), fmaxf(fabsf(o.z), fabsf(o.w)));
+        }
+    }
+    if (p.dh_amax != nullptr) {
+        const unsigned m = __reduce_max_sync(kFull, __float_as_uint(dmax));
+        if (lane == 0 && m != 0u) atomicMax(reinterpret_cast<unsigned int *>(p.dh_amax), m);
+    }
+    // column sums: the block's eight warps fold in fixed order through shared memory (the head weights are dead)
+    __syncthreads();
+    float4 *red = reinterpret_cast<float4 *>(sm);              // [kWarpsPerBlock][H / 4]
+#pragma unroll
+    for (int g = 0; g < NV; ++g) red[warp * (H >> 2) + g * 32 + lane] = csum[g];
+    __syncthreads();
+    for (int c = threadIdx.x; c < (H >> 2); c += blockDim.x) {
+        float4 t = red[c];
+        for (int w = 1; w < kWarpsPerBlock; ++w) {
+            const float4 v = red[w * (H >> 2) + c];
+            t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w;
+        }
+        reinterpret_cast<float4 *>(p.colsum_part + (int64_t)blockIdx.x * H)[c] = t;
+    }
+}
+
 // Single block: ordered sum of the block partials -> the seven logged scalars.
 __global__ void loss_finalize_kernel(const double *__restrict__ part, int n_part, int64_t mb, float ent_coef,
                                      float vf_coef, float *__restrict__ stats) {
+    // one warp per statistic (blockDim = 6 x 32): lane l sums partials l, l + 32, ... in order, then a fixed shuffle
+    // tree -- deterministic, and ~30 dependent global loads instead of ~600 in one thread
     __shared__ double s[6];
-    if (threadIdx.x < 6) {
+    const int q = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (q < 6) {
         double a = 0;
-        for (int b = 0; b < n_part; ++b) a += part[(int64_t)b * 8 + threadIdx.x];
-        s[threadIdx.x] = a / (double)mb;
+        for (int b = lane; b < n_part; b += 32) a += part[(int64_t)b * 8 + q];
+        a = warp_sum_d(a);
+        if (lane == 0) s[q] = a / (double)mb;
     }
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -771,16 +902,17 @@ int launch_explained_var(const ocppo_handle *h, const float *y_pred, const float
     return OCPPO_OK;
 }
 
-int launch_loss_head(const ocppo_handle *h, LossArgs a, int *blocks_used, int blocks_avail, cudaStream_t stream) {
+int launch_loss_head(const ocppo_handle *h, LossArgs a, int *blocks_used, int blocks_avail, cudaStream_t stream,
+                     bool forward_only) {
     const int smem = head_smem_bytes(a.A, a.H);
     const bool aligned = ((((uintptr_t)a.hidden | (uintptr_t)a.dh) & 15) == 0);
-    void (*kern)(LossArgs) = loss_head_kernel<0>;
-    if (aligned && a.H == 128) kern = loss_head_kernel<1>;
-    else if (aligned && a.H == 256) kern = loss_head_kernel<2>;
-    else if (aligned && a.H == 512) kern = loss_head_kernel<4>;
-    else if (aligned && a.H == 1024) kern = loss_head_kernel<8>;
+    void (*kern)(LossArgs) = forward_only ? loss_head_kernel<0, false> : loss_head_kernel<0, true>;
+    if (aligned && a.H == 128) kern = forward_only ? loss_head_kernel<1, false> : loss_head_kernel<1, true>;
+    else if (aligned && a.H == 256) kern = forward_only ? loss_head_kernel<2, false> : loss_head_kernel<2, true>;
+    else if (aligned && a.H == 512) kern = forward_only ? loss_head_kernel<4, false> : loss_head_kernel<4, true>;
+    else if (aligned && a.H == 1024) kern = forward_only ? loss_head_kernel<8, false> : loss_head_kernel<8, true>;
     OCPPO_TRY(ensure_head_smem((const void *)kern, smem));
-    int cap = h->sm_count * 4;
+    int cap = h->sm_count * (forward_only ? 8 : 4);
     if (cap > blocks_avail) cap = blocks_avail;
     OCPPO_CHECK_ARG(cap >= 1, "loss head: out of partial-sum slots");
     const unsigned grid = grid_for(a.rows, kWarpsPerBlock, cap);
@@ -791,10 +923,33 @@ int launch_loss_head(const ocppo_handle *h, LossArgs a, int *blocks_used, int bl
     return OCPPO_OK;
 }
 
+bool loss_head_pair_supported(int H, int A) {
+    return (H == 128 || H == 256 || H == 512 || H == 1024) && A >= 1 && A + 1 <= 32;
+}
+
+int launch_loss_head_bwd_pair(const ocppo_handle *h, LossBwdPairArgs a, int *colsum_blocks, cudaStream_t stream) {
+    OCPPO_CHECK_ARG(loss_head_pair_supported(a.H, a.A), "loss head (pair output): unsupported H=%d A=%d", a.H, a.A);
+    // shared memory: the head weights, later the 8 x H column-sum fold
+    const int smem = (int)(sizeof(float) * (size_t)a.H * (a.A + 1 > kWarpsPerBlock ? a.A + 1 : kWarpsPerBlock));
+    void (*kern)(LossBwdPairArgs) = loss_bwd_pair_kernel<1>;
+    if (a.H == 256) kern = loss_bwd_pair_kernel<2>;
+    else if (a.H == 512) kern = loss_bwd_pair_kernel<4>;
+    else if (a.H == 1024) kern = loss_bwd_pair_kernel<8>;
+    OCPPO_TRY(ensure_head_smem((const void *)kern, smem));
+    int cap = h->sm_count * 4;
+    if (cap > kColsumBlocksMax) cap = kColsumBlocksMax;
+    const unsigned grid = grid_for(a.rows, kWarpsPerBlock, cap);
+    ProfScope ps(KC_HEAD, 1, stream);
+    kern<<<grid, kHeadThreads, smem, stream>>>(a);
+    OCPPO_LAUNCH_CHECK("loss_bwd_pair_kernel");
+    *colsum_blocks = (int)grid;
+    return OCPPO_OK;
+}
+
 int launch_loss_finalize(const double *part, int n_part, int64_t mb, float ent_coef, float vf_coef, float *stats,
                          cudaStream_t stream) {
     ProfScope ps(KC_AUX, 1, stream);
-    loss_finalize_kernel<<<1, 32, 0, stream>>>(part, n_part, mb, ent_coef, vf_coef, stats);
+    loss_finalize_kernel<<<1, 192, 0, stream>>>(part, n_part, mb, ent_coef, vf_coef, stats);
     OCPPO_LAUNCH_CHECK("loss_finalize_kernel");
     return OCPPO_OK;
 }

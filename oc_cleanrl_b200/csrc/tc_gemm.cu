@@ -45,14 +45,17 @@ constexpr int TM = 128;                                     // rows of A (and of
 // A 128-column tile would let the split scheme double-buffer too, and was measured: 10-50 % SLOWER on every trunk
 // shape with K >= 512 -- at N = 128 the MMA re-reads its A operand from shared memory twice as often per flop
 // (SS mode: 128 B/cycle of operand traffic, the whole shared-memory bandwidth), so the kernel becomes smem-bound.
-template <bool SPLIT> struct Tile {
-    static constexpr int TN = 256;
+// (A 128-column tile exists all the same, for the conversion-free kernel only: layer widths that are a multiple of 128 but
+// not of 256 -- the reference class's own default encoder_dims=(128, 64), 384-wide layers -- would otherwise leave the
+// tensor cores altogether and run on the 9x slower FMA kernel.)
+template <bool SPLIT, int TN_> struct Tile {
+    static constexpr int TN = TN_;
     static constexpr int TBW = TN / 2;                      // columns of B staged per CTA
-    static constexpr int kStageBytesB = TBW * 32 * 4;       // 16 KB
+    static constexpr int kStageBytesB = TBW * 32 * 4;       // 16 KB (8 KB for the 128-column tile)
     static constexpr int kStageBytes = 2 * (128 * 32 * 4 + kStageBytesB);   // hi + lo: 64 KB
     static constexpr int kNumStages = 3;                    // 192 KB
-    static constexpr int kAccBufs = SPLIT ? 1 : 2;          // tiles whose accumulators fit in 512 TMEM columns
-    static constexpr int kAccStride = SPLIT ? 512 : 256;    // TMEM columns per tile
+    static constexpr int kAccStride = SPLIT ? 2 * TN : TN;  // TMEM columns per tile
+    static constexpr int kAccBufs = 512 / kAccStride >= 2 ? 2 : 1;   // tiles whose accumulators fit in 512 TMEM columns
 };
 constexpr int TK = 32;
 constexpr int kPairM = 2 * TM;                              // 256-row tile per CTA pair
@@ -388,7 +391,7 @@ __device__ __forceinline__ TileCoord tile_coord(const SgemmArgs &p, int tile, in
         : "r"(taddr)                                                                                                \
         : "memory")
 
-template <int MODE, bool SPLIT, int CORR>      // CORR: 0 = TF32 corrections, 1 = BF16 corrections, 2 = FP16 x 3 (no TF32 pass)
+template <int MODE, bool SPLIT, int CORR, int TN_ = 256>      // CORR: 0 = TF32 corrections, 1 = BF16 corrections, 2 = FP16 x 3 (no TF32 pass), 3 = FP16 x 3 on pair storage
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid0 : kTcThreads, 1) tc_gemm_kernel(SgemmArgs p, int nt_n, int nt_m, int ntiles, const __grid_constant__ CUtensorMap tmA,
                                                                                          const __grid_constant__ CUtensorMap tmB,
                                                                                          const __grid_constant__ CUtensorMap tmC,
@@ -399,9 +402,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
     constexpr bool A_MN = (MODE == SGEMM_WGRAD);
     constexpr bool B_MN = (MODE != SGEMM_FWD);
     constexpr bool CORR16 = CORR >= 1, F16 = CORR >= 2, PRE = CORR == 3;   // PRE: both operands arrive as fp16 hi / lo pairs
-    constexpr int TN = Tile<SPLIT>::TN, TBW = Tile<SPLIT>::TBW, kStageBytesB = Tile<SPLIT>::kStageBytesB;
-    constexpr int kStageBytes = Tile<SPLIT>::kStageBytes, kNumStages = Tile<SPLIT>::kNumStages;
-    constexpr int kAccStride = Tile<SPLIT>::kAccStride, kAccBufs = Tile<SPLIT>::kAccBufs;
+    typedef Tile<SPLIT, TN_> TileT;
+    static_assert(TN_ == 256 || (TN_ == 128 && CORR == 3), "the 128-column tile exists for the conversion-free kernel only");
+    constexpr int TN = TileT::TN, TBW = TileT::TBW, kStageBytesB = TileT::kStageBytesB;
+    constexpr int kStageBytes = TileT::kStageBytes, kNumStages = TileT::kNumStages;
+    constexpr int kAccStride = TileT::kAccStride, kAccBufs = TileT::kAccBufs;
     // MMA instructions chained into the (main) accumulator per 32-deep stage: 4 main products, plus the corrections when
     // they share the accumulator (8 TF32 or 4 BF16; a K = 16 BF16 instruction loses about 1.5x what a K = 8 TF32 one does)
     // FP16 x 3: calibrated on zero-mean products (tools/acc_sweep.sh) -- every GEMM of the trunk multiplies a signed operand,
@@ -544,7 +549,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
             // the accumulator is complete (DGRAD), or written chunk by chunk (FWD)
             uint4 rb = make_uint4(0u, 0u, 0u, 0u);
             const int64_t rb_off = (int64_t)(m_loc + lane) * (p.N >> 5) + (n_loc >> 5);
-            if (bits && m_loc + lane < p.M) rb = __ldg(reinterpret_cast<const uint4 *>(p.relu_bits + rb_off));
+            if (bits && m_loc + lane < p.M) {
+                if (TN == 256) rb = __ldg(reinterpret_cast<const uint4 *>(p.relu_bits + rb_off));
+                else { const uint2 r2 = __ldg(reinterpret_cast<const uint2 *>(p.relu_bits + rb_off)); rb.x = r2.x; rb.y = r2.y; }
+            }
             if (F16) mbar_wait_sleep(bar_tfull + 8 * acc, (uint32_t)((ai / nbuf) & 1), 200);
             else mbar_wait(bar_tfull + 8 * acc, (uint32_t)((ai / nbuf) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -792,15 +800,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
                         const uint32_t st = smem_u32(smem + s * stage_bytes), bar = bar_tma + 8 * s;
                         const int k0 = (int)(t.kbeg + (int64_t)kb * TK);
                         mbar_wait(bar_empty + 8 * s, (uint32_t)(sphase ^ 1));
-                        mbar_expect_tx(bar, kStageBytesA + kStageBytesB);
-                        if (A_MN) {
+                        // (bring-up timing experiments, results are garbage: 512 = no B loads, 1024 = no A loads)
+                        const bool skip_b = (p.dbg & 512) != 0, skip_a = (p.dbg & 1024) != 0;
+                        mbar_expect_tx(bar, (skip_a ? 0 : kStageBytesA) + (skip_b ? 0 : kStageBytesB));
+                        if (skip_a) {
+                        } else if (A_MN) {
                             tma_load_3d(st + kOffA16, &tmA, 0, k0, (t.m0 + rank_m) >> 6, bar);
                             tma_load_3d(st + kOffALo, &tmA2, 0, k0, (t.m0 + rank_m) >> 6, bar);
                         } else {
                             tma_load_2d(st + kOffA16, &tmA, k0, t.m0 + rank_m, bar);
                             tma_load_2d(st + kOffALo, &tmA2, k0, t.m0 + rank_m, bar);
                         }
-                        if (B_MN) {
+                        if (skip_b) {
+                        } else if (B_MN) {
                             tma_load_3d(st + kOffB16, &tmB, 0, k0, (t.n0 + rank_n) >> 6, bar);
                             tma_load_3d(st + kOffBLo, &tmB2, 0, k0, (t.n0 + rank_n) >> 6, bar);
                         } else {
@@ -851,7 +863,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
             }
         }
         __syncwarp();
-    } else if (!PRE) {
+    } else if constexpr (!PRE) {
         // ===================== producers =====================
         const int pt = tid - kProdTid0;
         const int pwarp_lane0 = (lane == 0);
@@ -922,11 +934,17 @@ inline bool al16(const void *p) { return (((uintptr_t)p) & 15) == 0; }
 }  // namespace
 
 // Shapes the tensor-core kernel takes; everything else stays on the FMA kernel.
-int tc_tile_n(bool single_acc) { return single_acc ? Tile<false>::TN : Tile<true>::TN; }   // both 256 today
+// N tile of the CTA pair for a GEMM with N output columns: 256, or 128 when N is a multiple of 128 only AND the launch will
+// be the conversion-free kernel (both operands as fp16 pairs: present already, or promised by the planner with want_pre)
+int tc_tile_n(const SgemmArgs &a) {
+    if (a.N % 256 == 0) return 256;
+    const bool pre = a.f16x3 && ((a.a16_hi != nullptr && a.b16_hi != nullptr) || a.want_pre);
+    return (pre && a.N % 128 == 0) ? 128 : 0;
+}
 
 bool tc_gemm_supported(SgemmMode mode, const SgemmArgs &a) {
     if (a.M <= 0 || a.N <= 0 || a.K <= 0) return false;
-    if (a.N % tc_tile_n(a.single_acc != 0) != 0) return false;
+    if (tc_tile_n(a) == 0) return false;
     if ((a.lda & 3) || (a.ldb & 3) || (a.ldc & 3) || !al16(a.A) || !al16(a.B) || !al16(a.C)) return false;
     if (mode == SGEMM_WGRAD) {
         if (a.M % TM != 0) return false;
@@ -1076,8 +1094,31 @@ int make_map_c16(CUtensorMap *tm, const void *base, int64_t rows, int64_t cols, 
 
 }  // namespace
 
-int tc_gemm_ctas(SgemmMode mode, const SgemmArgs &a, int sm_count) {
-    const int tn = tc_tile_n(a.single_acc != 0);
+// Plain (unswizzled) 2-D fp32 tile map over a row-major [rows, cols] tensor, box = box_rows x box_cols, zero fill outside:
+// the GAE kernel's loads and stores (gae.cu).  `tm_out` is a CUtensorMap (128 bytes, 64-byte aligned); memoised like the
+// GEMM maps.
+int tma_map_2d_f32_plain(void *tm_out, const float *base, int64_t rows, int64_t cols, int box_rows, int box_cols) {
+    CUtensorMap *tm = reinterpret_cast<CUtensorMap *>(tm_out);
+    const MapKey key{4, base, rows, cols, cols, box_rows * 65536 + box_cols};
+    if (map_lookup(key, tm)) return OCPPO_OK;
+    EncodeTiledFn fn = encode_fn();
+    if (fn == nullptr) { set_error("cuTensorMapEncodeTiled entry point not available"); return OCPPO_ECUDA; }
+    const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)cols * 4};
+    const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows}, estr[2] = {1, 1};
+    const CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (plain 2-D map) failed (%d)", (int)r); return OCPPO_ECUDA; }
+    map_store(key, *tm);
+    return OCPPO_OK;
+}
+
+int tc_gemm_ctas(SgemmMode mode, const SgemmArgs &a_in, int sm_count) {
+    SgemmArgs a = a_in;
+    if (!a.f16x3) sgemm_engine_flags(g_gemm_mode, &a);       // planning structs carry no engine flags yet
+    const int tn = tc_tile_n(a);
+    if (tn == 0) return 0;
     const int64_t ntiles = (int64_t)(a.N / tn) * ceil_div(a.M, kPairM) * (mode == SGEMM_WGRAD ? a.splits : 1);
     return (int)(2 * (ntiles < sm_count / 2 ? ntiles : sm_count / 2));
 }
@@ -1096,14 +1137,14 @@ int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
     OCPPO_CHECK_ARG(tc_gemm_supported(mode, a), "tc_gemm: unsupported shape M=%d N=%d K=%lld", a.M, a.N, (long long)a.K);
     const int splits = mode == SGEMM_WGRAD ? a.splits : 1;
     const bool split = a.single_acc == 0;
-    const int tn = tc_tile_n(!split);
+    const int tn = tc_tile_n(a);
     const int nt_n = a.N / tn, nt_m = (int)ceil_div(a.M, kPairM);
     const int64_t ntiles64 = (int64_t)nt_n * nt_m * splits;
     OCPPO_CHECK_ARG(ntiles64 < (1LL << 31), "tc_gemm: too many tiles");
     const int ntiles = (int)ntiles64;
     typedef void (*Kern)(SgemmArgs, int, int, int, const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap,
                          const CUtensorMap, const CUtensorMap);
-    constexpr int kVariants = 7;
+    constexpr int kVariants = 9;
     static const Kern kerns[kVariants][3] = {
         {tc_gemm_kernel<SGEMM_FWD, false, 0>, tc_gemm_kernel<SGEMM_DGRAD, false, 0>, tc_gemm_kernel<SGEMM_WGRAD, false, 0>},
         {tc_gemm_kernel<SGEMM_FWD, true, 0>, tc_gemm_kernel<SGEMM_DGRAD, true, 0>, tc_gemm_kernel<SGEMM_WGRAD, true, 0>},
@@ -1111,7 +1152,9 @@ int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
         {tc_gemm_kernel<SGEMM_FWD, false, 1>, tc_gemm_kernel<SGEMM_DGRAD, false, 1>, tc_gemm_kernel<SGEMM_WGRAD, false, 1>},
         {tc_gemm_kernel<SGEMM_FWD, true, 2>, tc_gemm_kernel<SGEMM_DGRAD, true, 2>, tc_gemm_kernel<SGEMM_WGRAD, true, 2>},
         {tc_gemm_kernel<SGEMM_FWD, true, 3>, tc_gemm_kernel<SGEMM_DGRAD, true, 3>, tc_gemm_kernel<SGEMM_WGRAD, true, 3>},
-        {tc_gemm_kernel<SGEMM_FWD, false, 3>, tc_gemm_kernel<SGEMM_DGRAD, false, 3>, tc_gemm_kernel<SGEMM_WGRAD, false, 3>}};
+        {tc_gemm_kernel<SGEMM_FWD, false, 3>, tc_gemm_kernel<SGEMM_DGRAD, false, 3>, tc_gemm_kernel<SGEMM_WGRAD, false, 3>},
+        {tc_gemm_kernel<SGEMM_FWD, true, 3, 128>, tc_gemm_kernel<SGEMM_DGRAD, true, 3, 128>, tc_gemm_kernel<SGEMM_WGRAD, true, 3, 128>},
+        {tc_gemm_kernel<SGEMM_FWD, false, 3, 128>, tc_gemm_kernel<SGEMM_DGRAD, false, 3, 128>, tc_gemm_kernel<SGEMM_WGRAD, false, 3, 128>}};
     // per device: SM count, and the opt-in shared-memory size (a function attribute lives in the device's context)
     static int sms_of[kMaxDevices] = {0};
     int dev = 0;
@@ -1176,7 +1219,9 @@ int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
     OCPPO_CHECK_ARG(!a.f16x3 || ((split || pre) && a.amax_a != nullptr && a.amax_b != nullptr), "tc_gemm: the FP16x3 engine needs both operands' max-abs");
     // fp16-pair storage with one accumulator (engine 8): FWD / DGRAD overlap their epilogue with the next tile's mainloop;
     // WGRAD drains only every 128 stages and keeps the split accumulators' 3x smaller rounding error
-    const int variant = a.f16x3 ? (pre ? ((split || (mode == SGEMM_WGRAD && !(dbg & 256))) ? 5 : 6) : 4) : (split ? (a.corr_bf16 ? 2 : 1) : (a.corr_bf16 ? 3 : 0));
+    OCPPO_CHECK_ARG(tn == 256 || pre, "tc_gemm: the 128-column tile needs both operands as fp16 pairs (N=%d)", a.N);
+    int variant = a.f16x3 ? (pre ? ((split || (mode == SGEMM_WGRAD && !(dbg & 256))) ? 5 : 6) : 4) : (split ? (a.corr_bf16 ? 2 : 1) : (a.corr_bf16 ? 3 : 0));
+    if (tn == 128) variant += 2;            // 5 / 6 -> 7 / 8
     kerns[variant][mi]<<<grid, pre ? kProdTid0 : kTcThreads, kTcSmemBytes, stream>>>(a, nt_n, nt_m, ntiles, tmA, tmB, tmC, tmX, tmB2, tmA2, tmC2);
     OCPPO_LAUNCH_CHECK("tc_gemm_kernel");
     return OCPPO_OK;

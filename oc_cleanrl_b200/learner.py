@@ -57,8 +57,10 @@ class LearnerArgs:
         return int(self.batch_size // self.num_minibatches)
 
 
-def compute_gae(rewards, values, dones, next_value, next_done, gamma, gae_lambda, out=None):
-    """Stateless GAE on (T,N) fp32 CUDA tensors -> (advantages, returns)."""
+def compute_gae(rewards, values, dones, next_value, next_done, gamma, gae_lambda, out=None, overlap_previous=False):
+    """Stateless GAE on (T,N) fp32 CUDA tensors -> (advantages, returns).  ``overlap_previous``: launch the scan as a
+    programmatic dependent of the kernel before it on the stream (``ocppo_gae_overlapped``) -- only when that kernel
+    writes none of the five buffers but ``next_value``."""
     for t in (rewards, values, dones, next_value, next_done):
         if not t.is_cuda or t.dtype != torch.float32:
             raise _abi.OcppoError("compute_gae needs fp32 CUDA tensors (no CPU path)")
@@ -73,9 +75,9 @@ def compute_gae(rewards, values, dones, next_value, next_done, gamma, gae_lambda
     else:
         advantages, returns = out
     stream = C.c_void_p(torch.cuda.current_stream(rewards.device).cuda_stream)
-    _abi.check(_abi.lib().ocppo_gae(_abi.ptr(rewards), _abi.ptr(values), _abi.ptr(dones), _abi.ptr(next_value),
-                                   _abi.ptr(next_done), T, N, float(gamma), float(gae_lambda),
-                                   _abi.ptr(advantages), _abi.ptr(returns), stream))
+    fn = _abi.lib().ocppo_gae_overlapped if overlap_previous else _abi.lib().ocppo_gae
+    _abi.check(fn(_abi.ptr(rewards), _abi.ptr(values), _abi.ptr(dones), _abi.ptr(next_value),
+          _abi.ptr(next_done), T, N, float(gamma), float(gae_lambda), _abi.ptr(advantages), _abi.ptr(returns), stream))
     return advantages, returns
 
 
@@ -151,8 +153,9 @@ class PPOLearner:
             next_value = self.agent.get_value(next_obs).reshape(-1)
         if self._gae_out is None or self._gae_out[0].shape != rewards.shape:
             self._gae_out = (torch.empty_like(rewards), torch.empty_like(rewards))
+        # the kernel before the scan is get_value's head kernel, whose only output is next_value: the scan may overlap it
         return compute_gae(rewards, values, dones, next_value, next_done, self.args.gamma, self.args.gae_lambda,
-                           out=self._gae_out)
+                           out=self._gae_out, overlap_previous=True)
 
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)

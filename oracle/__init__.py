@@ -7,7 +7,7 @@ as the checker / the CPU arm, never as the thing shipped.
 
 Parity status: PINNED against the reference's own ``PPObj`` class imported
 from ``/root/reference/cleanrl/architectures/ppo.py`` in the build container
-(``tests/test_oracle_vs_reference.py``; golden vectors written by
+(``tests/test_oracle_cpu.py::test_oracle_model_equals_reference_model``; golden vectors written by
 ``tests/golden/make_golden.py`` and committed under ``tests/golden/``).  The
 reference's learner loop is inline ``__main__`` code that cannot be imported
 (its module-level imports need gymnasium / stable_baselines3 / ocatari_wrappers,

@@ -78,7 +78,7 @@ def _layer_init(layer, std=np.sqrt(2), bias_const=0.0):
 class OraclePPObj(nn.Module):
     """Restatement of ``PPObj``; consumes the torch RNG in the same order so
     that ``torch.manual_seed(s); OraclePPObj(...)`` reproduces the reference's
-    initial weights bit for bit (checked in tests/test_oracle_vs_reference.py).
+    initial weights bit for bit (checked in tests/test_oracle_cpu.py::test_oracle_model_equals_reference_model).
     """
 
     def __init__(self, envs, device="cpu", encoder_dims=(128, 64), decoder_dims=(32,)):

@@ -35,6 +35,28 @@ def test_gemm_engine_vs_fp64(built_lib, engine, op, M, N, K, S):
         assert float(msg.split("bias_rel=")[1].split()[0]) < 2e-5, msg
 
 
+# widths that are a multiple of 128 but not of 256 (the reference class's own default encoder_dims=(128, 64); 384-wide
+# layers): the conversion-free kernel's 128-column tile.  Engines 1-5 have no such tile (those shapes run on the FMA kernel).
+CASES_128 = [
+    (0, 4096, 128, 256, 1), (0, 1000, 384, 128, 1), (0, 32768, 640, 512, 1),
+    (1, 4096, 128, 512, 1), (1, 640, 384, 256, 1), (1, 19999, 128, 384, 1),
+    (2, 256, 128, 4096, 4), (2, 128, 384, 8192, 8), (2, 384, 128, 16384, 9), (2, 640, 1152, 32768, 19),
+]
+
+
+@pytest.mark.parametrize("engine", [6, 7, 8])
+@pytest.mark.parametrize("op,M,N,K,S", CASES_128)
+def test_gemm_128_column_tile_vs_fp64(built_lib, engine, op, M, N, K, S):
+    import gemm_diag
+    if engine == 7 and op == 2:
+        pytest.skip("weight gradients always leave in fp32")
+    msg = gemm_diag.run(op, engine, M, N, K, S, "randn", seed=op * 7 + M)
+    assert "BAD" not in msg and "rc=" not in msg, msg
+    assert float(msg.split("rel_err=")[1].split()[0]) < 2e-5, msg
+    if op == 2:
+        assert float(msg.split("bias_rel=")[1].split()[0]) < 2e-5, msg
+
+
 @pytest.mark.parametrize("kind", ["wide", "big", "small", "zero", "relu", "tiny+relu"])
 @pytest.mark.parametrize("op,M,N,K,S", [(0, 1000, 512, 256, 1), (1, 640, 1024, 512, 1), (2, 256, 512, 8192, 4)])
 @pytest.mark.parametrize("engine", [5, 6, 7, 8])

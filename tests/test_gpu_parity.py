@@ -69,18 +69,44 @@ def agent_flat_grad(agent):
 
 
 # ---------------------------------------------------------------- GAE ------
+@pytest.mark.parametrize("variant", [0, 1])
 @pytest.mark.parametrize("T,N", [(123, 7), (128, 4096), (1, 1), (2, 33), (5, 4), (128, 4098), (300, 64),
-                                 (31, 32), (33, 36), (128, 8)])
-def test_gae_bit_exact_vs_reference_loop(dev, T, N):
+                                 (31, 32), (33, 36), (128, 8), (1, 4), (129, 36), (257, 100), (64, 160), (700, 44)])
+def test_gae_bit_exact_vs_reference_loop(dev, built_lib, T, N, variant):
+    """Both kernels (0: TMA + warp-specialised, taken when N % 4 == 0; 1: cp.async, the fallback) on the shapes of the
+    reference's only numeric test (tests/test_jax_compute_gae.py:69-91: 123 x 7, exact equality) and on ragged / tiny /
+    long rollouts: T not a multiple of the 32-step tile, T > 128 (stage ring reuse), N not a multiple of the 32-env slab."""
     from oc_cleanrl_b200.learner import compute_gae
     d = make_gae_inputs(T, N, seed=42)
     adv_ref, ret_ref = ref_ppo.ref_gae(d["rewards"], d["values"], d["dones"], d["next_value"], d["next_done"],
                                        0.99, 0.95)
     g = {k: v.to(dev) for k, v in d.items()}
-    adv, ret = compute_gae(g["rewards"], g["values"], g["dones"], g["next_value"], g["next_done"], 0.99, 0.95)
-    torch.cuda.synchronize()
+    assert built_lib.ocppo_set_gae_variant(variant) == 0
+    try:
+        out = (torch.full((T, N), float("nan"), device=dev), torch.full((T, N), float("nan"), device=dev))
+        adv, ret = compute_gae(g["rewards"], g["values"], g["dones"], g["next_value"], g["next_done"], 0.99, 0.95, out=out)
+        torch.cuda.synchronize()
+    finally:
+        built_lib.ocppo_set_gae_variant(0)
     assert torch.equal(adv.cpu(), adv_ref), f"adv max diff {(adv.cpu() - adv_ref).abs().max()}"
     assert torch.equal(ret.cpu(), ret_ref), f"ret max diff {(ret.cpu() - ret_ref).abs().max()}"
+
+
+def test_gae_writes_nothing_outside_its_buffers(dev, built_lib):
+    """Ragged N and T through the TMA kernel: its tiles overhang the buffers (32 x 32 boxes), the stores must be clipped."""
+    from oc_cleanrl_b200.learner import compute_gae
+    T, N = 37, 44
+    d = make_gae_inputs(T, N, seed=3)
+    g = {k: v.to(dev) for k, v in d.items()}
+    pad = 4096
+    big = [torch.full((T * N + 2 * pad,), 7.5, device=dev) for _ in range(2)]
+    out = tuple(b[pad:pad + T * N].view(T, N) for b in big)
+    compute_gae(g["rewards"], g["values"], g["dones"], g["next_value"], g["next_done"], 0.99, 0.95, out=out)
+    torch.cuda.synchronize()
+    adv_ref, ret_ref = ref_ppo.ref_gae(d["rewards"], d["values"], d["dones"], d["next_value"], d["next_done"], 0.99, 0.95)
+    assert torch.equal(out[0].cpu(), adv_ref) and torch.equal(out[1].cpu(), ret_ref)
+    for b in big:
+        assert bool((b[:pad] == 7.5).all()) and bool((b[pad + T * N:] == 7.5).all())
 
 
 def test_gae_empty_and_sparse_rollout(dev, built_lib):
@@ -399,6 +425,83 @@ def test_single_update_step_vs_live_oracle_other_games(dev, game, D, A, gemm_eng
     assert np.allclose(got, want, rtol=REL_TOL, atol=1e-6), (got, want)
     assert np.allclose(out["grad_norms"][0], float(trace[0]["gn"]), rtol=REL_TOL)
     assert rel_err(agent_flat(agent), ref_ppo.flat_params(oracle).numpy()) < REL_TOL
+
+
+@pytest.mark.parametrize("enc,dec,tc_layers,tc_dgrads", [((128, 384), (128,), 2, 2), ((128, 64), (32,), 0, 2),
+                                                         ((384, 128, 256), (640,), 3, 3)])
+@pytest.mark.parametrize("engine", [6, 8])
+def test_minibatch_gradients_with_widths_off_the_256_grid(dev, built_lib, enc, dec, tc_layers, tc_dgrads, engine):
+    """Trunk widths that are multiples of 128 but not of 256 take the conversion-free kernel's 128-column tile (forward,
+    dgrad and wgrad on the tensor cores); the reference class's own constructor default ``(128, 64), (32,)``
+    (architectures/ppo.py:61) has 64- and 32-wide layers, which stay on the CUDA-core kernels.  Rollout forward, loss
+    statistics and every gradient tensor of a 2,048-sample minibatch against the CPU oracle -- evaluated, as in
+    test_full_size_minibatch_properties, under the ReLU decisions the device path took, each differing decision proven
+    undecidable in fp32 -- and the launch counters say which kernels ran."""
+    from oc_cleanrl_b200 import _abi
+    from oc_cleanrl_b200.learner import LearnerArgs, PPOLearner
+    default = built_lib.ocppo_get_gemm_mode()
+    assert built_lib.ocppo_set_gemm_mode(engine) == 0
+    try:
+        F, D, A, T, N = 4, 6, 6, 128, 16
+        n = T * N
+        agent, oracle = make_pair(dev, F, D, A, enc, dec)
+        data = make_rollout(T, N, F, D, seed=78)
+        obs = data["obs"].to(dev)
+        torch.cuda.manual_seed(3)
+        with torch.no_grad():
+            action, logp, _, value = agent.get_action_and_value(obs.reshape(n, F, D))
+            _, logp_ref, _, value_ref = oracle.get_action_and_value(data["obs"].reshape(n, F, D), action.cpu())
+        assert rel_err(value.cpu().numpy(), value_ref.numpy()) < REL_TOL
+        assert np.allclose(logp.cpu().numpy(), logp_ref.numpy(), rtol=REL_TOL, atol=1e-5)
+        rs = np.random.RandomState(2)
+        cpu = (data["obs"].reshape(n, F, D), action.cpu(), logp.cpu(), torch.as_tensor(rs.randn(n), dtype=torch.float32),
+               torch.as_tensor(rs.randn(n), dtype=torch.float32), value.reshape(-1).cpu())
+        flat = tuple(t.to(dev) for t in cpu)
+        flat = (flat[0].reshape(n, -1),) + flat[1:]
+        idx = torch.as_tensor(rs.permutation(n), dtype=torch.int64).to(dev)
+        learner = PPOLearner(agent, LearnerArgs(num_envs=N, num_steps=T))
+        agent._ensure_workspace(n, training=True, exact=True)
+        stats = torch.zeros(8, device=dev)
+        c0, _ = _abi.launch_counts()
+        _abi.check(built_lib.ocppo_minibatch_fwd_bwd(agent._handle.raw, *[_abi.ptr(t) for t in flat], _abi.ptr(idx), n,
+                                                     C.byref(learner._hp), _abi.ptr(stats), agent._stream()))
+        torch.cuda.synchronize()
+        c1, _ = _abi.launch_counts()
+        assert c1["gemm_fwd"] - c0["gemm_fwd"] == tc_layers           # tcgen05 launches of this minibatch
+        assert c1["gemm_wgrad"] - c0["gemm_wgrad"] == tc_layers
+        # (a dgrad's N is the layer's INPUT width: 128 -> 64 and 256 -> 32 still have 128- / 256-wide input gradients)
+        assert c1["gemm_dgrad"] - c0["gemm_dgrad"] == tc_dgrads
+        grad = agent_flat_grad(agent)
+        masks = []
+        for l, width in enumerate(enc + dec):
+            act = torch.empty(n * (F if l < len(enc) else 1), width, device=dev)
+            _abi.check(built_lib.ocppo_read_activation(agent._handle.raw, l, n, _abi.ptr(act), agent._stream()))
+            torch.cuda.synchronize()
+            masks.append((act > 0).cpu())
+        with ref_ppo.relu_decisions(oracle, masks) as rd:
+            loss, ref_stats = ref_ppo.ref_minibatch_loss(oracle, *cpu, idx.cpu().numpy(), ref_ppo.PPOArgs())
+        loss.backward()
+        want = np.array([float(ref_stats[k]) for k in STAT_KEYS])
+        assert np.allclose(stats.cpu().numpy()[:7], want, rtol=REL_TOL, atol=1e-6), (stats, want)
+        g_ref = ref_ppo.flat_grads(oracle).numpy()
+        off = prev_k = 0
+        for i, q in enumerate(agent.parameters()):
+            k = q.numel()
+            lo = off - prev_k if k == 1 else off          # the critic's 1-element bias gradient is scaled with its weight tensor
+            e = rel_err(grad[lo:off + k], g_ref[lo:off + k])
+            assert e < REL_TOL, f"tensor {i}: {e:.3e} vs the oracle under the device path's ReLU decisions"
+            off, prev_k = off + k, k
+        differing = 0
+        for rec, mask in zip(rd.records, masks):
+            x, z, lin = rec["x"].reshape(-1, rec["x"].shape[-1]), rec["z"].reshape(mask.shape), rec["linear"]
+            s_idx, j_idx = torch.nonzero(mask != rec["decision"].reshape(mask.shape), as_tuple=True)
+            differing += len(s_idx)
+            if len(s_idx):
+                mag = (x[s_idx].abs().double() * lin.weight.detach()[j_idx].abs().double()).sum(1) + lin.bias.detach()[j_idx].abs().double()
+                assert (z[s_idx, j_idx].abs().double() <= 2.0 ** -17 * mag).all(), "a decidable ReLU decision differs"
+        assert differing <= 64
+    finally:
+        built_lib.ocppo_set_gemm_mode(default)
 
 
 def test_chunked_minibatch_is_equivalent_and_deterministic(dev):
