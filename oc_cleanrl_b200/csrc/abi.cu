@@ -479,8 +479,9 @@ static int wgrad(ocppo_handle *h, const float *dY, int out, const float *X, int 
             const int n = in - c0 < 32 ? in - c0 : 32;
             int G = 0, NS = 0;
             OCPPO_TRY(launch_skinny_wgrad(dY, out, out, X + c0, in, n, rows, h->sm_count, part, c0 == 0 ? wsum : nullptr, nullptr, &G, &NS, s));
-            OCPPO_TRY(launch_skinny_reduce(part, G, out, NS, 0, n, dW + c0, 1, in, accumulate, s));
-            if (c0 == 0) OCPPO_TRY(launch_skinny_reduce(wsum, G, out, 1, 0, 1, db, 1, 1, accumulate, s));
+            const SkinnyReduceJob jobs[2] = {{part, G, out, NS, 0, n, dW + c0, 1, in, accumulate},
+                                             {wsum, G, out, 1, 0, 1, db, 1, 1, accumulate}};
+            OCPPO_TRY(launch_skinny_reduce_multi(jobs, c0 == 0 ? 2 : 1, s));
         }
         return OCPPO_OK;
     }
@@ -1106,10 +1107,11 @@ int ocppo_minibatch_fwd_bwd(ocppo_handle *h, const float *b_obs, const int64_t *
             int G = 0, NS = 0;
             float *part = h->skinny, *ssum = h->skinny + (int64_t)h->sm_count * 4 * H * 32;
             OCPPO_TRY(launch_skinny_wgrad(a.hidden, H, H, h->gz, AP, A + 1, rows, h->sm_count, part, nullptr, ssum, &G, &NS, s));
-            OCPPO_TRY(launch_skinny_reduce(part, G, H, NS, 0, A, h->grads + h->actor.w_off, H, 1, acc, s));
-            OCPPO_TRY(launch_skinny_reduce(part, G, H, NS, A, A + 1, h->grads + h->critic.w_off, H, 1, acc, s));
-            OCPPO_TRY(launch_skinny_reduce(ssum, G, 1, NS, 0, A, h->grads + h->actor.b_off, 1, 0, acc, s));
-            OCPPO_TRY(launch_skinny_reduce(ssum, G, 1, NS, A, A + 1, h->grads + h->critic.b_off, 1, 0, acc, s));
+            const SkinnyReduceJob jobs[4] = {{part, G, H, NS, 0, A, h->grads + h->actor.w_off, H, 1, acc},
+                                             {part, G, H, NS, A, A + 1, h->grads + h->critic.w_off, H, 1, acc},
+                                             {ssum, G, 1, NS, 0, A, h->grads + h->actor.b_off, 1, 0, acc},
+                                             {ssum, G, 1, NS, A, A + 1, h->grads + h->critic.b_off, 1, 0, acc}};
+            OCPPO_TRY(launch_skinny_reduce_multi(jobs, 4, s));
         } else
         {
             SgemmArgs g{};

@@ -314,6 +314,8 @@ int launch_skinny_wgrad(const float *wide, int64_t ldw, int nw, const float *ski
                         cudaStream_t stream);
 int launch_skinny_reduce(const float *part, int G, int nw, int NS, int i0, int i1, float *out, int64_t si, int64_t sj,
                          int accumulate, cudaStream_t stream);
+struct SkinnyReduceJob { const float *part; int G, nw, NS, i0, i1; float *out; int64_t si, sj; int accumulate; };
+int launch_skinny_reduce_multi(const SkinnyReduceJob *jobs, int n, cudaStream_t stream);     // same sums, one launch
 int launch_relu_mask(const float *g, const float *act, int64_t n, float *out, int sm_count, cudaStream_t stream);
 int measure_fma_peak(double *tflops, cudaStream_t stream);
 int launch_store_words(void *dst, const void *words, int n, cudaStream_t stream);     // n <= 8 32-bit words

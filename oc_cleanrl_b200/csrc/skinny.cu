@@ -89,7 +89,44 @@ skinny_reduce_kernel(const float *__restrict__ part, int G, int nw, int NS, int 
     }
 }
 
+// up to four reductions of the kind above in ONE launch (blockIdx.y selects the job): the heads' four outputs (actor /
+// critic weights and biases) used to cost four launches per minibatch chunk
+struct SkinnyJobs { SkinnyReduceJob j[4]; int n; };
+__global__ void __launch_bounds__(256) skinny_reduce_multi_kernel(SkinnyJobs jobs) {
+    const SkinnyReduceJob &J = jobs.j[blockIdx.y];
+    const int ni = J.i1 - J.i0, lane = threadIdx.x & 31;
+    const int64_t total = (int64_t)J.nw * ni;
+    for (int64_t e = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); e < total; e += (int64_t)gridDim.x * 8) {
+        const int j = (int)(e / ni), i = J.i0 + (int)(e - (int64_t)j * ni);
+        float s = 0.f;
+        for (int g = lane; g < J.G; g += 32) s += J.part[((int64_t)g * J.nw + j) * J.NS + i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) {
+            float *o = J.out + (int64_t)(i - J.i0) * J.si + (int64_t)j * J.sj;
+            *o = J.accumulate ? *o + s : s;
+        }
+    }
+}
+
 }  // namespace
+
+int launch_skinny_reduce_multi(const SkinnyReduceJob *jobs, int n, cudaStream_t stream) {
+    OCPPO_CHECK_ARG(jobs != nullptr && n >= 1 && n <= 4, "skinny_reduce_multi: 1..4 jobs");
+    SkinnyJobs J{};
+    J.n = n;
+    int64_t most = 0;
+    for (int k = 0; k < n; ++k) {
+        J.j[k] = jobs[k];
+        const int64_t total = (int64_t)jobs[k].nw * (jobs[k].i1 - jobs[k].i0);
+        if (total > most) most = total;
+    }
+    if (most <= 0) return OCPPO_OK;
+    ProfScope ps(KC_AUX, 1, stream);
+    skinny_reduce_multi_kernel<<<dim3((unsigned)ceil_div(most, 8), (unsigned)n), 256, 0, stream>>>(J);
+    OCPPO_LAUNCH_CHECK("skinny_reduce_multi_kernel");
+    return OCPPO_OK;
+}
 
 int skinny_slabs(int64_t rows, int sm_count, int64_t *rows_per_cta) {
     int64_t G = (int64_t)sm_count * 4;

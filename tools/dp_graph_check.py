@@ -1,0 +1,72 @@
+"""Data-parallel update under CUDA graphs on real GPUs (torchrun --nproc-per-node K tools/dp_graph_check.py):
+the same three updates with (a) plain launches, (b) two graphs per minibatch around an eager NCCL all-reduce,
+(c) the all-reduce captured inside one graph per minibatch.  Weights must be bitwise equal across ranks and across the
+three modes (the kernels and the reduction are the same; only how they are launched differs)."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oc_cleanrl_b200.architectures.ppo import PPObj  # noqa: E402
+from oc_cleanrl_b200.learner import LearnerArgs, PPOLearner  # noqa: E402
+from oc_cleanrl_b200.synthetic import make_rollout, stub_envs  # noqa: E402
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", rank)))
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    F, D, A, T, N = 4, 6, 6, 32, 64
+    enc, dec = (256, 512), (256,)
+    data = {k: v.to(dev) for k, v in make_rollout(T, N, F, D, rank=rank).items()}
+    results = {}
+    for mode in ("plain", "split-graphs", "collective-in-graph"):
+        torch.manual_seed(1)
+        agent = PPObj(stub_envs(F, D, A), dev, enc, dec).to(dev)
+        torch.cuda.manual_seed(100 + rank)
+        with torch.no_grad():
+            action, logp, _, value = agent.get_action_and_value(data["obs"].reshape(T * N, F, D))
+        learner = PPOLearner(agent, LearnerArgs(num_envs=N, num_steps=T), world_size=world,
+                             np_rng=np.random.RandomState(7 + rank), use_graphs=mode != "plain",
+                             graph_collective=mode == "collective-in-graph")
+        try:
+            for it in range(3):
+                learner.anneal_lr(it + 1, 10)
+                adv, ret = learner.compute_gae(data["rewards"], value.reshape(T, N), data["dones"], data["next_obs"], data["next_done"])
+                stats = learner.update(data["obs"], action.reshape(T, N), logp.reshape(T, N), adv, ret, value.reshape(T, N))
+            flat = torch.cat([p.detach().reshape(-1) for p in agent.parameters()]).clone()
+            results[mode] = (flat, stats["loss"], learner._graph_hits)
+        except Exception as e:          # a capture that NCCL refuses must not take the other modes down
+            results[mode] = e
+        torch.cuda.synchronize()
+    ok = True
+    base = results["plain"][0]
+    for mode, r in results.items():
+        if isinstance(r, Exception):
+            if rank == 0:
+                print(f"dp_graph_check {mode}: FAILED TO RUN: {type(r).__name__}: {str(r)[:200]}", flush=True)
+            ok = ok and mode == "collective-in-graph"      # optional mode
+            continue
+        flat, loss, hits = r
+        everyone = [torch.empty_like(flat) for _ in range(world)]
+        dist.all_gather(everyone, flat)
+        same_ranks = all(torch.equal(everyone[0], e) for e in everyone[1:])
+        same_mode = torch.equal(flat, base)
+        ok = ok and same_ranks and same_mode
+        if rank == 0:
+            print(f"dp_graph_check world={world} {mode}: ranks_bitwise_equal={same_ranks} equals_plain_launches={same_mode} "
+                  f"loss={loss:.6f} graph_hits={hits}", flush=True)
+    if rank == 0:
+        print("dp_graph_check -> " + ("PASS" if ok else "FAIL"), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()
