@@ -280,6 +280,20 @@ int ocppo_clip_adam_dev(ocppo_handle *h, const float *scalars8, float *grad_norm
 int ocppo_explained_variance(ocppo_handle *h, const float *values, const float *returns, int64_t n, float *out2,
                              void *stream);
 
+/* Allocation-free variant of ocppo_explained_variance.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same kernels and the same result (out2[0] = var(returns), out2[1] = var(returns - values)), but the
+ * per-block partial sums live in a file-scope `static __device__` array inside the library (32 KB per GPU, held by
+ * every GPU that loads the library until the process exits) instead of a caller-bound workspace: the call takes no
+ * handle and needs no workspace; it calls no cudaMalloc / cudaFree / allocating routine.  values / returns / out2 are
+ * device pointers on one device (the call makes that device current for its duration).  Limits: 1 <= n <=
+ * OCPPO_EV_STATIC_MAX_N, beyond that OCPPO_EINVAL with a message naming the limit.  All calls on a device SHARE the
+ * array: it keeps the previous call's partial sums (every slot a call reads it has written first, so nothing needs
+ * clearing), and two calls that overlap on the same GPU -- different streams without an ordering between them --
+ * race.  Calls on one stream, or stream-ordered calls, are safe. */
+#define OCPPO_EV_STATIC_MAX_N (1LL << 28)
+int ocppo_explained_variance_static(const float *values, const float *returns, int64_t n, float *out2, void *stream);
+
 /* ---- host env feed (pure host code, host pointers) ---------- */
 /* Batched replacement of the per-env Python observation assembly and of VecNormalize's reward scaling:
  *  - submodules/OC_Atari/ocatari/core.py:444-448 (ns_state: chain of every slot's _nsrepr),

@@ -92,6 +92,7 @@ _SIGNATURES = {
     "ocppo_clip_adam_dev": (C.c_int, [_P, _P, _P, _P]),
     "ocppo_trunk_forward": (C.c_int, [_P, _P, _I64, _P, _P]),
     "ocppo_explained_variance": (C.c_int, [_P, _P, _P, _I64, _P, _P]),
+    "ocppo_explained_variance_static": (C.c_int, [_P, _P, _I64, _P, _P]),
     "ocppo_read_activation": (C.c_int, [_P, C.c_int32, _I64, _P, _P]),
     "ocppo_trunk_backward": (C.c_int, [_P, _P, _I64, _P, _P]),
     "ocppo_feed_create": (C.c_int, [_I32, _I32, _I32, _D, _D, _D, C.POINTER(_P)]),

@@ -1022,3 +1022,69 @@ int launch_clip_adam(ocppo_handle *h, const float *host8, const float *dev8, flo
 }
 
 }  // namespace ocppo
+
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free explained variance (ocppo_explained_variance_static, include/ocppo.h).  No counterpart in the
+// reference: added for callers that cannot call cudaMalloc (code under CUDA graph
+// capture, tight serving loops, harnesses that forbid it).  Same two kernels as ocppo_explained_variance; the per-block
+// partial sums live in the file-scope array below instead of a caller-bound workspace, so the call needs no handle, no
+// workspace and no allocation of any kind.
+//   * 32 KB per GPU (1024 blocks x 4 doubles), held by every GPU that loads the library until the process exits;
+//   * in HOST code the array's name is a host-side stand-in, not a device address: the address the kernels get comes
+//     from cudaGetSymbolAddress, once per device, with that device current;
+//   * every call on a device shares the array: a call leaves its partial sums behind, and the next call overwrites
+//     every slot it later reads (block b writes slots 4b..4b+3, the finalize kernel reads exactly the blocks launched),
+//     so nothing has to start at zero -- but two calls that OVERLAP on the same GPU (different streams) race.
+// ---------------------------------------------------------------------------------------------------------------
+#define OCPPO_EV_STATIC_BLOCKS 1024
+static __device__ __align__(256) double g_ev_static_scratch[OCPPO_EV_STATIC_BLOCKS * 4];
+
+namespace ocppo {
+
+static int explained_variance_static(const float *values, const float *returns, int64_t n, float *out2, cudaStream_t stream) {
+    OCPPO_CHECK_ARG(values != nullptr && returns != nullptr && out2 != nullptr, "explained_variance_static: null pointer");
+    OCPPO_CHECK_ARG(n >= 1, "explained_variance_static: n must be >= 1 (got %lld)", (long long)n);
+    OCPPO_CHECK_ARG(n <= (int64_t)OCPPO_EV_STATIC_MAX_N,
+                    "explained_variance_static: n = %lld exceeds the static-scratch variant's maximum of %lld elements "
+                    "(use ocppo_explained_variance with a bound workspace)", (long long)n, (long long)OCPPO_EV_STATIC_MAX_N);
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, values) != cudaSuccess || at.type != cudaMemoryTypeDevice) {
+        cudaGetLastError();
+        set_error("explained_variance_static: `values` is not device memory");
+        return OCPPO_EINVAL;
+    }
+    const int dev = at.device;
+    OCPPO_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "explained_variance_static: device ordinal %d out of range", dev);
+    int prev = -1;
+    OCPPO_CUDA(cudaGetDevice(&prev));
+    if (prev != dev) OCPPO_CUDA(cudaSetDevice(dev));
+    struct Restore { int prev, dev; ~Restore() { if (prev != dev) cudaSetDevice(prev); } } restore{prev, dev};
+    // set-up, once per device, with that device current: the array's DEVICE address and the SM count
+    static double *scratch_of[kMaxDevices] = {nullptr};
+    static int sms_of[kMaxDevices] = {0};
+    if (scratch_of[dev] == nullptr) {
+        double *ptr = nullptr;
+        OCPPO_CUDA(cudaGetSymbolAddress((void **)&ptr, g_ev_static_scratch));
+        int sms = 0;
+        OCPPO_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        sms_of[dev] = sms;
+        scratch_of[dev] = ptr;
+    }
+    double *scratch = scratch_of[dev];
+    // the grid of ocppo_explained_variance (so both entry points sum in the same order), capped by the array
+    const unsigned grid = grid_for(n, 256 * 8, sms_of[dev] * 2);
+    OCPPO_CHECK_ARG(grid <= OCPPO_EV_STATIC_BLOCKS, "explained_variance_static: %u blocks exceed the %d-block static scratch",
+                    grid, OCPPO_EV_STATIC_BLOCKS);
+    ProfScope ps(KC_AUX, 2, stream);
+    explained_var_partial_kernel<<<grid, 256, 0, stream>>>(values, returns, n, scratch);
+    OCPPO_LAUNCH_CHECK("explained_var_partial_kernel (static scratch)");
+    explained_var_finalize_kernel<<<1, 32, 0, stream>>>(scratch, (int)grid, n, out2);
+    OCPPO_LAUNCH_CHECK("explained_var_finalize_kernel (static scratch)");
+    return OCPPO_OK;
+}
+
+}  // namespace ocppo
+
+extern "C" int ocppo_explained_variance_static(const float *values, const float *returns, int64_t n, float *out2, void *stream) {
+    return ocppo::explained_variance_static(values, returns, n, out2, reinterpret_cast<cudaStream_t>(stream));
+}
