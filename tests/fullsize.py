@@ -29,6 +29,51 @@ def perturb_like_training(params, seed):
                 p.add_(0.1 * torch.randn(p.shape, generator=g))
 
 
+def permuted_twin(model, seed):
+    """The SAME function with every hidden layer's units renumbered (rows of W_l and b_l permuted, columns of W_{l+1}
+    permuted to match, frame blocks of the Flatten respected): torch evaluates it with the same kernels but sums every dot
+    product in a different order -- an independent, equally valid fp32 evaluation of the reference's operator sequence.
+    -> (twin model, function mapping the twin's per-tensor gradients back to the original numbering)."""
+    import copy
+    g = torch.Generator().manual_seed(7000 + seed)
+    twin = copy.deepcopy(model)
+    lins = [m for m in twin.network if isinstance(m, torch.nn.Linear)]
+    n_enc = len(ENC)
+    perms, col_perms = [], []
+    prev = None
+    with torch.no_grad():
+        for l, lin in enumerate(lins):
+            out_dim, in_dim = lin.weight.shape
+            if prev is None:
+                cp = torch.arange(in_dim)
+            elif l == n_enc:                       # first decoder layer: input index = frame * width + unit
+                width = prev.numel()
+                cp = torch.cat([f * width + prev for f in range(in_dim // width)])
+            else:
+                cp = prev
+            P = torch.randperm(out_dim, generator=g)
+            lin.weight.copy_(lin.weight[P][:, cp])
+            lin.bias.copy_(lin.bias[P])
+            perms.append(P); col_perms.append(cp)
+            prev = P
+        for head in (twin.actor, twin.critic):
+            head.weight.copy_(head.weight[:, prev])
+
+    def unpermute(grads):
+        out = []
+        for l in range(len(lins)):
+            gw = grads[2 * l].reshape(lins[l].weight.shape)
+            inv_r, inv_c = np.argsort(perms[l].numpy()), np.argsort(col_perms[l].numpy())
+            out.append(gw[inv_r][:, inv_c].reshape(-1))
+            out.append(grads[2 * l + 1][inv_r])
+        k = 2 * len(lins)
+        inv_c = np.argsort(prev.numpy())
+        out.append(grads[k].reshape(twin.actor.weight.shape)[:, inv_c].reshape(-1)); out.append(grads[k + 1])
+        out.append(grads[k + 2].reshape(twin.critic.weight.shape)[:, inv_c].reshape(-1)); out.append(grads[k + 3])
+        return out
+    return twin, unpermute
+
+
 def rel_max(got, want):
     d = np.abs(want).max()
     return float(np.abs(got - want).max() / (d if d > 0 else 1.0))
@@ -45,10 +90,11 @@ def rel_rows(got, want, shape):
     return float((num[ok] / den[ok]).max()) if ok.any() else 0.0
 
 
-def fullsize_case(dev, game, seed, engine, trained_like=False, with_masks=False):
+def fullsize_case(dev, game, seed, engine, trained_like=False, with_masks=False, with_twin=False):
     """-> dict(shapes, e32, e64, ref, rows32 [, e64m]): per parameter tensor, the max-norm relative error of our gradient
     against torch fp32 / fp64, torch fp32 against fp64, the per-row figure against torch fp32, and optionally against fp64
-    evaluated under the device path's own ReLU decisions."""
+    evaluated under the device path's own ReLU decisions; ``twin32``: torch fp32 on the unit-permuted twin (same function,
+    another summation order) against torch fp32 -- how far two valid fp32 evaluations of the reference are apart."""
     from oc_cleanrl_b200 import _abi
     from oc_cleanrl_b200.architectures.ppo import PPObj
     from oc_cleanrl_b200.learner import LearnerArgs, PPOLearner
@@ -93,10 +139,10 @@ def fullsize_case(dev, game, seed, engine, trained_like=False, with_masks=False)
         del agent, learner
         torch.cuda.empty_cache()
 
-        def torch_grads(dtype, m=None):
+        def torch_grads(dtype, m=None, source=None):
             o = ref_ppo.make_agent(F, D, A, ENC, DEC, seed=0, dtype=dtype).to(dev)
             with torch.no_grad():
-                for p, q in zip(o.parameters(), cpu_model.parameters()):
+                for p, q in zip(o.parameters(), (source or cpu_model).parameters()):
                     p.copy_(q.to(dev).to(dtype))
             args_t = tuple(t.to(dtype) if t.is_floating_point() else t for t in gpu)
             if m is None:
@@ -116,6 +162,10 @@ def fullsize_case(dev, game, seed, engine, trained_like=False, with_masks=False)
                    ref=[rel_max(a, b) for a, b in zip(g32, g64)],
                    rows32=[rel_rows(a, b, s) for a, b, s in zip(ours, g32, shapes)],
                    rows_ref=[rel_rows(a, b, s) for a, b, s in zip(g32, g64, shapes)])
+        if with_twin:
+            twin, unpermute = permuted_twin(cpu_model, seed)
+            g32t = unpermute(torch_grads(torch.float32, source=twin))
+            out["twin32"] = [rel_max(a, b) for a, b in zip(g32t, g32)]
         if with_masks:
             g64m = torch_grads(torch.float64, masks)
             out["e64m"] = [rel_max(a, b) for a, b in zip(ours, g64m)]
