@@ -51,10 +51,17 @@ EPOCHS, MINIBATCHES = 4, 4
 # ncu --set full captures of single launches (dram__bytes_read.sum + dram__bytes_write.sum), valid for the configuration
 # they were taken on only; `roofline.traffic` is null for any other
 NCU_TRAFFIC = {
-    # tc_gemm_kernel<FWD>, layer 3 (M=524288, N=512, K=1024), engine 8: 2.247 GB read + 1.044 GB written; algorithmic 3.22 GB
-    ("pong", 4096, 128, "tc"): {"bytes": 3291000000, "source": "profiles/r01_tc8_ncu_full.txt (tc_gemm_kernel<FWD> layer 3, one launch)"},
+    # tc_gemm_kernel<FWD>, trunk layer 3 (M=524288, N=512, K=1024) inside a full-size minibatch of the learner path, engine 8:
+    # 2.354 GB read + 1.078 GB written; algorithmic 3.22 GB (the A pair and the C pair once)
+    ("pong", 4096, 128, "tc"): {"bytes": 3432000000, "source": "profiles/r02_gemm_ncu_minibatch.txt (tc_gemm_kernel<FWD> layer 3, one launch)"},
 }
-NCU_TRAFFIC_GAE = {}      # (num_envs, num_steps) -> {"bytes", "source"}; filled from profiles/r02_gae_ncu.txt when captured
+# gae_tma_kernel, ncu --set full, cold L2 (profiles/r02_gae_ncu.txt): dram read + write per launch.  The outputs of the two
+# smaller sizes are still in the 126 MB L2 when the kernel ends, so ncu sees (almost) no DRAM write for them.
+NCU_TRAFFIC_GAE = {
+    (4096, 128): {"bytes": 6337792, "source": "profiles/r02_gae_ncu.txt (reads 6.34 MB = the three inputs; the 4.19 MB of outputs stay in L2)"},
+    (16384, 128): {"bytes": 25312512, "source": "profiles/r02_gae_ncu.txt (reads 25.31 MB; outputs stay in L2)"},
+    (65536, 128): {"bytes": 124140032, "source": "profiles/r02_gae_ncu.txt (101.20 MB read + 22.94 MB written back before the kernel ended)"},
+}
 ENGINES = {"fma": 0, "tc": 8, "tc-pair2": 6, "tc-f32": 5, "tc-bf16": 3, "tc-3xtf32": 1, "tc-fast": 4}
 ENGINE_TEXT = {
     "tc": "three FP16 products (hi.hi + hi.lo + lo.hi) on operands stored in HBM as power-of-two scaled fp16 (hi, lo) pairs, conversion-free six-stage pipeline",

@@ -178,6 +178,7 @@ struct SgemmArgs {
     const float *bnd_wl1;          //   weights) + *bnd_bmax (largest |bias|, may be null);
     const float *bnd_bmax;
     float *c_scale_src;            //   the kernel stores the bound here: the consumers' amax_a / amax_b
+    int epi2;                      // conversion-free kernel: two epilogue staging tiles per warp + five-stage ring (set by the launcher)
     int want_pre;                  // planning hint for tc_gemm_supported(): the launch will carry both operands as fp16 pairs
                                    // (that alone admits the 128-column tile for N % 256 != 0)
     int fma_bits;                  // FMA kernel, FWD: write relu_bits too (full 128-column tiles only)

@@ -69,6 +69,7 @@ constexpr int kProdQ = 1024 / kProdThreads;                 // 16-byte chunks of
 constexpr int kStageBytesA = TM * TK * 4;                   // 16 KB
 constexpr int kRingBytes = 192 * 1024;                      // 3 x 64 KB, 4 x 48 KB or 6 x 32 KB stages
 constexpr int kMaxStages = 6;
+constexpr int kEpi2Policy = 1, kEpi2MaxK = 512;            // see tc_gemm_launch (measured: profiles/r02_epi2_ab.txt)
 constexpr int kTmemCols = 512;                              // two tiles' accumulators
 // The TMEM accumulator rounds TOWARD ZERO on every accumulate (tools/tc_probe.cu Q4): each chained MMA shrinks the running
 // sum by half an ulp on average, a systematic loss that does not average out -- through five layers forward and
@@ -352,6 +353,7 @@ __device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap *tm, int c0, i
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_all0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 struct TileCoord { int m0, n0, split; int64_t kbeg, kend; int nk; };
@@ -425,7 +427,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
     // no conversion warps at all (the kernel is launched with the first ten warps only)
     const bool compact = !PRE && F16 && MODE != SGEMM_WGRAD && p.b16_hi != nullptr && !(p.dbg & 64);
     const int stage_bytes = PRE ? 32 * 1024 : (compact ? 48 * 1024 : kStageBytes);
-    const int nstages = PRE ? ((p.dbg & 128) ? 3 : 6) : (compact ? 4 : kNumStages);
+    // epi2 (conversion-free kernel): each epilogue warp owns TWO staging tiles, so a chunk's bulk store overlaps the next
+    // chunk's arithmetic instead of being waited for (ncu: the K <= 512 layers ran at 52-75 % tensor-pipe activity, their
+    // 17 k-cycle epilogue longer than the 12 k-cycle mainloop it should hide behind); the 32 KB come out of the stage ring:
+    // five 32 KB stages instead of six
+    const bool epi2 = PRE && p.epi2 != 0;
+    const int ring_bytes = epi2 ? kRingBytes - kEpiPadBytes : kRingBytes;
+    const int nstages = PRE ? ((p.dbg & 128) ? 3 : (epi2 ? 5 : 6)) : (compact ? 4 : kNumStages);
     const int kOffA16 = PRE ? 0 : (compact ? kStageBytesA : kOffA16_);
     const int kOffALo = PRE ? kStageBytesA / 2 : (compact ? kStageBytesA + kStageBytesA / 2 : kOffALo_);
     const int kOffB16 = PRE ? kStageBytesA : (compact ? 2 * kStageBytesA : kOffB16_);
@@ -438,7 +446,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
     constexpr int kSegStages = (MODE == SGEMM_WGRAD) ? 128 : (1 << 30);
     extern __shared__ __align__(1024) uint8_t smem[];       // SWIZZLE_128B tiles need 1024-byte aligned bases
     if ((smem_u32(smem) & 1023u) != 0) __trap();
-    float *epi_pad = reinterpret_cast<float *>(smem + kRingBytes);
+    float *epi_pad = reinterpret_cast<float *>(smem + ring_bytes);
     float *bias_red = reinterpret_cast<float *>(smem + kRingBytes + kEpiPadBytes);
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + kRingBytes + kEpiPadBytes + kBiasRedBytes);
     // bars[0..5] full (used in the leader CTA), [6..11] empty, [12..13] tmem_full, [14..15] tmem_empty (leader),
@@ -512,8 +520,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
         // first): it arrives by TMA in the same tile, is read to registers, and the result overwrites it.
         const int quarter = warp & 3, chalf = warp >> 2;
         constexpr int kChunks = TN / 64;                     // chunks per warp
-        uint8_t *out_tile = reinterpret_cast<uint8_t *>(epi_pad) + warp * kEpiChunkBytes;
-        const uint32_t out_s = smem_u32(out_tile), my_aux_bar = bar_aux + 8 * warp;
+        uint8_t *tile0 = reinterpret_cast<uint8_t *>(epi_pad) + warp * (epi2 ? 2 : 1) * kEpiChunkBytes;
+        const uint32_t tile0_s = smem_u32(tile0), my_aux_bar = bar_aux + 8 * warp;
+        uint32_t ec = 0;                      // chunks staged so far (epi2: staging tile = ec & 1)
+        bool prev_aux = false;
         const int swz = lane & 7;
         uint32_t aux_phase = 0;
         int ai = 0;                           // accumulator passes handled so far (tile x k-segment)
@@ -543,8 +553,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
                     for (int cc = 1; cc < kChunks; ++cc) tma_prefetch_2d(tmAux, n_loc + cc * 32, row0);
                 }
                 mbar_expect_tx(my_aux_bar, kEpiChunkBytes);
-                tma_load_2d(out_s, tmAux, n_loc, row0, my_aux_bar);
+                tma_load_2d(tile0_s, tmAux, n_loc, row0, my_aux_bar);
             }
+            // aux passes (the landing zone of the TMA load is tile 0) stay single-buffered; coming back from one, the
+            // last aux store may still be reading tile 0
+            if (epi2 && !aux && prev_aux && lane == 0) bulk_wait_read0();
+            prev_aux = aux;
             // packed ReLU decisions of this lane's row: the warp's 128 columns are 4 words = 16 bytes, fetched before
             // the accumulator is complete (DGRAD), or written chunk by chunk (FWD)
             uint4 rb = make_uint4(0u, 0u, 0u, 0u);
@@ -586,6 +600,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
                     v[j] = __float_as_uint(x);
                 }
                 // (the aux tile is read only now, when the correction registers are dead: 96 registers per thread)
+                const uint32_t bsel = (epi2 && !aux) ? (ec & 1u) : 0u;
+                ++ec;
+                uint8_t *out_tile = tile0 + bsel * kEpiChunkBytes;
+                const uint32_t out_s = tile0_s + bsel * kEpiChunkBytes;
                 float4 ax[8];
                 if (aux) {
                     mbar_wait(my_aux_bar, aux_phase);
@@ -594,7 +612,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
                     for (int c = 0; c < 8; ++c)
                         ax[c] = *reinterpret_cast<const float4 *>(out_tile + lane * 128 + ((c ^ swz) << 4));
                 } else if (lane == 0) {
-                    bulk_wait_read0();         // the previous chunk's store has read the tile
+                    if (epi2) bulk_wait_read1();   // the store issued two chunks ago has read THIS tile; the last one may still be reading the other
+                    else bulk_wait_read0();        // the previous chunk's store has read the tile
                 }
                 __syncwarp();
                 const int n = n_loc + cc * 32;
@@ -1134,6 +1153,14 @@ int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
     SgemmArgs a = a_in;
     a.dbg = dbg;
     a.trunc_scale = trunc_scale;
+    // epilogue staging policy of the conversion-free kernel: 0 = one tile per warp + six stages everywhere; 1 = two tiles +
+    // five stages for FWD / DGRAD with K <= kEpi2MaxK (the epilogue-bound layers); 2 = for every FWD / DGRAD; 3 = WGRAD too
+#ifdef OCPPO_BRINGUP
+    static const int epi2_policy = getenv("OCPPO_TC_EPI2") ? atoi(getenv("OCPPO_TC_EPI2")) : kEpi2Policy;
+#else
+    constexpr int epi2_policy = kEpi2Policy;
+#endif
+    a.epi2 = epi2_policy >= 3 || (mode != SGEMM_WGRAD && (epi2_policy == 2 || (epi2_policy == 1 && a.K <= kEpi2MaxK)));
     OCPPO_CHECK_ARG(tc_gemm_supported(mode, a), "tc_gemm: unsupported shape M=%d N=%d K=%lld", a.M, a.N, (long long)a.K);
     const int splits = mode == SGEMM_WGRAD ? a.splits : 1;
     const bool split = a.single_acc == 0;
