@@ -142,6 +142,29 @@ def test_gae_large_batch_sweep_vs_c_oracle(dev, oracle_lib, N):
     assert torch.allclose(ret - adv, g["values"], atol=1e-5)
 
 
+@pytest.mark.parametrize("N", [16384, 8192])
+def test_gae_overlapped_behind_the_bootstrap_value_kernel(dev, N):
+    """``PPOLearner.compute_gae`` launches the scan as a PROGRAMMATIC DEPENDENT of the bootstrap ``ocppo_value`` head
+    kernel (``ocppo_gae_overlapped``; grids larger than the SM count really overlap): it may start while that kernel
+    drains, but must not read ``next_value`` before it has finished.  Repeated with fresh bootstrap observations so a stale
+    ``next_value`` would show; bit-exact against the reference loop fed with the separately computed bootstrap values."""
+    from oc_cleanrl_b200.learner import LearnerArgs, PPOLearner
+    T = 128
+    agent, _ = make_pair(dev, 4, 6, 6, (256, 512), (256,))
+    learner = PPOLearner(agent, LearnerArgs(num_envs=N, num_steps=T))
+    d = make_gae_inputs(T, N, seed=5)
+    g = {k: v.to(dev) for k, v in d.items()}
+    for rep in range(3):
+        next_obs = torch.randint(0, 200, (N, 4, 6), generator=torch.Generator().manual_seed(rep)).float().to(dev)
+        with torch.no_grad():
+            nv = agent.get_value(next_obs).reshape(-1).clone()
+        torch.cuda.synchronize()
+        adv, ret = learner.compute_gae(g["rewards"], g["values"], g["dones"], next_obs, g["next_done"])
+        torch.cuda.synchronize()
+        a_ref, r_ref = ref_ppo.ref_gae(d["rewards"], d["values"], d["dones"], nv.cpu(), d["next_done"], 0.99, 0.95)
+        assert torch.equal(adv.cpu(), a_ref) and torch.equal(ret.cpu(), r_ref), rep
+
+
 # ---------------------------------------------------------- sampling -------
 @pytest.mark.parametrize("numel", [1, 6, 24576, 1_000_003, 1_300_000])
 def test_exponential_stream_equals_torch_cuda(dev, built_lib, numel):
