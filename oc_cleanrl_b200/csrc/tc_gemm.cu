@@ -167,6 +167,12 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes
     return d;
 }
 
+// the address-independent part of such a descriptor (everything but the 14-bit start address)
+__host__ __device__ constexpr uint64_t make_desc_const(uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout_type) {
+    return ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) | ((uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32) | ((uint64_t)1 << 46) |
+           ((uint64_t)layout_type << 61);
+}
+
 // kind::tf32 instruction descriptor (cute::UMMA::InstrDescriptor): F32 accumulate, TF32 A/B.
 __host__ __device__ constexpr uint32_t make_idesc(int M, int N, bool a_mn_major, bool b_mn_major) {
     return (1u << 4) | (2u << 7) | (2u << 10) | ((a_mn_major ? 1u : 0u) << 15) | ((b_mn_major ? 1u : 0u) << 16) |
@@ -195,6 +201,58 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint6
         "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
+}
+// The same MMA with the two 64-bit shared-memory descriptors handed over as (low word, high word): only the 14-bit
+// address field in the low word changes from stage to stage, so the issuer keeps 32-bit running values instead of
+// rebuilding 64-bit descriptors (the MMA issuer is ONE thread whose instruction stream paces the tensor pipe).
+__device__ __forceinline__ void umma_f16_lohi(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                              uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %6, 0;\n\t"
+        "mov.b64 da, {%1, %2};\n\t"
+        "mov.b64 db, {%3, %4};\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %5, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// Warp-convergent variants: the WHOLE warp executes the issuer loop (every value in it is warp-uniform) and one elected
+// lane issues.  Inside an `if (lane == 0)` region the compiler must assume arbitrary divergence and wraps every
+// tcgen05 instruction in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop (9 extra instructions per MMA).
+__device__ __forceinline__ void umma_f16_lohi_elect(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                                    uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t.reg .b64 da, db;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "setp.ne.b32 p, %6, 0;\n\t"
+        "mov.b64 da, {%1, %2};\n\t"
+        "mov.b64 db, {%3, %4};\n\t"
+        "@q tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %5, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair_elect(uint32_t bar) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}"
+        ::"r"(bar), "h"((uint16_t)3)
+        : "memory");
+}
+// mainloop wait of the two single-thread roles: no clock reads in the polling loop (a spin counter bounds it instead)
+__device__ __forceinline__ void mbar_wait_lean(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0, spins = 0;
+    while (true) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (done) break;
+        if (++spins > (1u << 28)) __trap();               // never hang the device on a protocol bug
+    }
 }
 // arrives (count 1) on the barrier at this smem offset in BOTH CTAs once all prior MMAs have completed
 __device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
@@ -707,7 +765,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
         }
     } else if (warp < kEpiWarps + 2) {
         // ===================== MMA issuer (warp 8 of the leader; the peer's warp 8 forwards) =====================
-        if (warp == kEpiWarps && lane == 0 && cta_rank == 0) {
+        if (warp == kEpiWarps && cta_rank == 0 && (PRE || lane == 0)) {      // PRE: the whole warp, convergent (see umma_f16_lohi_elect)
             constexpr uint32_t idesc = make_idesc(kPairM, TN, A_MN, B_MN);   // M = 256 across the pair
             // K-major: SBO = 8-row group stride (1024 B), LBO unused.  MN-major: LBO = stride between
             // 32-float MN chunks (4096 B), SBO = stride between 4-row k groups (512 B).
@@ -733,6 +791,36 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
                         mbar_wait(bar_rawfull + 8 * s, (uint32_t)fphase);    // the peer's
                     }
                     if (++stage == nstages) { stage = 0; sphase ^= 1; }
+                    if constexpr (PRE) {
+                        // conversion-free kernel: lean issue path.  Descriptor HIGH words are constants of the operand
+                        // layout; LOW words = (address >> 4) | lbo << 16 with address = ring base + s * 32 KB + tile offset.
+                        constexpr uint32_t a16_lbo = A_MN ? 4096 : 16, a16_sbo = A_MN ? 1024 : 512, a16_ty = A_MN ? 2 : 4;
+                        constexpr uint32_t b16_lbo = B_MN ? 4096 : 16, b16_sbo = B_MN ? 1024 : 512, b16_ty = B_MN ? 2 : 4;
+                        constexpr uint32_t a_step = (A_MN ? 2048 : 32) >> 4, b_step = (B_MN ? 2048 : 32) >> 4;
+                        constexpr uint32_t a_hiw = (uint32_t)(make_desc_const(a16_lbo, a16_sbo, a16_ty) >> 32);
+                        constexpr uint32_t b_hiw = (uint32_t)(make_desc_const(b16_lbo, b16_sbo, b16_ty) >> 32);
+                        constexpr uint32_t a_low = (uint32_t)make_desc_const(a16_lbo, a16_sbo, a16_ty);
+                        constexpr uint32_t b_low = (uint32_t)make_desc_const(b16_lbo, b16_sbo, b16_ty);
+                        constexpr uint32_t idescf = make_idesc_f16(kPairM, TN, A_MN, B_MN);
+                        const uint32_t sa = (smem_u32(smem) >> 4) + (uint32_t)s * (32768u >> 4);      // stage base, 16-byte units
+                        const uint32_t ah = a_low + sa, al = a_low + sa + ((kStageBytesA / 2) >> 4);
+                        const uint32_t bh = b_low + sa + (kStageBytesA >> 4), bl = b_low + sa + ((kStageBytesA + kStageBytesB / 2) >> 4);
+                        mbar_wait_lean(bar_tma + 8 * s, (uint32_t)fphase);        // own fp16 tiles (TMA)
+                        mbar_wait_lean(bar_rawfull + 8 * s, (uint32_t)fphase);    // the peer's
+                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                        const uint32_t d_corrf = split_acc ? d_tmem + TN : d_tmem;
+                        const uint32_t first = kb > kb0 ? 1u : 0u;
+                        umma_f16_lohi_elect(d_tmem, ah, a_hiw, bh, b_hiw, idescf, first);
+                        umma_f16_lohi_elect(d_tmem, ah + a_step, a_hiw, bh + b_step, b_hiw, idescf, 1u);
+                        if (!(p.dbg & 32)) {       // (bring-up timing experiment: main product only)
+                            umma_f16_lohi_elect(d_corrf, al, a_hiw, bh, b_hiw, idescf, split_acc ? first : 1u);
+                            umma_f16_lohi_elect(d_corrf, ah, a_hiw, bl, b_hiw, idescf, 1u);
+                            umma_f16_lohi_elect(d_corrf, al + a_step, a_hiw, bh + b_step, b_hiw, idescf, 1u);
+                            umma_f16_lohi_elect(d_corrf, ah + a_step, a_hiw, bl + b_step, b_hiw, idescf, 1u);
+                        }
+                        umma_commit_pair_elect(bar_empty + 8 * s);
+                        continue;
+                    }
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     uint8_t *st = smem + s * stage_bytes;
                     const uint32_t a_hi = smem_u32(st) + kOffA, a_lo = smem_u32(st) + kOffALo;
@@ -801,7 +889,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
                     }
                     umma_commit_pair(bar_empty + 8 * s);     // stage free (in both CTAs) once these MMAs have read it
                 }
-                umma_commit_pair(bar_tfull + 8 * acc);       // accumulator (k-segment) complete in both CTAs
+                if constexpr (PRE) umma_commit_pair_elect(bar_tfull + 8 * acc);
+                else umma_commit_pair(bar_tfull + 8 * acc);       // accumulator (k-segment) complete in both CTAs
               }
             }
         }
@@ -818,7 +907,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
                         // both operands as fp16 hi / lo pairs, straight into the MMA's tiles: four loads per stage
                         const uint32_t st = smem_u32(smem + s * stage_bytes), bar = bar_tma + 8 * s;
                         const int k0 = (int)(t.kbeg + (int64_t)kb * TK);
-                        mbar_wait(bar_empty + 8 * s, (uint32_t)(sphase ^ 1));
+                        mbar_wait_lean(bar_empty + 8 * s, (uint32_t)(sphase ^ 1));
                         // (bring-up timing experiments, results are garbage: 512 = no B loads, 1024 = no A loads)
                         const bool skip_b = (p.dbg & 512) != 0, skip_a = (p.dbg & 1024) != 0;
                         mbar_expect_tx(bar, (skip_a ? 0 : kStageBytesA) + (skip_b ? 0 : kStageBytesB));
