@@ -239,6 +239,9 @@ __device__ __forceinline__ void umma_commit_pair_elect(uint32_t bar) {
         ::"r"(bar), "h"((uint16_t)3)
         : "memory");
 }
+// (Measured on top of this and rejected, profiles/r02_issue_experiments.txt: the TMA issuer made warp-convergent the same
+// way, and .cta_group::2 TMA loads counting both CTAs' bytes on the leader's barrier -- one wait per stage in the MMA
+// issuer and no forwarder thread in the peer: correct, but 0 .. +5 % cycles per launch.)
 // mainloop wait of the two single-thread roles: no clock reads in the polling loop (a spin counter bounds it instead)
 __device__ __forceinline__ void mbar_wait_lean(uint32_t bar, uint32_t parity) {
     uint32_t done = 0, spins = 0;

@@ -1,6 +1,6 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_gemm.py -m gpu -q -x > gpurun_out/m_pytest_gemm.txt 2>&1; echo "gemm tests rc=$?"; tail -1 gpurun_out/m_pytest_gemm.txt
+timeout 240 python -m pytest tests/test_gpu_gemm.py -m gpu -q -x > gpurun_out/m_pytest_gemm.txt 2>&1; echo "gemm tests rc=$?"; tail -1 gpurun_out/m_pytest_gemm.txt
 timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -q -x -k "golden or full_size_minibatch_properties or off_the_256 or other_games or seeds_and_games" > gpurun_out/m_pytest_parity.txt 2>&1; echo "parity rc=$?"; tail -1 gpurun_out/m_pytest_parity.txt
 timeout 300 python bench.py --steps 10 --warmup 5 --no-cpu-baseline --no-e2e --no-configs --gae-sweep "" > gpurun_out/m_bench.json 2> gpurun_out/m_bench.err
 python - <<PY
