@@ -73,7 +73,7 @@ __global__ void __launch_bounds__(256) split_f16_multi_kernel(AbsmaxSegs segs, c
 int launch_split_f16_multi(const AbsmaxSegs &segs, const float *base, void *hi, void *lo, cudaStream_t stream) {
     if (segs.count <= 0) return OCPPO_OK;
     ProfScope ps(KC_AUX, 1, stream);
-    split_f16_multi_kernel<<<dim3(64, (unsigned)segs.count), 256, 0, stream>>>(segs, base, reinterpret_cast<uint16_t *>(hi),
+    split_f16_multi_kernel<<<dim3(296, (unsigned)segs.count), 256, 0, stream>>>(segs, base, reinterpret_cast<uint16_t *>(hi),
                                                                               reinterpret_cast<uint16_t *>(lo));
     OCPPO_LAUNCH_CHECK("split_f16_multi_kernel");
     return OCPPO_OK;
@@ -82,7 +82,7 @@ int launch_split_f16_multi(const AbsmaxSegs &segs, const float *base, void *hi, 
 int launch_absmax_multi(const AbsmaxSegs &segs, cudaStream_t stream) {
     if (segs.count <= 0) return OCPPO_OK;
     ProfScope ps(KC_AUX, 1, stream);
-    absmax_multi_kernel<<<dim3(32, (unsigned)segs.count), 256, 0, stream>>>(segs);
+    absmax_multi_kernel<<<dim3(148, (unsigned)segs.count), 256, 0, stream>>>(segs);     // (32 blocks per tensor were latency-bound: 21 us for 9 MB)
     OCPPO_LAUNCH_CHECK("absmax_multi_kernel");
     return OCPPO_OK;
 }

@@ -329,7 +329,7 @@ int launch_colsum_reduce(const float *part, int parts, int cols, float *out, int
 int launch_wnorm(const WnormSegs &segs, cudaStream_t stream) {
     if (segs.count <= 0) return OCPPO_OK;
     ProfScope ps(KC_AUX, 1, stream);
-    wnorm_kernel<<<dim3(32, (unsigned)segs.count), 256, 0, stream>>>(segs);
+    wnorm_kernel<<<dim3(128, (unsigned)segs.count), 256, 0, stream>>>(segs);     // (32 slices per matrix were latency-bound: 36 us for 9 MB)
     OCPPO_LAUNCH_CHECK("wnorm_kernel");
     return OCPPO_OK;
 }
