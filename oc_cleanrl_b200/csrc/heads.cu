@@ -5,6 +5,7 @@
 //             (ppo_atari_oc.py:566-602 forward, closed-form backward SURVEY.md A.4)
 // One warp per sample; lane k holds logit k (n_actions <= 32).
 #include "common.cuh"
+#include <stdlib.h>
 #include "philox.cuh"
 #include <math_constants.h>
 #include <string.h>
@@ -17,14 +18,17 @@ constexpr unsigned kFull = 0xffffffffu;
 constexpr int kHeadThreads = 256;
 constexpr int kWarpsPerBlock = kHeadThreads / 32;
 
+// butterfly reductions over aligned groups of G lanes (G = 32: the whole warp)
+template <int G = 32>
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
+    for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
     return v;
 }
+template <int G = 32>
 __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(kFull, v, o));
+    for (int o = G / 2; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(kFull, v, o));
     return v;
 }
 __device__ __forceinline__ double warp_sum_d(double v) {
@@ -35,16 +39,19 @@ __device__ __forceinline__ double warp_sum_d(double v) {
 
 // torch/distributions/categorical.py:78 (logits - logsumexp), logits_to_probs
 // (softmax of the normalised logits), :159-163 (entropy).
+// G < 32: one distribution per aligned group of G lanes (`lane` is then the lane's index inside its group); the terms of
+// lanes >= A are exact zeros, so the sums are bit-identical to the whole-warp form.
+template <int G = 32>
 __device__ __forceinline__ void warp_categorical(float z, int lane, int A, float &ell, float &p, float &H) {
     const bool on = lane < A;
-    const float m = warp_max(on ? z : -CUDART_INF_F);
-    const float s = warp_sum(on ? expf(z - m) : 0.f);
+    const float m = warp_max<G>(on ? z : -CUDART_INF_F);
+    const float s = warp_sum<G>(on ? expf(z - m) : 0.f);
     ell = z - (m + logf(s));
-    const float m2 = warp_max(on ? ell : -CUDART_INF_F);
+    const float m2 = warp_max<G>(on ? ell : -CUDART_INF_F);
     const float e2 = on ? expf(ell - m2) : 0.f;
-    const float s2 = warp_sum(e2);
+    const float s2 = warp_sum<G>(e2);
     p = __fdiv_rn(e2, s2);
-    H = -warp_sum(on ? fmaxf(ell, -3.402823466e+38f) * p : 0.f);
+    H = -warp_sum<G>(on ? fmaxf(ell, -3.402823466e+38f) * p : 0.f);
 }
 
 // torch multinomial single-draw path: argmax_k p_k / q_k, first index on ties.
@@ -226,16 +233,21 @@ __device__ __forceinline__ float load_sample_scalar(const LossArgs &p, int64_t i
     return 0.f;
 }
 
-__device__ __forceinline__ void ppo_sample_loss(const LossArgs &p, int64_t i, float sc, float z, float v, int lane, float inv_mb,
-                                                float mean, float stdv, float &dz, float &dv, double (&acc)[6]) {
+// G < 32: one sample per aligned group of G lanes (G >= 8 > the five scalars); `valid` = this group's sample exists
+// (a group past the end still takes part in the shuffles but stores and accumulates nothing).
+template <int G = 32>
+__device__ __forceinline__ void ppo_sample_loss(const LossArgs &p, int64_t i, float sc, float z, float v, int wlane, float inv_mb,
+                                                float mean, float stdv, float &dz, float &dv, double (&acc)[6],
+                                                bool valid = true) {
     const int A = p.A;
+    const int lane = wlane & (G - 1), base = wlane & ~(G - 1);
     float ell, pk, Hh;
-    warp_categorical(z, lane, A, ell, pk, Hh);
-    const int a = __float_as_int(__shfl_sync(kFull, sc, 0));
-    const float newlogp = __shfl_sync(kFull, ell, a & 31);
-    const float logratio = newlogp - __shfl_sync(kFull, sc, 1);
+    warp_categorical<G>(z, lane, A, ell, pk, Hh);
+    const int a = __float_as_int(__shfl_sync(kFull, sc, base));
+    const float newlogp = __shfl_sync(kFull, ell, base + (a & (G - 1)));
+    const float logratio = newlogp - __shfl_sync(kFull, sc, base + 1);
     const float ratio = expf(logratio);
-    float advn = __shfl_sync(kFull, sc, 2);
+    float advn = __shfl_sync(kFull, sc, base + 2);
     if (p.norm_adv) advn = __fdiv_rn(advn - mean, stdv + 1e-8f);
     // clipped surrogate (:581-583)
     const float l1 = -advn * ratio;
@@ -248,7 +260,7 @@ __device__ __forceinline__ void ppo_sample_loss(const LossArgs &p, int64_t i, fl
     else if (l2 > l1) g_ratio = in_range ? -advn : 0.f;
     else g_ratio = 0.5f * (-advn) + (in_range ? 0.5f * (-advn) : 0.f);
     // value loss (:585-597)
-    const float R = __shfl_sync(kFull, sc, 3), Vold = __shfl_sync(kFull, sc, 4);
+    const float R = __shfl_sync(kFull, sc, base + 3), Vold = __shfl_sync(kFull, sc, base + 4);
     const float du = v - R;
     const float u = du * du;
     float vterm = u, g_v = du;           // d (0.5*vterm) / d v
@@ -270,8 +282,8 @@ __device__ __forceinline__ void ppo_sample_loss(const LossArgs &p, int64_t i, fl
     dz = 0.f;
     if (lane < A) dz = coef_a * ((lane == a ? 1.f : 0.f) - pk) + coef_e * pk * (ell + Hh);
     dv = p.vf_coef * inv_mb * g_v;
-    if (lane < p.AP) p.gz[i * p.AP + lane] = lane < A ? dz : (lane == A ? dv : 0.f);
-    if (lane == 0) {
+    if (valid && lane < p.AP) p.gz[i * p.AP + lane] = lane < A ? dz : (lane == A ? dv : 0.f);
+    if (valid && lane == 0) {
         acc[0] += (double)pg;
         acc[1] += (double)vterm;
         acc[2] += (double)Hh;
@@ -399,6 +411,143 @@ __global__ void __launch_bounds__(kHeadThreads) loss_head_kernel(LossArgs p) {
     __shared__ double red[kWarpsPerBlock][6];
     if (lane == 0)
         for (int q = 0; q < 6; ++q) red[warp][q] = acc[q];
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        double s = 0;
+        for (int w = 0; w < kWarpsPerBlock; ++w) s += red[w][threadIdx.x];
+        p.part[(int64_t)blockIdx.x * 8 + threadIdx.x] = s;
+    }
+}
+
+// Forward half of the loss head, FOUR samples per warp pass (A + 1 <= 8 outputs, H = 128 * HV <= 512).
+// The one-sample-per-warp kernel above spends 780 warp instructions and 16 KB of shared-memory weight reads on every sample
+// (ncu: 43 % issue-active, short-scoreboard stalls, 5x the HBM time of the 2 KB row it reads).  Here each head-weight
+// float4 is read from shared memory once per four samples, the 32 (sample, output) partial sums are reduced with a
+// transposed butterfly (31 shuffles for four samples instead of 40 per sample; lane 8 s + k ends up owning output k of
+// sample s -- the same pairwise sums as the plain butterfly, so the logits are bit-identical), and the categorical /
+// PPO-loss arithmetic then runs for four samples at once in the four 8-lane groups.  The next four rows are requested as
+// soon as the dot products are done, so the reduction and loss arithmetic hide the HBM latency without a second register
+// set.  Forward only: d(hidden) is written by loss_bwd_pair_kernel.
+template <int HV>
+__global__ void __launch_bounds__(kHeadThreads, 2) loss_head_quad_kernel(LossArgs p) {
+    extern __shared__ __align__(16) float sm[];
+    const int A = p.A, H = p.H;
+    float *sW = sm, *sB = sm + (size_t)(A + 1) * H;
+    stage_head_weights(sW, sB, p.Wa, p.ba, p.Wc, p.bc, A, H);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int grp = lane >> 3, sub = lane & 7;
+    const float inv_mb = 1.0f / (float)p.mb;
+    float mean = 0.f, stdv = 1.f;
+    if (p.norm_adv) { mean = p.adv_stat[0]; stdv = p.adv_stat[1]; }
+    const float bias = sB[sub < A ? sub : A];
+    const int64_t last = p.rows - 1;
+
+    double acc[6] = {0, 0, 0, 0, 0, 0};   // lanes 0, 8, 16, 24: the sums of their group's samples
+    float l1max = 0.f;
+    const int64_t q0 = (int64_t)blockIdx.x * kWarpsPerBlock + warp, qstep = (int64_t)gridDim.x * kWarpsPerBlock;
+    const int64_t quads = (p.rows + 3) >> 2;
+    float4 hv[4][HV];
+    if (q0 < quads) {
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+            const int64_t r = q0 * 4 + s < last ? q0 * 4 + s : last;
+#pragma unroll
+            for (int g = 0; g < HV; ++g) hv[s][g] = __ldcs(reinterpret_cast<const float4 *>(p.hidden + r * H + g * 128) + lane);
+        }
+    }
+    for (int64_t q = q0; q < quads; q += qstep) {
+        const int64_t i = q * 4 + grp;                       // this group's sample
+        const bool valid = i <= last;
+        const float sc = (valid && sub < 5) ? load_sample_scalar(p, i, sub) : 0.f;
+        float part[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) part[j] = 0.f;
+#pragma unroll
+        for (int g = 0; g < HV; ++g) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const int kr = k <= A ? k : A;               // rows past A repeat row A and are ignored
+                const float4 w = *(reinterpret_cast<const float4 *>(sW + kr * H + g * 128) + lane);
+#pragma unroll
+                for (int s = 0; s < 4; ++s) {
+                    float a = part[s * 8 + k];
+                    a = fmaf(w.x, hv[s][g].x, a);
+                    a = fmaf(w.y, hv[s][g].y, a);
+                    a = fmaf(w.z, hv[s][g].z, a);
+                    a = fmaf(w.w, hv[s][g].w, a);
+                    part[s * 8 + k] = a;
+                }
+            }
+        }
+        if (q + qstep < quads) {                             // the rows of the next pass, into the registers just freed
+#pragma unroll
+            for (int s = 0; s < 4; ++s) {
+                const int64_t r = (q + qstep) * 4 + s < last ? (q + qstep) * 4 + s : last;
+#pragma unroll
+                for (int g = 0; g < HV; ++g)
+                    hv[s][g] = __ldcs(reinterpret_cast<const float4 *>(p.hidden + r * H + g * 128) + lane);
+            }
+        }
+        // transposed butterfly: after the step with offset o a lane keeps the values whose index agrees with its own
+        // lane number in bit o, having added its partner's partial sums of them
+        float v16[16], v8[8], v4[4], v2[2];
+        {
+            const bool up = (lane & 16) != 0;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const float keep = up ? part[j + 16] : part[j], send = up ? part[j] : part[j + 16];
+                v16[j] = keep + __shfl_xor_sync(kFull, send, 16);
+            }
+        }
+        {
+            const bool up = (lane & 8) != 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float keep = up ? v16[j + 8] : v16[j], send = up ? v16[j] : v16[j + 8];
+                v8[j] = keep + __shfl_xor_sync(kFull, send, 8);
+            }
+        }
+        {
+            const bool up = (lane & 4) != 0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float keep = up ? v8[j + 4] : v8[j], send = up ? v8[j] : v8[j + 4];
+                v4[j] = keep + __shfl_xor_sync(kFull, send, 4);
+            }
+        }
+        {
+            const bool up = (lane & 2) != 0;
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const float keep = up ? v4[j + 2] : v4[j], send = up ? v4[j] : v4[j + 2];
+                v2[j] = keep + __shfl_xor_sync(kFull, send, 2);
+            }
+        }
+        float tot;
+        {
+            const bool up = (lane & 1) != 0;
+            const float keep = up ? v2[1] : v2[0], send = up ? v2[0] : v2[1];
+            tot = keep + __shfl_xor_sync(kFull, send, 1);
+        }
+        tot += bias;                                         // lane 8 s + k: logit k (k < A) / value (k == A) of sample s
+        const float z = tot;
+        const float v = __shfl_sync(kFull, tot, (lane & ~7) + A);
+        float dz, dv;
+        ppo_sample_loss<8>(p, i, sc, z, v, lane, inv_mb, mean, stdv, dz, dv, acc, valid);
+        const float l1 = fabsf(dv) + warp_sum<8>(fabsf(dz));
+        if (valid) l1max = fmaxf(l1max, l1);
+    }
+    if (p.gz_l1max != nullptr) {
+        const unsigned m = __reduce_max_sync(kFull, __float_as_uint(l1max));
+        if (lane == 0 && m != 0u) atomicMax(reinterpret_cast<unsigned int *>(p.gz_l1max), m);
+    }
+    __shared__ double red[kWarpsPerBlock][6];
+#pragma unroll
+    for (int qq = 0; qq < 6; ++qq) {                         // the four group leaders, in order
+        const double a0 = __shfl_sync(kFull, acc[qq], 0), a1 = __shfl_sync(kFull, acc[qq], 8);
+        const double a2 = __shfl_sync(kFull, acc[qq], 16), a3 = __shfl_sync(kFull, acc[qq], 24);
+        if (lane == 0) red[warp][qq] = ((a0 + a1) + a2) + a3;
+    }
     __syncthreads();
     if (threadIdx.x < 6) {
         double s = 0;
@@ -902,6 +1051,15 @@ int launch_explained_var(const ocppo_handle *h, const float *y_pred, const float
     return OCPPO_OK;
 }
 
+static bool loss_head_quad_enabled() {
+#ifdef OCPPO_BRINGUP
+    static const bool on = getenv("OCPPO_LOSS_HEAD_QUAD") ? atoi(getenv("OCPPO_LOSS_HEAD_QUAD")) != 0 : true;   // bring-up A/B
+    return on;
+#else
+    return true;
+#endif
+}
+
 int launch_loss_head(const ocppo_handle *h, LossArgs a, int *blocks_used, int blocks_avail, cudaStream_t stream,
                      bool forward_only) {
     const int smem = head_smem_bytes(a.A, a.H);
@@ -911,11 +1069,14 @@ int launch_loss_head(const ocppo_handle *h, LossArgs a, int *blocks_used, int bl
     else if (aligned && a.H == 256) kern = forward_only ? loss_head_kernel<2, false> : loss_head_kernel<2, true>;
     else if (aligned && a.H == 512) kern = forward_only ? loss_head_kernel<4, false> : loss_head_kernel<4, true>;
     else if (aligned && a.H == 1024) kern = forward_only ? loss_head_kernel<8, false> : loss_head_kernel<8, true>;
+    // four samples per warp pass when the outputs fit an 8-lane group (Pong / SpaceInvaders 6 + 1, Breakout 4 + 1)
+    const bool quad = forward_only && aligned && a.A + 1 <= 8 && (a.H == 128 || a.H == 256 || a.H == 512) && loss_head_quad_enabled();
+    if (quad) kern = a.H == 128 ? loss_head_quad_kernel<1> : a.H == 256 ? loss_head_quad_kernel<2> : loss_head_quad_kernel<4>;
     OCPPO_TRY(ensure_head_smem((const void *)kern, smem));
-    int cap = h->sm_count * (forward_only ? 8 : 4);
+    int cap = h->sm_count * (quad ? 2 : forward_only ? 8 : 4);       // quad: the two resident blocks per SM, ~14 passes each
     if (cap > blocks_avail) cap = blocks_avail;
     OCPPO_CHECK_ARG(cap >= 1, "loss head: out of partial-sum slots");
-    const unsigned grid = grid_for(a.rows, kWarpsPerBlock, cap);
+    const unsigned grid = grid_for(quad ? (a.rows + 3) / 4 : a.rows, kWarpsPerBlock, cap);
     ProfScope ps(KC_HEAD, 1, stream);
     kern<<<grid, kHeadThreads, smem, stream>>>(a);
     OCPPO_LAUNCH_CHECK("loss_head_kernel");
