@@ -308,7 +308,7 @@ int launch_loss_finalize(const double *part, int n_part, int64_t mb, float ent_c
                          cudaStream_t stream);
 int launch_splitk_reduce(const float *part, int splits, int64_t stride, int64_t count, float *out, int accumulate,
                          int sm_count, cudaStream_t stream);
-int skinny_slabs(int64_t rows, int sm_count, int64_t *rows_per_cta);
+int skinny_slabs(int64_t rows, int sm_count, int64_t *rows_per_cta, int per_sm = 4);
 static inline int64_t skinny_slabs_max(int64_t rows, int sm_count) { int64_t per; return skinny_slabs(rows, sm_count, &per); }
 int launch_skinny_wgrad(const float *wide, int64_t ldw, int nw, const float *skinny, int64_t lds, int ns, int64_t rows,
                         int sm_count, float *part, float *wsum_part, float *ssum_part, int *G_out, int *NS_out,

@@ -221,6 +221,112 @@ __global__ void __launch_bounds__(kThreads, 2) sgemm_kernel(SgemmArgs p) {
     }
 }
 
+// First trunk layer with a handful of input features (Pong: K = frames' object vector of 6 floats), fp16-pair output.
+// The 128x128x8 tile kernel above pads K to 8, stages both operands through shared memory and takes 210 us for the
+// 524,288 x 256 layer of a full-size minibatch; the work is really one 537 MB write (HBM floor 85 us).  Here a thread keeps
+// its four output columns' weights and biases in registers, reads the K inputs of a row as warp-uniform loads, and
+// streams out (hi, lo) fp16 + the ReLU decision words.  Same products in the same order (k ascending from zero), so the
+// activations are bit-identical to the tile kernel's.
+// one row of four outputs per thread: products k ascending from zero, + bias, ReLU; the decision nibble ORed over the 8
+// lanes of a 32-column word; (hi, lo) fp16 pair out
+template <int KD>
+__device__ __forceinline__ void thin_fwd_row(const float (&x)[KD], const float (&w)[4][KD], const float4 &bb, float scale_c,
+                                             int lane8, bool live, uint32_t *bits, uint2 *hi, uint2 *lo, float &run_max) {
+    float v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        float a = 0.f;
+#pragma unroll
+        for (int k = 0; k < KD; ++k) a = fmaf(x[k], w[j][k], a);
+        v[j] = a;
+    }
+    v[0] = fmaxf(v[0] + bb.x, 0.f); v[1] = fmaxf(v[1] + bb.y, 0.f);
+    v[2] = fmaxf(v[2] + bb.z, 0.f); v[3] = fmaxf(v[3] + bb.w, 0.f);
+    if (bits != nullptr) {                                        // (uniform) 8 lanes x 4 columns = one 32-column word
+        uint32_t word = ((v[0] > 0.f ? 1u : 0u) | (v[1] > 0.f ? 2u : 0u) | (v[2] > 0.f ? 4u : 0u) | (v[3] > 0.f ? 8u : 0u))
+                        << (4 * lane8);
+        word |= __shfl_xor_sync(0xffffffffu, word, 1);
+        word |= __shfl_xor_sync(0xffffffffu, word, 2);
+        word |= __shfl_xor_sync(0xffffffffu, word, 4);
+        if (lane8 == 0 && live) *bits = word;
+    }
+    if (!live) return;
+    uint32_t h0, l0, h1, l1;
+    split_f16x2(v[0], v[1], scale_c, h0, l0);
+    split_f16x2(v[2], v[3], scale_c, h1, l1);
+    __stcs(hi, make_uint2(h0, h1));
+    __stcs(lo, make_uint2(l0, l1));
+    run_max = fmaxf(fmaxf(run_max, fmaxf(v[0], v[1])), fmaxf(v[2], v[3]));
+}
+
+// FAST: K == KD (even), lda even, A 8-byte aligned and the block's row slab complete -- no per-element predicates, a row
+// is read as KD / 2 warp-uniform 8-byte loads and every pointer advances by a constant.
+template <int KD, bool FAST>
+__device__ __forceinline__ void thin_fwd_rows(const SgemmArgs &p, const float (&w)[4][KD], const float4 &bb, float scale_c,
+                                              int64_t r0, int64_t r1, int rl, int rpp, int c, int lane8, float &run_max) {
+    const int wpr = p.N >> 5;
+    uint16_t *const hi16 = reinterpret_cast<uint16_t *>(p.c16_hi), *const lo16 = reinterpret_cast<uint16_t *>(p.c16_lo);
+    if (FAST) {
+        const float2 *xa = reinterpret_cast<const float2 *>(p.A + (r0 + rl) * p.lda);
+        const int64_t xrow = ((int64_t)rpp * p.lda) >> 1, crow = ((int64_t)rpp * p.ldc) >> 2, brow = (int64_t)rpp * wpr;
+        uint2 *ha = reinterpret_cast<uint2 *>(hi16 + (r0 + rl) * p.ldc + c), *la = reinterpret_cast<uint2 *>(lo16 + (r0 + rl) * p.ldc + c);
+        uint32_t *ba = p.relu_bits != nullptr ? p.relu_bits + (r0 + rl) * wpr + (c >> 5) : nullptr;
+        for (int64_t mb = r0; mb < r1; mb += 2 * rpp) {
+            float x[2][KD];
+#pragma unroll
+            for (int u = 0; u < 2; ++u)
+#pragma unroll
+                for (int k = 0; k < KD; k += 2) {
+                    const float2 t = __ldg(xa + u * xrow + (k >> 1));
+                    x[u][k] = t.x; x[u][k + 1] = t.y;
+                }
+            thin_fwd_row<KD>(x[0], w, bb, scale_c, lane8, true, ba, ha, la, run_max);
+            thin_fwd_row<KD>(x[1], w, bb, scale_c, lane8, true, ba != nullptr ? ba + brow : nullptr, ha + crow, la + crow, run_max);
+            xa += 2 * xrow; ha += 2 * crow; la += 2 * crow;
+            if (ba != nullptr) ba += 2 * brow;
+        }
+        return;
+    }
+    for (int64_t mb = r0; mb < r1; mb += 2 * rpp) {               // warp-uniform trip count (a warp sits inside one row)
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const int64_t m = mb + u * rpp + rl;
+            const bool live = m < r1;
+            float x[KD];
+#pragma unroll
+            for (int k = 0; k < KD; ++k) x[k] = (live && k < p.K) ? __ldg(p.A + m * p.lda + k) : 0.f;
+            thin_fwd_row<KD>(x, w, bb, scale_c, lane8, live, p.relu_bits != nullptr ? p.relu_bits + m * wpr + (c >> 5) : nullptr,
+                             reinterpret_cast<uint2 *>(hi16 + m * p.ldc + c), reinterpret_cast<uint2 *>(lo16 + m * p.ldc + c), run_max);
+        }
+    }
+}
+
+template <int KD>
+__global__ void __launch_bounds__(256) thin_fwd_pair_kernel(SgemmArgs p, int64_t rows_per_cta, int fast_ok) {
+    const int tid = threadIdx.x, tpr = p.N >> 2;                  // threads per row: N / 4 in {32, 64, 128, 256}
+    const int rl = tid / tpr, c = (tid - rl * tpr) * 4, rpp = 256 / tpr;
+    float w[4][KD];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int k = 0; k < KD; ++k) w[j][k] = k < p.K ? __ldg(p.B + (int64_t)(c + j) * p.ldb + k) : 0.f;
+    const float4 bb = *reinterpret_cast<const float4 *>(p.bias + c);
+    const float bound = __ldg(p.bnd_amax) * __ldg(p.bnd_wl1) + (p.bnd_bmax != nullptr ? __ldg(p.bnd_bmax) : 0.f);
+    float scale_c, inv_c;
+    f16_scale_of(bound, scale_c, inv_c);
+    if (blockIdx.x == 0 && tid == 0) *p.c_scale_src = bound;
+    float run_max = 0.f;
+    const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta;
+    const int64_t r1 = r0 + rows_per_cta < p.M ? r0 + rows_per_cta : p.M;
+    // (rows_per_cta is a multiple of the 2 * rpp rows of one pass, so a complete slab needs no row guards)
+    if (fast_ok && r0 + rows_per_cta <= p.M) thin_fwd_rows<KD, true>(p, w, bb, scale_c, r0, r1, rl, rpp, c, tid & 7, run_max);
+    else thin_fwd_rows<KD, false>(p, w, bb, scale_c, r0, r1, rl, rpp, c, tid & 7, run_max);
+    if (p.amax_out != nullptr) {
+        const unsigned mx = __reduce_max_sync(0xffffffffu, __float_as_uint(run_max));
+        if ((tid & 31) == 0 && mx != 0u) atomicMax(reinterpret_cast<unsigned int *>(p.amax_out), mx);
+    }
+}
+
 inline bool aligned16(const void *p) { return (((uintptr_t)p) & 15) == 0; }
 
 template <int MODE>
@@ -288,8 +394,36 @@ int sgemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream) {
     return fma_gemm_launch(mode, a, stream);
 }
 
+static bool thin_fwd_enabled() {
+#ifdef OCPPO_BRINGUP
+    static const bool on = getenv("OCPPO_THIN_FWD") ? atoi(getenv("OCPPO_THIN_FWD")) != 0 : true;   // bring-up A/B
+    return on;
+#else
+    return true;
+#endif
+}
+
 int fma_gemm_launch(SgemmMode mode, const SgemmArgs &a, cudaStream_t stream) {
     if (a.M <= 0 || a.N <= 0) return OCPPO_OK;
+    if (mode == SGEMM_FWD && a.c16_hi != nullptr && a.K <= 8 && (a.N == 128 || a.N == 256 || a.N == 512 || a.N == 1024) &&
+        (a.ldc & 3) == 0 && aligned16(a.bias) && (a.relu_bits == nullptr || a.fma_bits) && thin_fwd_enabled()) {
+        int dev = 0, sms = 148;
+        OCPPO_CUDA(cudaGetDevice(&dev));
+        OCPPO_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        const int rpp2 = 2 * (256 / (a.N >> 2));                  // rows one block pass covers
+        int64_t per = round_up(ceil_div((int64_t)a.M, (int64_t)sms * 8), rpp2);
+        if (per < rpp2) per = rpp2;
+        const unsigned grid = (unsigned)ceil_div((int64_t)a.M, per);
+        ProfScope ps(KC_GEMM_CUDA_CORE, 1, stream);
+        const int kd = a.K <= 2 ? 2 : a.K <= 4 ? 4 : a.K <= 6 ? 6 : 8;
+        const int fast = a.K == kd && a.lda % 2 == 0 && (((uintptr_t)a.A) & 7) == 0;
+        if (kd == 2) thin_fwd_pair_kernel<2><<<grid, 256, 0, stream>>>(a, per, fast);
+        else if (kd == 4) thin_fwd_pair_kernel<4><<<grid, 256, 0, stream>>>(a, per, fast);
+        else if (kd == 6) thin_fwd_pair_kernel<6><<<grid, 256, 0, stream>>>(a, per, fast);
+        else thin_fwd_pair_kernel<8><<<grid, 256, 0, stream>>>(a, per, fast);
+        OCPPO_LAUNCH_CHECK("thin_fwd_pair_kernel");
+        return OCPPO_OK;
+    }
     const int splits = mode == SGEMM_WGRAD ? a.splits : 1;
     OCPPO_CHECK_ARG(splits >= 1 && splits <= kSplitMax, "sgemm: bad split count %d", splits);
     dim3 grid((unsigned)ceil_div(a.N, BN), (unsigned)ceil_div(a.M, BM), (unsigned)splits);
