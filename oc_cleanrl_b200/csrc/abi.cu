@@ -302,20 +302,22 @@ static int trunk_forward(ocppo_handle *h, const float *x, int64_t B, cudaStream_
             segs.x[l] = h->params + L.w_off; segs.n[l] = (int64_t)L.out_dim * L.in_dim; segs.out[l] = h->amax + kAmaxW + l;
         }
         segs.count = h->n_layers;
-        OCPPO_TRY(launch_absmax_multi(segs, s));
-        OCPPO_TRY(launch_split_f16_multi(segs, h->params, h->w16_hi, h->w16_lo, s));
-        h->w_amax_valid = 1;
-        if (pre16) {        // the weight norms the epilogues bound their fp16-pair outputs with
+        if (pre16) {        // the weight norms the epilogues bound their fp16-pair outputs with, and max |W| in the same pass
             OCPPO_CUDA(cudaMemsetAsync(h->amax + kWRowL1, 0, (kAmaxSlots - kWRowL1) * sizeof(float), s));
             WnormSegs w{};
             for (int l = 0; l < h->n_layers; ++l) {
                 const Layer &L = h->layers[l];
                 w.w[l] = h->params + L.w_off; w.b[l] = h->params + L.b_off; w.out_dim[l] = L.out_dim; w.in_dim[l] = L.in_dim;
                 w.row_l1[l] = h->amax + kWRowL1 + l; w.col_l1[l] = h->amax + kWColL1 + l; w.b_max[l] = h->amax + kBMax + l;
+                w.w_amax[l] = h->amax + kAmaxW + l;
             }
             w.count = h->n_layers;
             OCPPO_TRY(launch_wnorm(w, s));
+        } else {
+            OCPPO_TRY(launch_absmax_multi(segs, s));
         }
+        OCPPO_TRY(launch_split_f16_multi(segs, h->params, h->w16_hi, h->w16_lo, s));
+        h->w_amax_valid = 1;
         h->w_prepared_mode = g_gemm_mode;
     } else {
         h->w_amax_valid = 0;

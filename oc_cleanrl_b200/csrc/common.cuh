@@ -230,6 +230,7 @@ int launch_split_f16_multi(const AbsmaxSegs &segs, const float *base, void *hi, 
 struct WnormSegs {
     const float *w[2 * OCPPO_MAX_LAYERS]; const float *b[2 * OCPPO_MAX_LAYERS]; int out_dim[2 * OCPPO_MAX_LAYERS], in_dim[2 * OCPPO_MAX_LAYERS];
     float *row_l1[2 * OCPPO_MAX_LAYERS], *col_l1[2 * OCPPO_MAX_LAYERS], *b_max[2 * OCPPO_MAX_LAYERS]; int count;
+    float *w_amax[2 * OCPPO_MAX_LAYERS];   // optional (null: skipped): max |W| too, saving launch_absmax_multi's pass over the weights
 };
 constexpr int kColsumBlocksMax = 1024;
 constexpr int kPadCols = 256;              // padded width of the first layer's input / weight rows in pair storage (one N tile)

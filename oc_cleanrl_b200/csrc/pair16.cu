@@ -162,35 +162,43 @@ __global__ void __launch_bounds__(256) wnorm_kernel(WnormSegs segs) {
     const float *W = segs.w[m];
     const int out = segs.out_dim[m], in = segs.in_dim[m];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    float rmax = 0.f;
+    float rmax = 0.f, amax = 0.f;
     for (int j = blockIdx.x * 8 + warp; j < out; j += gridDim.x * 8) {          // warp per row
         float s = 0.f;
-        for (int k = lane; k < in; k += 32) s += fabsf(__ldg(W + (int64_t)j * in + k));
+        for (int k = lane; k < in; k += 32) {
+            const float a = fabsf(__ldg(W + (int64_t)j * in + k));
+            s += a;
+            amax = fmaxf(amax, a);
+        }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
         rmax = fmaxf(rmax, s);
     }
-    // columns: block = 32 columns at a time, warp w adds rows w, w + 8, ..., the 8 partial sums fold in order
+    // columns: block = 32 columns at a time, warp w adds rows w, w + 8, ... (eight loads in flight: two at a time left this
+    // pass latency-bound), the 8 partial sums fold in order
     __shared__ float red[8][33];
     float cmax = 0.f;
     for (int k0 = blockIdx.x * 32; k0 < in; k0 += gridDim.x * 32) {
         const int k = k0 + lane;
-        float s0 = 0.f, s1 = 0.f;
+        float s[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         if (k < in) {
             int j = warp;
-            for (; j + 8 < out; j += 16) {
-                s0 += fabsf(__ldg(W + (int64_t)j * in + k));
-                s1 += fabsf(__ldg(W + (int64_t)(j + 8) * in + k));
+            for (; j + 56 < out; j += 64) {
+                float v[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) v[u] = fabsf(__ldg(W + (int64_t)(j + 8 * u) * in + k));
+#pragma unroll
+                for (int u = 0; u < 8; ++u) s[u] += v[u];
             }
-            if (j < out) s0 += fabsf(__ldg(W + (int64_t)j * in + k));
+            for (; j < out; j += 8) s[0] += fabsf(__ldg(W + (int64_t)j * in + k));
         }
-        red[warp][lane] = s0 + s1;
+        red[warp][lane] = ((s[0] + s[1]) + (s[2] + s[3])) + ((s[4] + s[5]) + (s[6] + s[7]));
         __syncthreads();
         if (warp == 0) {
-            float s = 0.f;
+            float t = 0.f;
 #pragma unroll
-            for (int w = 0; w < 8; ++w) s += red[w][lane];
-            cmax = fmaxf(cmax, s);
+            for (int w = 0; w < 8; ++w) t += red[w][lane];
+            cmax = fmaxf(cmax, t);
         }
         __syncthreads();
     }
@@ -202,6 +210,10 @@ __global__ void __launch_bounds__(256) wnorm_kernel(WnormSegs segs) {
     const unsigned r = __reduce_max_sync(0xffffffffu, __float_as_uint(rmax));
     const unsigned c = __reduce_max_sync(0xffffffffu, __float_as_uint(cmax));
     const unsigned b = __reduce_max_sync(0xffffffffu, __float_as_uint(bmax));
+    if (segs.w_amax[m] != nullptr) {
+        const unsigned a = __reduce_max_sync(0xffffffffu, __float_as_uint(amax));
+        if (lane == 0 && a) atomicMax(reinterpret_cast<unsigned *>(segs.w_amax[m]), a);
+    }
     if (lane == 0) {
         if (r) atomicMax(reinterpret_cast<unsigned *>(segs.row_l1[m]), r);
         if (c) atomicMax(reinterpret_cast<unsigned *>(segs.col_l1[m]), c);

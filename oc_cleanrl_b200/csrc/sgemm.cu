@@ -232,16 +232,18 @@ __global__ void __launch_bounds__(kThreads, 2) sgemm_kernel(SgemmArgs p) {
 template <int KD>
 __device__ __forceinline__ void thin_fwd_row(const float (&x)[KD], const float (&w)[4][KD], const float4 &bb, float scale_c,
                                              int lane8, bool live, uint32_t *bits, uint2 *hi, uint2 *lo, float &run_max) {
-    float v[4];
+    // packed fp32 FMAs (FFMA2: two IEEE round-to-nearest FMAs per issue slot -- this kernel is issue-bound): columns (0, 1)
+    // and (2, 3) share an instruction, same products in the same order as the scalar form
+    float2 a01 = make_float2(0.f, 0.f), a23 = make_float2(0.f, 0.f);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        float a = 0.f;
-#pragma unroll
-        for (int k = 0; k < KD; ++k) a = fmaf(x[k], w[j][k], a);
-        v[j] = a;
+    for (int k = 0; k < KD; ++k) {
+        const float2 xx = make_float2(x[k], x[k]);
+        a01 = __ffma2_rn(xx, make_float2(w[0][k], w[1][k]), a01);
+        a23 = __ffma2_rn(xx, make_float2(w[2][k], w[3][k]), a23);
     }
-    v[0] = fmaxf(v[0] + bb.x, 0.f); v[1] = fmaxf(v[1] + bb.y, 0.f);
-    v[2] = fmaxf(v[2] + bb.z, 0.f); v[3] = fmaxf(v[3] + bb.w, 0.f);
+    a01 = __fadd2_rn(a01, make_float2(bb.x, bb.y));
+    a23 = __fadd2_rn(a23, make_float2(bb.z, bb.w));
+    float v[4] = {fmaxf(a01.x, 0.f), fmaxf(a01.y, 0.f), fmaxf(a23.x, 0.f), fmaxf(a23.y, 0.f)};
     if (bits != nullptr) {                                        // (uniform) 8 lanes x 4 columns = one 32-column word
         uint32_t word = ((v[0] > 0.f ? 1u : 0u) | (v[1] > 0.f ? 2u : 0u) | (v[2] > 0.f ? 4u : 0u) | (v[3] > 0.f ? 8u : 0u))
                         << (4 * lane8);

@@ -91,24 +91,25 @@ skinny_wgrad4_kernel(const float *__restrict__ wide, int64_t ldw, int nw, const 
     const bool active = j4 < nw;
     const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta;
     const int64_t r1 = r0 + rows_per_cta < rows ? r0 + rows_per_cta : rows;
-    float acc[4][NS];
+    // accumulators as fp32 pairs: FFMA2 does two IEEE round-to-nearest FMAs per issue slot (same sums as scalar FMAs)
+    float2 acc[4][NS / 2];
 #pragma unroll
     for (int c = 0; c < 4; ++c)
 #pragma unroll
-        for (int i = 0; i < NS; ++i) acc[c][i] = 0.f;
+        for (int i = 0; i < NS / 2; ++i) acc[c][i] = make_float2(0.f, 0.f);
     float wsum[4] = {0.f, 0.f, 0.f, 0.f};
     float ssum = 0.f;
     auto row = [&](const float4 &w, int r) {
         const float4 s0 = *reinterpret_cast<const float4 *>(&sk[r][0]);
         const float4 s1 = *reinterpret_cast<const float4 *>(&sk[r][4]);
+        const float2 p0 = make_float2(s0.x, s0.y), p1 = make_float2(s0.z, s0.w), p2 = make_float2(s1.x, s1.y), p3 = make_float2(s1.z, s1.w);
         const float wv[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
             wsum[c] += wv[c];
-            acc[c][0] = fmaf(wv[c], s0.x, acc[c][0]); acc[c][1] = fmaf(wv[c], s0.y, acc[c][1]);
-            acc[c][2] = fmaf(wv[c], s0.z, acc[c][2]); acc[c][3] = fmaf(wv[c], s0.w, acc[c][3]);
-            acc[c][4] = fmaf(wv[c], s1.x, acc[c][4]); acc[c][5] = fmaf(wv[c], s1.y, acc[c][5]);
-            acc[c][6] = fmaf(wv[c], s1.z, acc[c][6]); acc[c][7] = fmaf(wv[c], s1.w, acc[c][7]);
+            const float2 ww = make_float2(wv[c], wv[c]);
+            acc[c][0] = __ffma2_rn(ww, p0, acc[c][0]); acc[c][1] = __ffma2_rn(ww, p1, acc[c][1]);
+            acc[c][2] = __ffma2_rn(ww, p2, acc[c][2]); acc[c][3] = __ffma2_rn(ww, p3, acc[c][3]);
         }
     };
     for (int64_t rc = r0; rc < r1; rc += kSkRows) {
@@ -147,8 +148,8 @@ skinny_wgrad4_kernel(const float *__restrict__ wide, int64_t ldw, int nw, const 
         float *f = fold[tid];
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
-            *reinterpret_cast<float4 *>(f + c * NS) = make_float4(acc[c][0], acc[c][1], acc[c][2], acc[c][3]);
-            *reinterpret_cast<float4 *>(f + c * NS + 4) = make_float4(acc[c][4], acc[c][5], acc[c][6], acc[c][7]);
+            *reinterpret_cast<float4 *>(f + c * NS) = make_float4(acc[c][0].x, acc[c][0].y, acc[c][1].x, acc[c][1].y);
+            *reinterpret_cast<float4 *>(f + c * NS + 4) = make_float4(acc[c][2].x, acc[c][2].y, acc[c][3].x, acc[c][3].y);
         }
         *reinterpret_cast<float4 *>(f + 4 * NS) = make_float4(wsum[0], wsum[1], wsum[2], wsum[3]);
     }
@@ -159,8 +160,8 @@ skinny_wgrad4_kernel(const float *__restrict__ wide, int64_t ldw, int nw, const 
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 const float4 a0 = *reinterpret_cast<const float4 *>(f + c * NS), a1 = *reinterpret_cast<const float4 *>(f + c * NS + 4);
-                acc[c][0] += a0.x; acc[c][1] += a0.y; acc[c][2] += a0.z; acc[c][3] += a0.w;
-                acc[c][4] += a1.x; acc[c][5] += a1.y; acc[c][6] += a1.z; acc[c][7] += a1.w;
+                acc[c][0].x += a0.x; acc[c][0].y += a0.y; acc[c][1].x += a0.z; acc[c][1].y += a0.w;
+                acc[c][2].x += a1.x; acc[c][2].y += a1.y; acc[c][3].x += a1.z; acc[c][3].y += a1.w;
             }
             const float4 ws = *reinterpret_cast<const float4 *>(f + 4 * NS);
             wsum[0] += ws.x; wsum[1] += ws.y; wsum[2] += ws.z; wsum[3] += ws.w;
@@ -168,8 +169,8 @@ skinny_wgrad4_kernel(const float *__restrict__ wide, int64_t ldw, int nw, const 
         float *dst = part + ((int64_t)blockIdx.x * nw + j4) * NS;
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
-            *reinterpret_cast<float4 *>(dst + c * NS) = make_float4(acc[c][0], acc[c][1], acc[c][2], acc[c][3]);
-            *reinterpret_cast<float4 *>(dst + c * NS + 4) = make_float4(acc[c][4], acc[c][5], acc[c][6], acc[c][7]);
+            *reinterpret_cast<float4 *>(dst + c * NS) = make_float4(acc[c][0].x, acc[c][0].y, acc[c][1].x, acc[c][1].y);
+            *reinterpret_cast<float4 *>(dst + c * NS + 4) = make_float4(acc[c][2].x, acc[c][2].y, acc[c][3].x, acc[c][3].y);
         }
         if (wsum_part != nullptr)
             *reinterpret_cast<float4 *>(wsum_part + (int64_t)blockIdx.x * nw + j4) = make_float4(wsum[0], wsum[1], wsum[2], wsum[3]);
