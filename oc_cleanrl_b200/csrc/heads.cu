@@ -665,6 +665,100 @@ __global__ void __launch_bounds__(kHeadThreads) loss_bwd_pair_kernel(LossBwdPair
     }
 }
 
+// The same pass for H = 512 with the head weights in REGISTERS: a lane always writes the same 16 columns, so its NR x 16
+// weights (NR = A + 1 rows, critic last) are loaded once per block instead of 28 shared-memory float4 reads per sample
+// (ncu on the kernel above: 61 % issue-active, short-scoreboard stalls on those reads), and the rank-1 updates run as packed
+// FFMA2.  One block per SM (the weights alone take 16 NR registers); same products, same order, so d(hidden), its
+// bound and its column-sum partial layout [blocks][H] are what the kernel above writes.
+template <int NR>
+__global__ void __launch_bounds__(kHeadThreads, 1) loss_bwd_pair_reg_kernel(LossBwdPairArgs p) {
+    extern __shared__ __align__(16) float sm[];                // [kWarpsPerBlock][H / 4] float4 column-sum fold
+    constexpr int H = 512, NV = 4;
+    const int A = NR - 1;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float2 w2[NR][2 * NV];                                     // row k, columns g * 128 + 4 lane .. + 3 as two pairs per g
+    float wmax = 0.f;
+#pragma unroll
+    for (int k = 0; k < NR; ++k) {
+        const float *row = k < A ? p.Wa + (size_t)k * H : p.Wc;
+#pragma unroll
+        for (int g = 0; g < NV; ++g) {
+            const float4 w = __ldg(reinterpret_cast<const float4 *>(row + g * 128) + lane);
+            w2[k][2 * g] = make_float2(w.x, w.y);
+            w2[k][2 * g + 1] = make_float2(w.z, w.w);
+            wmax = fmaxf(fmaxf(wmax, fmaxf(fabsf(w.x), fabsf(w.y))), fmaxf(fabsf(w.z), fabsf(w.w)));
+        }
+    }
+    wmax = __uint_as_float(__reduce_max_sync(kFull, __float_as_uint(wmax)));      // a warp covers all NR x 512 weights
+    const float bound = __ldg(p.gz_l1max) * wmax;
+    float scale, inv;
+    f16_scale_of(bound, scale, inv);
+    if (blockIdx.x == 0 && threadIdx.x == 0) *p.bound = bound;
+    constexpr int wpr = H >> 5;                                // ReLU decision words per sample
+    float4 csum[NV];
+#pragma unroll
+    for (int g = 0; g < NV; ++g) csum[g] = make_float4(0.f, 0.f, 0.f, 0.f);
+    float dmax = 0.f;
+    const int64_t i0 = (int64_t)blockIdx.x * kWarpsPerBlock + warp, istep = (int64_t)gridDim.x * kWarpsPerBlock;
+    float gz_next = 0.f;
+    uint32_t bits_next = 0u;
+    if (i0 < p.rows) {
+        if (lane < p.AP) gz_next = __ldg(p.gz + i0 * p.AP + lane);
+        if (lane < wpr) bits_next = __ldg(p.relu_bits + i0 * wpr + lane);
+    }
+    for (int64_t i = i0; i < p.rows; i += istep) {
+        const float gzv = gz_next;
+        const uint32_t bitsv = bits_next;
+        if (i + istep < p.rows) {
+            if (lane < p.AP) gz_next = __ldg(p.gz + (i + istep) * p.AP + lane);
+            if (lane < wpr) bits_next = __ldg(p.relu_bits + (i + istep) * wpr + lane);
+        }
+        const float dv = __shfl_sync(kFull, gzv, A);
+        const float2 dv2 = make_float2(dv, dv);
+        float2 s2[2 * NV];
+#pragma unroll
+        for (int j = 0; j < 2 * NV; ++j) s2[j] = __fmul2_rn(dv2, w2[NR - 1][j]);
+#pragma unroll
+        for (int k = 0; k < NR - 1; ++k) {
+            const float dzk = __shfl_sync(kFull, gzv, k);
+            const float2 dz2 = make_float2(dzk, dzk);
+#pragma unroll
+            for (int j = 0; j < 2 * NV; ++j) s2[j] = __ffma2_rn(dz2, w2[k][j], s2[j]);
+        }
+#pragma unroll
+        for (int g = 0; g < NV; ++g) {
+            // columns g * 128 + 4 * lane .. + 3 sit in word g * 4 + lane / 8, bits 4 * (lane % 8) ..
+            const uint32_t nib = (__shfl_sync(kFull, bitsv, g * 4 + (lane >> 3)) >> ((lane & 7) * 4)) & 0xFu;
+            const float4 o = make_float4((nib & 1u) ? s2[2 * g].x : 0.f, (nib & 2u) ? s2[2 * g].y : 0.f,
+                                         (nib & 4u) ? s2[2 * g + 1].x : 0.f, (nib & 8u) ? s2[2 * g + 1].y : 0.f);
+            uint32_t h0, l0, h1, l1;
+            split_f16x2(o.x, o.y, scale, h0, l0);
+            split_f16x2(o.z, o.w, scale, h1, l1);
+            const int64_t e = (i * H + g * 128) / 4 + lane;    // uint2 index: 4 fp16 per lane
+            __stcs(reinterpret_cast<uint2 *>(p.dh_hi) + e, make_uint2(h0, h1));
+            __stcs(reinterpret_cast<uint2 *>(p.dh_lo) + e, make_uint2(l0, l1));
+            csum[g].x += o.x; csum[g].y += o.y; csum[g].z += o.z; csum[g].w += o.w;
+            dmax = fmaxf(fmaxf(dmax, fmaxf(fabsf(o.x), fabsf(o.y))), fmaxf(fabsf(o.z), fabsf(o.w)));
+        }
+    }
+    if (p.dh_amax != nullptr) {
+        const unsigned m = __reduce_max_sync(kFull, __float_as_uint(dmax));
+        if (lane == 0 && m != 0u) atomicMax(reinterpret_cast<unsigned int *>(p.dh_amax), m);
+    }
+    float4 *red = reinterpret_cast<float4 *>(sm);              // [kWarpsPerBlock][H / 4]
+#pragma unroll
+    for (int g = 0; g < NV; ++g) red[warp * (H >> 2) + g * 32 + lane] = csum[g];
+    __syncthreads();
+    for (int c = threadIdx.x; c < (H >> 2); c += blockDim.x) {
+        float4 t = red[c];
+        for (int w = 1; w < kWarpsPerBlock; ++w) {
+            const float4 v = red[w * (H >> 2) + c];
+            t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w;
+        }
+        reinterpret_cast<float4 *>(p.colsum_part + (int64_t)blockIdx.x * H)[c] = t;
+    }
+}
+
 // Single block: ordered sum of the block partials -> the seven logged scalars.
 __global__ void loss_finalize_kernel(const double *__restrict__ part, int n_part, int64_t mb, float ent_coef,
                                      float vf_coef, float *__restrict__ stats) {
@@ -1084,6 +1178,15 @@ int launch_loss_head(const ocppo_handle *h, LossArgs a, int *blocks_used, int bl
     return OCPPO_OK;
 }
 
+static bool loss_bwd_reg_enabled() {
+#ifdef OCPPO_BRINGUP
+    static const bool on = getenv("OCPPO_LOSS_BWD_REG") ? atoi(getenv("OCPPO_LOSS_BWD_REG")) != 0 : true;   // bring-up A/B
+    return on;
+#else
+    return true;
+#endif
+}
+
 bool loss_head_pair_supported(int H, int A) {
     return (H == 128 || H == 256 || H == 512 || H == 1024) && A >= 1 && A + 1 <= 32;
 }
@@ -1096,8 +1199,11 @@ int launch_loss_head_bwd_pair(const ocppo_handle *h, LossBwdPairArgs a, int *col
     if (a.H == 256) kern = loss_bwd_pair_kernel<2>;
     else if (a.H == 512) kern = loss_bwd_pair_kernel<4>;
     else if (a.H == 1024) kern = loss_bwd_pair_kernel<8>;
+    // H = 512 with the usual action counts and the ReLU decision words at hand: head weights in registers, one block per SM
+    const bool reg = a.H == 512 && a.relu_bits != nullptr && (a.A + 1 == 5 || a.A + 1 == 7) && loss_bwd_reg_enabled();
+    if (reg) kern = a.A + 1 == 5 ? loss_bwd_pair_reg_kernel<5> : loss_bwd_pair_reg_kernel<7>;
     OCPPO_TRY(ensure_head_smem((const void *)kern, smem));
-    int cap = h->sm_count * 4;
+    int cap = h->sm_count * (reg ? 1 : 4);
     if (cap > kColsumBlocksMax) cap = kColsumBlocksMax;
     const unsigned grid = grid_for(a.rows, kWarpsPerBlock, cap);
     ProfScope ps(KC_HEAD, 1, stream);
