@@ -700,18 +700,25 @@ __global__ void __launch_bounds__(kHeadThreads, 1) loss_bwd_pair_reg_kernel(Loss
     for (int g = 0; g < NV; ++g) csum[g] = make_float4(0.f, 0.f, 0.f, 0.f);
     float dmax = 0.f;
     const int64_t i0 = (int64_t)blockIdx.x * kWarpsPerBlock + warp, istep = (int64_t)gridDim.x * kWarpsPerBlock;
-    float gz_next = 0.f;
-    uint32_t bits_next = 0u;
+    // the sample's 48 input bytes are requested two samples ahead (one ahead left the eight warps of the block waiting:
+    // ncu long-scoreboard 2.6 per issue at 40 % issue-active)
+    float gz_n1 = 0.f, gz_n2 = 0.f;
+    uint32_t bits_n1 = 0u, bits_n2 = 0u;
     if (i0 < p.rows) {
-        if (lane < p.AP) gz_next = __ldg(p.gz + i0 * p.AP + lane);
-        if (lane < wpr) bits_next = __ldg(p.relu_bits + i0 * wpr + lane);
+        if (lane < p.AP) gz_n1 = __ldg(p.gz + i0 * p.AP + lane);
+        if (lane < wpr) bits_n1 = __ldg(p.relu_bits + i0 * wpr + lane);
+    }
+    if (i0 + istep < p.rows) {
+        if (lane < p.AP) gz_n2 = __ldg(p.gz + (i0 + istep) * p.AP + lane);
+        if (lane < wpr) bits_n2 = __ldg(p.relu_bits + (i0 + istep) * wpr + lane);
     }
     for (int64_t i = i0; i < p.rows; i += istep) {
-        const float gzv = gz_next;
-        const uint32_t bitsv = bits_next;
-        if (i + istep < p.rows) {
-            if (lane < p.AP) gz_next = __ldg(p.gz + (i + istep) * p.AP + lane);
-            if (lane < wpr) bits_next = __ldg(p.relu_bits + (i + istep) * wpr + lane);
+        const float gzv = gz_n1;
+        const uint32_t bitsv = bits_n1;
+        gz_n1 = gz_n2; bits_n1 = bits_n2;
+        if (i + 2 * istep < p.rows) {
+            if (lane < p.AP) gz_n2 = __ldg(p.gz + (i + 2 * istep) * p.AP + lane);
+            if (lane < wpr) bits_n2 = __ldg(p.relu_bits + (i + 2 * istep) * wpr + lane);
         }
         const float dv = __shfl_sync(kFull, gzv, A);
         const float2 dv2 = make_float2(dv, dv);

@@ -273,18 +273,30 @@ __device__ __forceinline__ void thin_fwd_rows(const SgemmArgs &p, const float (&
         const int64_t xrow = ((int64_t)rpp * p.lda) >> 1, crow = ((int64_t)rpp * p.ldc) >> 2, brow = (int64_t)rpp * wpr;
         uint2 *ha = reinterpret_cast<uint2 *>(hi16 + (r0 + rl) * p.ldc + c), *la = reinterpret_cast<uint2 *>(lo16 + (r0 + rl) * p.ldc + c);
         uint32_t *ba = p.relu_bits != nullptr ? p.relu_bits + (r0 + rl) * wpr + (c >> 5) : nullptr;
+        // the two rows of the next pass are requested before this pass's arithmetic (ncu: long-scoreboard 5.7 per issue
+        // without -- the loads are warp-uniform 24-byte rows, nothing but latency)
+        float xn[2][KD];
+        auto load_rows = [&](const float2 *src) {
+#pragma unroll
+            for (int u = 0; u < 2; ++u)
+#pragma unroll
+                for (int k = 0; k < KD; k += 2) {
+                    const float2 t = __ldg(src + u * xrow + (k >> 1));
+                    xn[u][k] = t.x; xn[u][k + 1] = t.y;
+                }
+        };
+        if (r0 < r1) load_rows(xa);
         for (int64_t mb = r0; mb < r1; mb += 2 * rpp) {
             float x[2][KD];
 #pragma unroll
             for (int u = 0; u < 2; ++u)
 #pragma unroll
-                for (int k = 0; k < KD; k += 2) {
-                    const float2 t = __ldg(xa + u * xrow + (k >> 1));
-                    x[u][k] = t.x; x[u][k + 1] = t.y;
-                }
+                for (int k = 0; k < KD; ++k) x[u][k] = xn[u][k];
+            xa += 2 * xrow;
+            if (mb + 2 * rpp < r1) load_rows(xa);
             thin_fwd_row<KD>(x[0], w, bb, scale_c, lane8, true, ba, ha, la, run_max);
             thin_fwd_row<KD>(x[1], w, bb, scale_c, lane8, true, ba != nullptr ? ba + brow : nullptr, ha + crow, la + crow, run_max);
-            xa += 2 * xrow; ha += 2 * crow; la += 2 * crow;
+            ha += 2 * crow; la += 2 * crow;
             if (ba != nullptr) ba += 2 * brow;
         }
         return;

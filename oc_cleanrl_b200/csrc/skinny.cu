@@ -14,6 +14,7 @@ namespace {
 
 constexpr int kSkThreads = 256;
 constexpr int kSkRows = 128;           // skinny rows staged per iteration
+constexpr int kSk4DepthDefault = 4;
 constexpr int kSkBatch = 16;           // Wide rows a thread has in flight at once (8 left the kernel latency-bound at ~3 TB/s)
 
 template <int NS>
@@ -76,9 +77,9 @@ skinny_wgrad_kernel(const float *__restrict__ wide, int64_t ldw, int nw, const f
 // every RG-th row of the slab; the groups' sums fold through shared memory in fixed order at the end.  The one-column kernel
 // above issues 29 instructions per 4-byte element (ncu: issue-bound at 3 TB/s, 64 % issue-active); here a row costs one
 // LDG.128, two broadcast LDS.128 and 36 FP instructions for four elements.
-constexpr int kSk4Depth = 4;           // rows (16-byte loads) a thread has in flight
-template <int NS>
-__global__ void __launch_bounds__(kSkThreads, 3)
+// kSk4Depth: rows (16-byte loads) a thread has in flight; 4 with three resident blocks per SM, 8 with two
+template <int NS, int kSk4Depth>
+__global__ void __launch_bounds__(kSkThreads, kSk4Depth == 4 ? 3 : 2)
 skinny_wgrad4_kernel(const float *__restrict__ wide, int64_t ldw, int nw, const float *__restrict__ skinny,
                      int64_t lds, int ns, int64_t rows, int64_t rows_per_cta, int tpr_log2, float *__restrict__ part,
                      float *__restrict__ wsum_part, float *__restrict__ ssum_part) {
@@ -257,6 +258,15 @@ static bool skinny_vec4_enabled() {
 #endif
 }
 
+static int skinny_vec4_depth() {
+#ifdef OCPPO_BRINGUP
+    static const int d = getenv("OCPPO_SK4_DEPTH") ? atoi(getenv("OCPPO_SK4_DEPTH")) : kSk4DepthDefault;   // bring-up A/B
+    return d;
+#else
+    return kSk4DepthDefault;
+#endif
+}
+
 // part: [G][nw][NS] floats, wsum_part: [G][nw] or null, ssum_part: [G][NS] or null.  NS = 8 if ns <= 8 else 32.
 int launch_skinny_wgrad(const float *wide, int64_t ldw, int nw, const float *skinny, int64_t lds, int ns, int64_t rows,
                         int sm_count, float *part, float *wsum_part, float *ssum_part, int *G_out, int *NS_out,
@@ -265,14 +275,18 @@ int launch_skinny_wgrad(const float *wide, int64_t ldw, int nw, const float *ski
     int64_t per = 0;
     const int NS = ns <= 8 ? 8 : 32;
     const bool vec4 = NS == 8 && nw % 4 == 0 && ldw % 4 == 0 && (((uintptr_t)wide) & 15) == 0 && skinny_vec4_enabled();
-    const int G = skinny_slabs(rows, sm_count, &per, vec4 ? 3 : 4);
+    const int G = skinny_slabs(rows, sm_count, &per, vec4 ? (skinny_vec4_depth() == 8 ? 2 : 3) : 4);
     ProfScope ps(KC_GEMM_CUDA_CORE, 1, stream);
     if (vec4) {
         int tpr_log2 = 5;                                  // threads per row: the power of two covering nw / 4, 32 .. 256
         while ((1 << tpr_log2) < nw / 4 && tpr_log2 < 8) ++tpr_log2;
         dim3 grid4((unsigned)G, (unsigned)ceil_div(nw / 4, 1 << tpr_log2));
-        skinny_wgrad4_kernel<8><<<grid4, kSkThreads, 0, stream>>>(wide, ldw, nw, skinny, lds, ns, rows, per, tpr_log2, part,
-                                                                 wsum_part, ssum_part);
+        if (skinny_vec4_depth() == 8)
+            skinny_wgrad4_kernel<8, 8><<<grid4, kSkThreads, 0, stream>>>(wide, ldw, nw, skinny, lds, ns, rows, per, tpr_log2, part,
+                                                                        wsum_part, ssum_part);
+        else
+            skinny_wgrad4_kernel<8, 4><<<grid4, kSkThreads, 0, stream>>>(wide, ldw, nw, skinny, lds, ns, rows, per, tpr_log2, part,
+                                                                        wsum_part, ssum_part);
         OCPPO_LAUNCH_CHECK("skinny_wgrad4_kernel");
         *G_out = G;
         *NS_out = NS;
