@@ -38,8 +38,8 @@ def make_rollout(num_steps, num_envs, frames=4, obs_dim=6, seed=1234, rank=0, sp
     hi[0::2] = 159.0
     hi[1::2] = 209.0
     state = torch.floor(torch.rand((N, D), generator=g) * (hi + 1.0))
-    visible = (torch.rand((N, D // 2 if D >= 2 else 1), generator=g) >= 0.10).float()
-    visible = visible.repeat_interleave(2, dim=1)[:, :D] if D >= 2 else visible[:, :D]
+    visible = (torch.rand((N, (D + 1) // 2), generator=g) >= 0.10).float()      # (an odd width ends with half an object slot)
+    visible = visible.repeat_interleave(2, dim=1)[:, :D]
     total = T + F                                 # states s_0 .. s_{T+F-1}
     states = torch.empty((total, N, D))
     for i in range(total):

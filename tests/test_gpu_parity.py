@@ -466,25 +466,19 @@ def test_single_update_step_vs_live_oracle_other_games(dev, game, D, A, gemm_eng
     assert rel_err(agent_flat(agent), ref_ppo.flat_params(oracle).numpy()) < REL_TOL
 
 
-@pytest.mark.parametrize("enc,dec,tc_layers,tc_dgrads", [((128, 384), (128,), 2, 2), ((128, 64), (32,), 0, 2),
-                                                         ((384, 128, 256), (640,), 3, 3)])
-@pytest.mark.parametrize("engine", [6, 8])
-def test_minibatch_gradients_with_widths_off_the_256_grid(dev, built_lib, enc, dec, tc_layers, tc_dgrads, engine):
-    """Trunk widths that are multiples of 128 but not of 256 take the conversion-free kernel's 128-column tile (forward,
-    dgrad and wgrad on the tensor cores); the reference class's own constructor default ``(128, 64), (32,)``
-    (architectures/ppo.py:61) has 64- and 32-wide layers, which stay on the CUDA-core kernels.  Rollout forward, loss
-    statistics and every gradient tensor of a 2,048-sample minibatch against the CPU oracle -- evaluated, as in
-    test_full_size_minibatch_properties, under the ReLU decisions the device path took, each differing decision proven
-    undecidable in fp32 -- and the launch counters say which kernels ran."""
+def _minibatch_vs_oracle_under_device_decisions(dev, built_lib, F, D, A, enc, dec, engine, counts=None, seed=78):
+    """Rollout forward, loss statistics and every gradient tensor of a 2,048-sample minibatch against the CPU oracle --
+    evaluated, as in test_full_size_minibatch_properties, under the ReLU decisions the device path took, each differing
+    decision proven undecidable in fp32.  `counts` = expected tcgen05 (fwd, wgrad, dgrad) launches of the minibatch."""
     from oc_cleanrl_b200 import _abi
     from oc_cleanrl_b200.learner import LearnerArgs, PPOLearner
     default = built_lib.ocppo_get_gemm_mode()
     assert built_lib.ocppo_set_gemm_mode(engine) == 0
     try:
-        F, D, A, T, N = 4, 6, 6, 128, 16
+        T, N = 128, 16
         n = T * N
         agent, oracle = make_pair(dev, F, D, A, enc, dec)
-        data = make_rollout(T, N, F, D, seed=78)
+        data = make_rollout(T, N, F, D, seed=seed)
         obs = data["obs"].to(dev)
         torch.cuda.manual_seed(3)
         with torch.no_grad():
@@ -506,10 +500,12 @@ def test_minibatch_gradients_with_widths_off_the_256_grid(dev, built_lib, enc, d
                                                      C.byref(learner._hp), _abi.ptr(stats), agent._stream()))
         torch.cuda.synchronize()
         c1, _ = _abi.launch_counts()
-        assert c1["gemm_fwd"] - c0["gemm_fwd"] == tc_layers           # tcgen05 launches of this minibatch
-        assert c1["gemm_wgrad"] - c0["gemm_wgrad"] == tc_layers
-        # (a dgrad's N is the layer's INPUT width: 128 -> 64 and 256 -> 32 still have 128- / 256-wide input gradients)
-        assert c1["gemm_dgrad"] - c0["gemm_dgrad"] == tc_dgrads
+        if counts is not None:
+            tc_layers, tc_dgrads = counts
+            assert c1["gemm_fwd"] - c0["gemm_fwd"] == tc_layers           # tcgen05 launches of this minibatch
+            assert c1["gemm_wgrad"] - c0["gemm_wgrad"] == tc_layers
+            # (a dgrad's N is the layer's INPUT width: 128 -> 64 and 256 -> 32 still have 128- / 256-wide input gradients)
+            assert c1["gemm_dgrad"] - c0["gemm_dgrad"] == tc_dgrads
         grad = agent_flat_grad(agent)
         masks = []
         for l, width in enumerate(enc + dec):
@@ -541,6 +537,35 @@ def test_minibatch_gradients_with_widths_off_the_256_grid(dev, built_lib, enc, d
         assert differing <= 64
     finally:
         built_lib.ocppo_set_gemm_mode(default)
+
+
+@pytest.mark.parametrize("enc,dec,tc_layers,tc_dgrads", [((128, 384), (128,), 2, 2), ((128, 64), (32,), 0, 2),
+                                                         ((384, 128, 256), (640,), 3, 3)])
+@pytest.mark.parametrize("engine", [6, 8])
+def test_minibatch_gradients_with_widths_off_the_256_grid(dev, built_lib, enc, dec, tc_layers, tc_dgrads, engine):
+    """Trunk widths that are multiples of 128 but not of 256 take the conversion-free kernel's 128-column tile (forward,
+    dgrad and wgrad on the tensor cores); the reference class's own constructor default ``(128, 64), (32,)``
+    (architectures/ppo.py:61) has 64- and 32-wide layers, which stay on the CUDA-core kernels.  The launch counters say
+    which kernels ran."""
+    _minibatch_vs_oracle_under_device_decisions(dev, built_lib, 4, 6, 6, enc, dec, engine, counts=(tc_layers, tc_dgrads))
+
+
+@pytest.mark.parametrize("D,A,enc,dec", [
+    (5, 6, (256, 256), (512,)),       # odd object-vector width: the guarded path of thin_fwd_pair_kernel<6>
+    (8, 3, (128, 256), (256,)),       # K = 8, 128-wide first layer; H = 256: loss_head_quad_kernel<2>, AP = 4
+    (3, 7, (512, 256), (128,)),       # K = 3 (padded to 4), 512-wide first layer; eight head outputs fill an 8-lane group
+    (2, 1, (1024, 256), (512,)),      # K = 2, 1024-wide first layer; one action; H = 512 with NR = 2: shared-memory backward
+    (6, 4, (256, 256), (512,)),       # Breakout's action count: loss_bwd_pair_reg_kernel<5>
+    (6, 8, (256, 256), (512,)),       # nine head outputs: the one-sample-per-warp loss head, one-column skinny kernel stays off
+    (6, 18, (256, 256), (512,)),      # the full Atari action set (19 outputs, NS = 32 skinny kernel)
+    (7, 6, (256, 512), (512,)),       # seven input features (odd row stride: scalar loads)
+])
+def test_minibatch_gradients_over_first_layer_and_head_shapes(dev, built_lib, D, A, enc, dec):
+    """The CUDA-core kernels around the trunk GEMMs pick their variant by shape (first layer: thin_fwd_pair_kernel<2|4|6|8>,
+    fast or guarded; loss head: four samples per warp pass up to 8 outputs, else one; backward half: head weights in
+    registers for H = 512 with 5 / 7 rows, else in shared memory; skinny weight gradients: four columns per thread up to 8
+    skinny columns, else one).  Every variant against the CPU oracle at the default engine."""
+    _minibatch_vs_oracle_under_device_decisions(dev, built_lib, 4, D, A, enc, dec, 8, seed=78 + D + A)
 
 
 def test_chunked_minibatch_is_equivalent_and_deterministic(dev):
