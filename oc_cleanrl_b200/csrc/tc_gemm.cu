@@ -400,6 +400,38 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *tm,
         ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tm)), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
         : "memory");
 }
+// warp-convergent forms for the TMA issuer of the conversion-free kernel (the whole warp runs the loop, one elected lane
+// issues; see umma_f16_lohi_elect): inside `if (lane == 0)` every UTMALDG costs an ELECT / 4 x R2UR.BROADCAST /
+// BRA.U.ANY loop, and ncu's source view showed the issuing lane busy 72 % of a 978-cycle stage (768 of them tensor work).
+// Same-box A/B (profiles/r02_tma_issue_ab.txt): forward GEMMs -2 % cycles, the others unchanged, results bitwise equal.
+__device__ __forceinline__ void mbar_expect_tx_elect(uint32_t bar, uint32_t bytes) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n\t}"
+        ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_elect(uint32_t dst, const CUtensorMap *tm, int c0, int c1, uint32_t bar) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];\n\t}"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tm)), "r"(c0), "r"(c1), "r"(bar)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_3d_elect(uint32_t dst, const CUtensorMap *tm, int c0, int c1, int c2, uint32_t bar) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];\n\t}"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tm)), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+        : "memory");
+}
+#ifdef OCPPO_TMA_LANE0
+constexpr bool kTmaConv = false;      // the single-lane issuer this replaced (A/B: profiles/r02_tma_issue_ab.txt)
+#else
+constexpr bool kTmaConv = true;
+#endif
 
 // epilogue side: a finished 32 x 32 chunk leaves through a swizzled 4 KB smem tile and one bulk tensor store
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap *tm, uint32_t src, int c0, int c1) {
@@ -692,7 +724,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
                         const float4 bb = __ldg(reinterpret_cast<const float4 *>(p.bias + n) + c);
                         o.x = fmaxf(o.x + bb.x, 0.f); o.y = fmaxf(o.y + bb.y, 0.f);
                         o.z = fmaxf(o.z + bb.z, 0.f); o.w = fmaxf(o.w + bb.w, 0.f);
-                        if (p.relu_bits != nullptr)
+                        if (p.relu_bits != nullptr && !(p.dbg & 4096))      // (4096: timing experiment without the decision bits)
                             word |= ((o.x > 0.f ? 1u : 0u) | (o.y > 0.f ? 2u : 0u) | (o.z > 0.f ? 4u : 0u) | (o.w > 0.f ? 8u : 0u)) << (4 * c);
                     } else if (MODE == SGEMM_DGRAD) {
                         if (bits) {
@@ -726,7 +758,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
                     *reinterpret_cast<float4 *>(out_tile + lane * 128 + ((c ^ swz) << 4)) = o;
                     if (MODE != SGEMM_WGRAD && m_loc + lane < p.M) run_max = fmaxf(fmaxf(run_max, fmaxf(fabsf(o.x), fabsf(o.y))), fmaxf(fabsf(o.z), fabsf(o.w)));
                 }
-                if (MODE == SGEMM_FWD && p.relu_bits != nullptr && m_loc + lane < p.M) p.relu_bits[rb_off + cc] = word;
+                if (MODE == SGEMM_FWD && p.relu_bits != nullptr && !(p.dbg & 4096) && m_loc + lane < p.M) p.relu_bits[rb_off + cc] = word;
                 if (PRE && MODE == SGEMM_DGRAD && p.colsum_part != nullptr) {
                     // bias gradient of the layer below = column sums of this output: the warp's 32 rows fold in a butterfly
                     // (31 shuffles; lane j ends with column j), then onto the warp's PRIVATE partial row in global memory
@@ -748,8 +780,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
                 __syncwarp();
                 if (lane == 0) {
                     if (!(p.dbg & 2)) {
-                        tma_store_2d(&tmC, out_s, n, row0);
-                        if (out16) tma_store_2d(&tmC2, out_s + 2048, n, row0);
+                        // (8192: timing experiment, every store lands in the tensor's first 4096 rows (L2-resident) -- the
+                        // store engine's shared-memory reads without the HBM write traffic; profiles/r02_store_experiments.txt)
+                        const int srow = (p.dbg & 8192) ? (row0 & 4095) : row0;
+                        tma_store_2d(&tmC, out_s, n, srow);
+                        if (out16) tma_store_2d(&tmC2, out_s + 2048, n, srow);
                         bulk_commit();
                     }
                     if (aux && cc + 1 < kChunks) {           // next aux chunk, once the store has read the tile
@@ -897,8 +932,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
               }
             }
         }
-        else if (warp == kEpiWarps + 1 && lane == 0) {
-            // ===================== TMA issuer (warp 9, both CTAs) =====================
+        else if (warp == kEpiWarps + 1 && ((PRE && kTmaConv) || lane == 0)) {
+            // ===================== TMA issuer (warp 9, both CTAs; PRE + kTmaConv: the whole warp, convergent) =====================
             // raw fp32 tiles of this CTA's A rows / B columns, straight into the hi slots of the stage ring
             const int rank_m = (int)cta_rank * TM, rank_n = (int)cta_rank * TBW;
             int stage = 0, sphase = 0;
@@ -913,6 +948,25 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
                         mbar_wait_lean(bar_empty + 8 * s, (uint32_t)(sphase ^ 1));
                         // (bring-up timing experiments, results are garbage: 512 = no B loads, 1024 = no A loads)
                         const bool skip_b = (p.dbg & 512) != 0, skip_a = (p.dbg & 1024) != 0;
+                        if constexpr (kTmaConv) {
+                            mbar_expect_tx_elect(bar, kStageBytesA + kStageBytesB);
+                            if (A_MN) {
+                                tma_load_3d_elect(st + kOffA16, &tmA, 0, k0, (t.m0 + rank_m) >> 6, bar);
+                                tma_load_3d_elect(st + kOffALo, &tmA2, 0, k0, (t.m0 + rank_m) >> 6, bar);
+                            } else {
+                                tma_load_2d_elect(st + kOffA16, &tmA, k0, t.m0 + rank_m, bar);
+                                tma_load_2d_elect(st + kOffALo, &tmA2, k0, t.m0 + rank_m, bar);
+                            }
+                            if (B_MN) {
+                                tma_load_3d_elect(st + kOffB16, &tmB, 0, k0, (t.n0 + rank_n) >> 6, bar);
+                                tma_load_3d_elect(st + kOffBLo, &tmB2, 0, k0, (t.n0 + rank_n) >> 6, bar);
+                            } else {
+                                tma_load_2d_elect(st + kOffB16, &tmB, k0, t.n0 + rank_n, bar);
+                                tma_load_2d_elect(st + kOffBLo, &tmB2, k0, t.n0 + rank_n, bar);
+                            }
+                            if (++stage == nstages) { stage = 0; sphase ^= 1; }
+                            continue;
+                        }
                         mbar_expect_tx(bar, (skip_a ? 0 : kStageBytesA) + (skip_b ? 0 : kStageBytesB));
                         if (skip_a) {
                         } else if (A_MN) {
