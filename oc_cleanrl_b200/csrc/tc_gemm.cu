@@ -758,7 +758,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CORR == 3 ? kProdTid
                     *reinterpret_cast<float4 *>(out_tile + lane * 128 + ((c ^ swz) << 4)) = o;
                     if (MODE != SGEMM_WGRAD && m_loc + lane < p.M) run_max = fmaxf(fmaxf(run_max, fmaxf(fabsf(o.x), fabsf(o.y))), fmaxf(fabsf(o.z), fabsf(o.w)));
                 }
-                if (MODE == SGEMM_FWD && p.relu_bits != nullptr && !(p.dbg & 4096) && m_loc + lane < p.M) p.relu_bits[rb_off + cc] = word;
+                if (MODE == SGEMM_FWD && p.relu_bits != nullptr && !(p.dbg & 4096)) {
+                    // the row's decision words of this warp's columns leave as ONE 16-byte (TN = 128: 8-byte) store per tile
+                    // instead of one 4-byte store per chunk: a quarter of the partial-sector writes
+                    if (cc == 0) rb.x = word; else if (cc == 1) rb.y = word; else if (cc == 2) rb.z = word; else rb.w = word;
+                    if (cc == kChunks - 1 && m_loc + lane < p.M) {
+                        if (TN == 256) *reinterpret_cast<uint4 *>(p.relu_bits + rb_off) = rb;
+                        else *reinterpret_cast<uint2 *>(p.relu_bits + rb_off) = make_uint2(rb.x, rb.y);
+                    }
+                }
                 if (PRE && MODE == SGEMM_DGRAD && p.colsum_part != nullptr) {
                     // bias gradient of the layer below = column sums of this output: the warp's 32 rows fold in a butterfly
                     // (31 shuffles; lane j ends with column j), then onto the warp's PRIVATE partial row in global memory
