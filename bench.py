@@ -52,8 +52,8 @@ EPOCHS, MINIBATCHES = 4, 4
 # they were taken on only; `roofline.traffic` is null for any other
 NCU_TRAFFIC = {
     # tc_gemm_kernel<FWD>, trunk layer 3 (M=524288, N=512, K=1024) inside a full-size minibatch of the learner path, engine 8:
-    # 2.354 GB read + 1.078 GB written; algorithmic 3.22 GB (the A pair and the C pair once)
-    ("pong", 4096, 128, "tc"): {"bytes": 3432000000, "source": "profiles/r02_gemm_ncu_minibatch.txt (tc_gemm_kernel<FWD> layer 3, one launch)"},
+    # 2.153 GB read + 1.072 GB written; algorithmic 3.22 GB (the A pair and the C pair once)
+    ("pong", 4096, 128, "tc"): {"bytes": 3225000000, "source": "profiles/r02_gemm_ncu_minibatch.txt (tc_gemm_kernel<FWD> layer 3, one launch)"},
 }
 # gae_tma_kernel, ncu --set full, cold L2 (profiles/r02_gae_ncu.txt): dram read + write per launch.  The outputs of the two
 # smaller sizes are still in the 126 MB L2 when the kernel ends, so ncu sees (almost) no DRAM write for them.
