@@ -1318,11 +1318,6 @@ int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
     OCPPO_CHECK_ARG(tc_gemm_supported(mode, a), "tc_gemm: unsupported shape M=%d N=%d K=%lld", a.M, a.N, (long long)a.K);
     const int splits = mode == SGEMM_WGRAD ? a.splits : 1;
     const bool split = a.single_acc == 0;
-    const int tn = tc_tile_n(a);
-    const int nt_n = a.N / tn, nt_m = (int)ceil_div(a.M, kPairM);
-    const int64_t ntiles64 = (int64_t)nt_n * nt_m * splits;
-    OCPPO_CHECK_ARG(ntiles64 < (1LL << 31), "tc_gemm: too many tiles");
-    const int ntiles = (int)ntiles64;
     typedef void (*Kern)(SgemmArgs, int, int, int, const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap,
                          const CUtensorMap, const CUtensorMap);
     constexpr int kVariants = 9;
@@ -1350,6 +1345,17 @@ int tc_gemm_launch(SgemmMode mode, const SgemmArgs &a_in, cudaStream_t stream) {
         sms_of[dev] = n;
     }
     const int sms = sms_of[dev];
+    int tn = tc_tile_n(a);
+    // a forward launch whose 256-column tiles would leave half of the CTA pairs idle (rollout inference: the decoder layer
+    // of a 4096-env batch has 32 tiles for 74 pairs) takes the conversion-free kernel's 128-column tile instead: twice
+    // the tiles, half the MMA work per stage, the same sums per output element (results are bit-identical)
+    if (mode == SGEMM_FWD && tn == 256 && a.f16x3 && a.a16_hi != nullptr && a.b16_hi != nullptr &&
+        2 * (int64_t)(a.N / 256) * ceil_div(a.M, kPairM) <= sms / 2)
+        tn = 128;
+    const int nt_n = a.N / tn, nt_m = (int)ceil_div(a.M, kPairM);
+    const int64_t ntiles64 = (int64_t)nt_n * nt_m * splits;
+    OCPPO_CHECK_ARG(ntiles64 < (1LL << 31), "tc_gemm: too many tiles");
+    const int ntiles = (int)ntiles64;
     const int grid = 2 * (ntiles < sms / 2 ? ntiles : sms / 2);     // CTA pairs
     CUtensorMap tmA, tmB, tmC, tmX, tmB2, tmA2, tmC2;
     // operands that already live in global memory as fp16 hi / lo pairs: both (PRE kernel: no conversion warps), or only
