@@ -520,7 +520,8 @@ static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, i
     }
     // which representations of the gradient entering layer l exist: fp32 in gbuf[cur], fp16 pair in g16[cur]
     bool dy32 = top_pair_scale == nullptr, dy16 = top_pair_scale != nullptr;
-    bool db_done = false;                 // the dgrad above already reduced this layer's bias gradient (fused column sums)
+    bool db_done = false;                 // the dgrad above already formed this layer's bias gradient (fused column sums) ...
+    int pending_parts = 0;                // ... as this many partial rows in colsum_part that still have to be folded
     const float *dy_scale = top_pair_scale;
     for (int l = h->n_layers - 1; l >= 0; --l) {
         const Layer &L = h->layers[l];
@@ -587,8 +588,23 @@ static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, i
                 OCPPO_TRY(ensure_act16(h, l - 1, B, s));
                 wa.b16_hi = h->act16_hi[l - 1]; wa.b16_lo = h->act16_lo[l - 1]; wa.amax_b = h->act_scale[l - 1];
                 OCPPO_TRY(sgemm_launch(SGEMM_WGRAD, wa, s));
-                OCPPO_TRY(launch_splitk_reduce(h->splitk, wa.splits, (int64_t)L.out_dim * L.in_dim, (int64_t)L.out_dim * L.in_dim,
-                                               h->grads + L.w_off, accumulate, h->sm_count, s));
+                // the bias gradient's column-sum partials are at hand -- left by the loss head, by the dgrad above
+                // (pending_parts) or formed now -- and fold in the same launch as the split-K partials
+                int blocks = pending_parts;
+                if (!db_done) {
+                    if (l == h->n_layers - 1 && top_colsum_blocks > 0) blocks = top_colsum_blocks;      // left by the loss head
+                    else OCPPO_TRY(launch_colsum16(h->g16_hi[cur], h->g16_lo[cur], rows, L.out_dim, dy_scale, h->colsum_part, &blocks, h->sm_count, s));
+                }
+                if (blocks > 0) {
+                    OCPPO_TRY(launch_wgrad_fold(h->splitk, wa.splits, (int64_t)L.out_dim * L.in_dim, (int64_t)L.out_dim * L.in_dim,
+                                                h->grads + L.w_off, accumulate, h->colsum_part, blocks, L.out_dim,
+                                                h->grads + L.b_off, accumulate, h->sm_count, s));
+                    db_done = true;
+                } else {
+                    OCPPO_TRY(launch_splitk_reduce(h->splitk, wa.splits, (int64_t)L.out_dim * L.in_dim, (int64_t)L.out_dim * L.in_dim,
+                                                   h->grads + L.w_off, accumulate, h->sm_count, s));
+                }
+                pending_parts = 0;
             }
             if (!db_done) {
                 int blocks = 0;
@@ -655,7 +671,10 @@ static int trunk_backward(ocppo_handle *h, const float *x, int64_t B, int cur, i
                 // [parts, in] partial rows read as [parts * in / out', out']: the flatten's frame groups fold with the rest
                 const Layer &Ln = h->layers[l - 1];
                 const int parts = tc_gemm_ctas(SGEMM_DGRAD, a, h->sm_count) * 4 * (L.in_dim / Ln.out_dim);
-                OCPPO_TRY(launch_colsum_reduce(h->colsum_part, parts, Ln.out_dim, h->grads + Ln.b_off, accumulate, s));
+                // layers above the first fold these partials together with their weight gradient's (launch_wgrad_fold, after
+                // the layer's WGRAD and before its DGRAD reuses colsum_part); the padded first layer folds them now
+                if (l - 1 > 0) pending_parts = parts;
+                else OCPPO_TRY(launch_colsum_reduce(h->colsum_part, parts, Ln.out_dim, h->grads + Ln.b_off, accumulate, s));
                 db_done = true;
             }
             if (pair_out) { dy16 = true; dy32 = false; dy_scale = h->amax + kBndGrad + l - 1; }

@@ -244,6 +244,9 @@ int launch_colsum16(const void *hi, const void *lo, int64_t rows, int cols, cons
 int launch_split16_colsum(const float *x, int64_t rows, int cols, const float *scale_src, void *hi, void *lo, float *part, int *blocks,
                           int sm_count, cudaStream_t stream);   // pair + column-sum partials of an fp32 tensor in one read
 int launch_colsum_reduce(const float *part, int parts, int cols, float *out, int accumulate, cudaStream_t stream);
+// split-K fold of a weight gradient + column-sum fold of its bias gradient in one launch (same sums as the two kernels)
+int launch_wgrad_fold(const float *part, int splits, int64_t stride, int64_t count, float *out, int acc_w, const float *cpart,
+                      int parts, int cols, float *cout, int acc_b, int sm_count, cudaStream_t stream);
 int launch_wnorm(const WnormSegs &segs, cudaStream_t stream);                     // outputs pre-zeroed
 int launch_absmax_multi(const AbsmaxSegs &segs, cudaStream_t stream);             // several small contiguous tensors, one launch; outs pre-zeroed
 // out[0] = max |x[r, c]| over an [rows, cols] view with row stride ld (zeroed first); absmax.cu

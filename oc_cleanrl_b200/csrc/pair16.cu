@@ -248,6 +248,45 @@ __global__ void __launch_bounds__(1024) colsum_reduce_kernel(const float *__rest
     }
 }
 
+// The two folds that follow a weight-gradient GEMM on pair storage, in ONE launch: blockIdx.y == 0 sums the split-K partial
+// tiles into dW (splitk_reduce_kernel's loop), blockIdx.y == 1 folds the column-sum partials of the bias gradient
+// (colsum_reduce_kernel's fixed tree).  Same sums in the same order as the two kernels, so the gradients are bit-identical;
+// four launches per minibatch fewer.
+__global__ void __launch_bounds__(1024) wgrad_fold_kernel(const float *__restrict__ part, int splits, int64_t stride, int64_t count,
+                                                         float *__restrict__ out, int acc_w, const float *__restrict__ cpart,
+                                                         int parts, int cols, float *__restrict__ cout, int acc_b) {
+    if (blockIdx.y == 0) {
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x) {
+            float s = 0.f;
+            for (int k = 0; k < splits; ++k) s += part[(int64_t)k * stride + i];
+            out[i] = acc_w ? out[i] + s : s;
+        }
+        return;
+    }
+    if ((int)blockIdx.x * 32 >= cols) return;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, c = blockIdx.x * 32 + lane;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    if (c < cols) {
+        int r = warp;
+        for (; r + 96 < parts; r += 128) {
+            s0 += __ldg(cpart + (int64_t)r * cols + c);
+            s1 += __ldg(cpart + (int64_t)(r + 32) * cols + c);
+            s2 += __ldg(cpart + (int64_t)(r + 64) * cols + c);
+            s3 += __ldg(cpart + (int64_t)(r + 96) * cols + c);
+        }
+        for (; r < parts; r += 32) s0 += __ldg(cpart + (int64_t)r * cols + c);
+    }
+    __shared__ float red[32][33];
+    red[warp][lane] = (s0 + s1) + (s2 + s3);
+    __syncthreads();
+    if (warp == 0 && c < cols) {
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < 32; ++w) s += red[w][lane];
+        cout[c] = acc_b ? cout[c] + s : s;
+    }
+}
+
 inline int grid_of(int64_t items, int sm_count) {
     int64_t g = ceil_div(items, 256 * 4);
     const int64_t cap = (int64_t)(sm_count > 0 ? sm_count : 148) * 8;
@@ -335,6 +374,20 @@ int launch_colsum_reduce(const float *part, int parts, int cols, float *out, int
     ProfScope ps(KC_AUX, 1, stream);
     colsum_reduce_kernel<<<(unsigned)ceil_div(cols, 32), 1024, 0, stream>>>(part, parts, cols, out, accumulate);
     OCPPO_LAUNCH_CHECK("colsum_reduce_kernel");
+    return OCPPO_OK;
+}
+
+int launch_wgrad_fold(const float *part, int splits, int64_t stride, int64_t count, float *out, int acc_w, const float *cpart,
+                      int parts, int cols, float *cout, int acc_b, int sm_count, cudaStream_t stream) {
+    OCPPO_CHECK_ARG(part && out && cpart && cout && splits >= 1 && count >= 1 && parts >= 1 && cols >= 1, "wgrad_fold: bad arguments");
+    int64_t gx = ceil_div(count, 1024);
+    const int64_t cap = (int64_t)(sm_count > 0 ? sm_count : 148) * 2;
+    if (gx > cap) gx = cap;
+    const int64_t cb = ceil_div(cols, 32);
+    if (gx < cb) gx = cb;
+    ProfScope ps(KC_AUX, 1, stream);
+    wgrad_fold_kernel<<<dim3((unsigned)gx, 2), 1024, 0, stream>>>(part, splits, stride, count, out, acc_w, cpart, parts, cols, cout, acc_b);
+    OCPPO_LAUNCH_CHECK("wgrad_fold_kernel");
     return OCPPO_OK;
 }
 
