@@ -568,6 +568,46 @@ def test_minibatch_gradients_over_first_layer_and_head_shapes(dev, built_lib, D,
     _minibatch_vs_oracle_under_device_decisions(dev, built_lib, 4, D, A, enc, dec, 8, seed=78 + D + A)
 
 
+def test_chunked_minibatch_on_the_tensor_core_path(dev, built_lib):
+    """A minibatch cut into chunks that each fit the tensor-core tiles (multiples of 128 rows): chunks after the first
+    ACCUMULATE into the gradient arena -- through wgrad_fold_kernel (split-K partials + bias column sums of a layer in one
+    launch), the skinny reductions and the heads' folds.  One minibatch step over 2,048 samples in 1 / 4 / 16 chunks: the
+    gradients agree to re-association accuracy, each run is bitwise repeatable, and the launch counters confirm that the
+    chunked runs took the tcgen05 kernels."""
+    from oc_cleanrl_b200 import _abi
+    from oc_cleanrl_b200.learner import LearnerArgs, PPOLearner
+    F, D, A, T, N = 4, 6, 6, 128, 16
+    n = T * N
+    data = make_rollout(T, N, F, D, seed=5)
+    rs = np.random.RandomState(3)
+    grads, stats_all = [], []
+    for chunk in (n, 512, 128, 512):
+        agent, _ = make_pair(dev, F, D, A, (256, 512, 1024, 512), (512,))
+        with torch.no_grad():
+            action, logp, _, value = agent.get_action_and_value(data["obs"].reshape(n, F, D).to(dev),
+                                                                torch.as_tensor(np.random.RandomState(4).randint(0, A, n)).to(dev))
+        rs2 = np.random.RandomState(3)
+        flat = (data["obs"].reshape(n, -1).to(dev), action, logp, torch.as_tensor(rs2.randn(n), dtype=torch.float32).to(dev),
+                torch.as_tensor(rs2.randn(n), dtype=torch.float32).to(dev), value.reshape(-1))
+        idx = torch.as_tensor(rs2.permutation(n), dtype=torch.int64).to(dev)
+        learner = PPOLearner(agent, LearnerArgs(num_envs=N, num_steps=T), chunk_rows=chunk)
+        agent._ensure_workspace(chunk, training=True, exact=True)
+        stats = torch.zeros(8, device=dev)
+        c0, _ = _abi.launch_counts()
+        _abi.check(built_lib.ocppo_minibatch_fwd_bwd(agent._handle.raw, *[_abi.ptr(t) for t in flat], _abi.ptr(idx), n,
+                                                     C.byref(learner._hp), _abi.ptr(stats), agent._stream()))
+        torch.cuda.synchronize()
+        c1, _ = _abi.launch_counts()
+        assert c1["gemm_wgrad"] - c0["gemm_wgrad"] == 4 * (n // chunk)          # four tcgen05 WGRADs per chunk
+        grads.append(agent_flat_grad(agent).copy())
+        stats_all.append(stats.cpu().numpy().copy())
+    assert np.array_equal(grads[1], grads[3]) and np.array_equal(stats_all[1], stats_all[3])     # repeatable
+    for g in grads[1:3]:
+        assert rel_err(g, grads[0]) < 2e-5                    # chunking only re-associates sums (and re-derives scales)
+    for st in stats_all[1:3]:
+        assert np.allclose(st[:7], stats_all[0][:7], rtol=1e-5, atol=1e-7)
+
+
 def test_chunked_minibatch_is_equivalent_and_deterministic(dev):
     g, agent, _, data, (F, D, A, T, N) = _golden_case(dev, "small_pong")
     tensors = (data["obs"].to(dev), torch.as_tensor(g["actions"]).to(dev), torch.as_tensor(g["logprobs_old"]).to(dev),
